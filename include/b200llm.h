@@ -1,0 +1,239 @@
+/*
+ * b200llm.h -- C ABI of the B200-native Llama decode engine (libb200llm.so).
+ *
+ * Drop-in boundary.  The reference (Rajwardhan0511/LLM-Based-Apache-Spark-Optimization)
+ * reaches the decode path only through
+ *     res = ollama.generate(model=..., system=..., prompt=...);  res.response
+ * at six call sites: Flask/app.py:102-107 and :160-166, FastAPI/app.py:85-90 and
+ * :105-111, Model_Evaluation_&_Comparision.py:23-45 and :114-120.  Everything below
+ * that call (Ollama server + llama.cpp: tokenise -> prefill -> decode loop -> sampler)
+ * is replaced by this library; the Python package `ollama/` shipped in this repo binds
+ * these entry points with ctypes.
+ *
+ * Conventions
+ *   - plain C, no C++/torch types; every function returns 0 on success or a negative
+ *     B200LLM_E* code; b200llm_last_error() gives the message of the calling thread's
+ *     last failure (valid until that thread's next failing call).
+ *   - all device buffers (weights, KV pool, workspace) are allocated by the host
+ *     (PyTorch) and only BORROWED: the engine never frees them and the caller keeps
+ *     them alive until b200llm_destroy().  The engine owns its stream, events and
+ *     CUDA graphs only.
+ *   - one engine = one GPU (one process per GPU; tensor-parallel groups pass
+ *     tp_rank/tp_size and an NCCL unique id).
+ *   - there is no CPU fallback: every entry point fails with B200LLM_ENODEV when no
+ *     sm_100 device is present.
+ */
+#ifndef B200LLM_H_
+#define B200LLM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200LLM_ABI_VERSION 1
+
+enum {
+    B200LLM_OK = 0,
+    B200LLM_EINVAL = -1,   /* bad argument / unsupported shape            */
+    B200LLM_ENODEV = -2,   /* no sm_100 device, or wrong device current   */
+    B200LLM_ECUDA = -3,    /* a CUDA runtime call or kernel failed        */
+    B200LLM_ESTATE = -4,   /* call order violated (weights not bound ...) */
+    B200LLM_ENCCL = -5,    /* NCCL missing or an NCCL call failed         */
+    B200LLM_ENOMEM = -6    /* caller-provided buffer too small            */
+};
+
+typedef struct b200llm_engine b200llm_engine;
+
+/* Geometry of the whole (un-sharded) model + this rank's engine limits.
+ * Replaces: the model Ollama resolves from the `model=` string of
+ * ollama.generate (Flask/app.py:103,161; FastAPI/app.py:86,106). */
+typedef struct b200llm_config {
+    int32_t abi_version;        /* B200LLM_ABI_VERSION */
+    int32_t d;                  /* hidden size */
+    int32_t n_layers;
+    int32_t n_q;                /* query heads (global) */
+    int32_t n_kv;               /* key/value heads (global) */
+    int32_t head_dim;           /* 64 or 128 */
+    int32_t ffn;                /* MLP inner size (global) */
+    int32_t vocab;              /* global vocabulary */
+    float rms_eps;
+    int32_t page_tokens;        /* tokens per KV page (16) */
+    int32_t max_lanes;          /* concurrent sequences the engine tracks */
+    int32_t max_pages_per_lane; /* page-table width: max context = this * page_tokens */
+    int32_t max_rows;           /* max rows (tokens) of one forward pass: >= max decode batch and prefill chunk */
+    int32_t tp_rank, tp_size;   /* tensor-parallel placement (1 = replica) */
+    int32_t device;             /* CUDA ordinal; must be the current device of the calling thread */
+    int32_t use_graphs;         /* capture the decode step into a CUDA graph */
+    int32_t use_pdl;            /* programmatic dependent launch between kernels */
+    int32_t attn_splits;        /* split-T factor of decode attention, 0 = auto */
+    void *stream;               /* cudaStream_t to run on; NULL = engine creates its own */
+    const void *nccl_unique_id; /* 128-byte ncclUniqueId when tp_size > 1, else NULL */
+} b200llm_config;
+
+/* Packed weight tensors (bf16 unless noted; row-major [rows, cols]).  Layout is the
+ * engine's own (DESIGN.md "Data layout in HBM"); b200llm.weights.pack() builds it
+ * from HF-named tensors. */
+enum {
+    B200LLM_W_EMBED = 0,      /* [vocab, d]                       global            */
+    B200LLM_W_LM_HEAD = 1,    /* [vocab/tp, d]   rows of this rank (may alias EMBED) */
+    B200LLM_W_FINAL_NORM = 2, /* [d]                                                 */
+    B200LLM_W_INV_FREQ = 3,   /* fp32 [head_dim/2]                global             */
+    B200LLM_W_ATTN_NORM = 4,  /* [d]                              per layer          */
+    B200LLM_W_QKV = 5,        /* [(n_q+2 n_kv)/tp * head_dim, d]  per layer; q,k rows pair-interleaved */
+    B200LLM_W_O = 6,          /* [d, n_q/tp * head_dim]           per layer          */
+    B200LLM_W_MLP_NORM = 7,   /* [d]                              per layer          */
+    B200LLM_W_GATE_UP = 8,    /* [2 ffn/tp, d]  row 2i = gate_i, row 2i+1 = up_i     */
+    B200LLM_W_DOWN = 9        /* [d, ffn/tp]                      per layer          */
+};
+
+typedef struct b200llm_tensor_desc {
+    int32_t kind;   /* B200LLM_W_* */
+    int32_t layer;  /* -1 for global tensors */
+    const void *dev;
+    int64_t rows, cols;
+} b200llm_tensor_desc;
+
+/* Sampler chain of one lane.  Replaces: Ollama's sampler (Modelfile PARAMETERs /
+ * `options=`); temperature 0 = greedy argmax with lowest-id tie-break (parity mode). */
+typedef struct b200llm_sampling {
+    float temperature;    /* 0 = greedy */
+    int32_t top_k;        /* <= 0: 1024 candidates */
+    float top_p;          /* >= 1: off */
+    float repeat_penalty; /* 1 = off; applied to the last 64 tokens of the lane */
+    uint64_t seed;
+} b200llm_sampling;
+
+typedef struct b200llm_timing {
+    float prefill_ms;      /* device time of the last b200llm_prefill  */
+    float decode_ms;       /* device time of the last b200llm_decode   */
+    int32_t prefill_tokens;
+    int32_t decode_steps;
+    int64_t kernel_launches; /* kernels of this library launched by the last decode call */
+} b200llm_timing;
+
+const char *b200llm_last_error(void);
+int b200llm_abi_version(void);
+
+/* ---- engine life cycle ---------------------------------------------------------- */
+int b200llm_create(const b200llm_config *cfg, b200llm_engine **out);
+int b200llm_destroy(b200llm_engine *e);
+/* Rank 0 of a tensor-parallel group calls this and hands the 128 bytes to the other
+ * ranks (any host channel); every rank passes them in b200llm_config.nccl_unique_id. */
+int b200llm_nccl_unique_id(void *out128);
+/* Bytes of scratch (activations, logits, attention split partials) the host must bind. */
+int b200llm_workspace_bytes(const b200llm_config *cfg, size_t *bytes);
+/* Bytes of one KV page across all layers of this rank: n_layers * 2 * (n_kv/tp) * page_tokens * head_dim * 2. */
+int b200llm_kv_page_bytes(const b200llm_config *cfg, size_t *bytes);
+int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, int32_t n);
+int b200llm_bind_kv_pool(b200llm_engine *e, void *dev, size_t bytes);
+int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes);
+
+/* ---- sequence ("lane") state ------------------------------------------------------ */
+/* Host-side page allocator decides the pages; this copies lane's table (n entries). */
+int b200llm_set_page_table(b200llm_engine *e, int32_t lane, const int32_t *pages, int32_t n);
+int b200llm_set_sampling(b200llm_engine *e, int32_t lane, const b200llm_sampling *s);
+/* Overwrite the lane's next input token / position (teacher forcing, resume). */
+int b200llm_set_lane(b200llm_engine *e, int32_t lane, int32_t next_token, int32_t pos);
+
+/* ---- the hot path ---------------------------------------------------------------- */
+/* Prefill: run `n` prompt ids (host buffer) of `lane` starting at position pos0, append
+ * their K/V to the lane's pages, sample the first new token into the lane. Asynchronous. */
+int b200llm_prefill(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t n, int32_t pos0);
+/* Decode: n_steps autoregressive steps for the given lanes as one batch; sampled tokens
+ * feed back on the device (no host round trip between steps). Asynchronous. */
+int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int32_t n_steps);
+/* Wait and copy out the tokens produced by the last decode call: out[step * n_lanes + i]. */
+int b200llm_read_tokens(b200llm_engine *e, int32_t *out, int32_t n_steps, int32_t n_lanes);
+/* Wait and read the first token sampled by the last prefill of `lane`. */
+int b200llm_read_lane(b200llm_engine *e, int32_t lane, int32_t *next_token, int32_t *pos);
+/* Test hook for logits parity: fp32 logits (this rank's vocab rows) of batch row `row`
+ * of the last forward pass. */
+int b200llm_step_logits(b200llm_engine *e, int32_t row, float *out, int32_t n);
+int b200llm_sync(b200llm_engine *e);
+int b200llm_last_timing(b200llm_engine *e, b200llm_timing *t);
+/* The cudaStream_t the engine launches on (for CUDA-event timing by the caller). */
+void *b200llm_stream(b200llm_engine *e);
+
+/* ---- single kernels (unit-test and profiling entry points; same kernels the engine runs) */
+
+/* bf16 weight GEMV  y[b, n] = sum_k W[n, k] * x[b, k],  fp32 accumulate, bs <= 4.
+ * Optional fused RMSNorm prologue (norm_gain != NULL) and epilogue `epi`. */
+enum {
+    B200LLM_EPI_STORE = 0,    /* y -> out fp32 [bs, N]                                   */
+    B200LLM_EPI_RESIDUAL = 1, /* out[b, n] += y                                          */
+    B200LLM_EPI_SWIGLU = 2,   /* rows (2i, 2i+1) = (gate, up): out[b, i] = silu(g) * u   */
+    B200LLM_EPI_QKV_ROPE = 3, /* RoPE on q/k pairs; q -> out fp32; k, v -> bf16 KV pages */
+    B200LLM_EPI_LOGITS = 4    /* y -> out fp32 and per-CTA (max, argmax) partials        */
+};
+typedef struct b200llm_gemv_args {
+    const void *w;           /* bf16 [N, K] */
+    const float *x;          /* fp32 [bs, x_stride] */
+    int64_t x_stride;
+    const void *norm_gain;   /* bf16 [K] or NULL */
+    float rms_eps;
+    float *out;              /* fp32 [bs, out_stride] */
+    int64_t out_stride;
+    int32_t N, K, bs, epi;
+    /* QKV_ROPE only */
+    int32_t n_q, n_kv, head_dim, page_tokens, max_pages_per_lane;
+    const float *inv_freq;   /* fp32 [head_dim/2] */
+    const int32_t *row_lane; /* [bs] */
+    const int32_t *row_pos;  /* [bs] */
+    const int32_t *page_table; /* [lanes, max_pages_per_lane] */
+    void *k_pages;           /* bf16 [pages, n_kv, page_tokens, head_dim] of this layer */
+    void *v_pages;
+    /* LOGITS only */
+    float *part_max;         /* fp32 [bs, grid] */
+    int32_t *part_idx;       /* int32 [bs, grid] */
+    int32_t logits_idx_offset; /* added to the argmax ids (vocab-parallel shards) */
+    int32_t grid_hint;       /* 0 = auto */
+} b200llm_gemv_args;
+int b200llm_op_gemv(const b200llm_gemv_args *a, void *stream);
+/* Number of CTAs b200llm_op_gemv will launch for (N, K, bs, epi): size of the LOGITS partials. */
+int b200llm_op_gemv_grid(int32_t N, int32_t K, int32_t bs, int32_t epi, int32_t *grid);
+
+/* Paged GQA decode attention with split-T partials merged by the last CTA to finish.
+ * `scratch` holds the split partials and arrival counters; it must be zeroed once
+ * before first use (the kernel leaves the counters at zero). */
+typedef struct b200llm_attn_args {
+    const float *q;          /* fp32 [bs, n_q * head_dim] (RoPE applied) */
+    float *out;              /* fp32 [bs, n_q * head_dim] */
+    const void *k_pages;     /* bf16 [pages, n_kv, page_tokens, head_dim] */
+    const void *v_pages;
+    const int32_t *row_lane; /* [bs] */
+    const int32_t *row_pos;  /* [bs]: attends to tokens 0..pos inclusive */
+    const int32_t *page_table;
+    int32_t bs, n_q, n_kv, head_dim, page_tokens, max_pages_per_lane, n_splits;
+    void *scratch;
+    size_t scratch_bytes;
+} b200llm_attn_args;
+int b200llm_op_attn_decode(const b200llm_attn_args *a, void *stream);
+int b200llm_op_attn_scratch_bytes(int32_t bs, int32_t n_q, int32_t n_kv, int32_t head_dim,
+                                  int32_t n_splits, size_t *bytes);
+
+/* Sampler over fp32 logits [bs, vocab] (+ the LOGITS partials for greedy rows). */
+typedef struct b200llm_sample_args {
+    const float *logits;     /* fp32 [bs, vocab]; may be modified (repeat penalty) */
+    int32_t bs, vocab;
+    const float *part_max;   /* [bs, n_part] or NULL */
+    const int32_t *part_idx;
+    int32_t n_part;
+    const b200llm_sampling *params; /* DEVICE pointer, [bs] */
+    const int32_t *history;  /* DEVICE int32 [bs, 64] recent tokens (-1 = empty) or NULL */
+    uint64_t step;           /* RNG counter */
+    int32_t *out_token;      /* DEVICE int32 [bs] */
+} b200llm_sample_args;
+int b200llm_op_sample(const b200llm_sample_args *a, void *stream);
+
+/* Seeded random-init weights, generated on the device (no checkpoints exist offline):
+ * element i of stream `seed` (see DESIGN.md "Weights"); bf16 out. */
+int b200llm_op_fill_weights(void *dev_bf16, uint64_t n, uint64_t seed, float sigma, float mean,
+                            void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200LLM_H_ */

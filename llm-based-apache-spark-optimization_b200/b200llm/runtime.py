@@ -1,0 +1,59 @@
+"""Model manager behind the `ollama` shim: resolves a model name to a loaded engine,
+loading it on first use and keeping it resident (what Ollama's scheduler + keep_alive do
+for the reference).  Weights are seeded random-init: the reference's GGUF
+blobs are not on this box (BASELINE.json: "random-init weights").
+"""
+from __future__ import annotations
+
+import os
+import threading
+import time
+from dataclasses import dataclass
+from typing import Dict
+
+import torch
+
+from . import _lib, geometry, weights
+from .engine import Engine
+from .tokenizer import ByteTokenizer
+
+SEED = 0xB200
+
+
+@dataclass
+class LoadedModel:
+    name: str
+    engine: Engine
+    tokenizer: ByteTokenizer
+    load_ns: int
+
+
+_models: Dict[str, LoadedModel] = {}
+_lock = threading.Lock()
+
+
+def get_model(name: str) -> LoadedModel:
+    geo = geometry.resolve(name)          # KeyError -> the shim turns it into ResponseError 404
+    with _lock:
+        m = _models.get(geo.name)
+        if m is not None:
+            return LoadedModel(m.name, m.engine, m.tokenizer, 0)
+        if not torch.cuda.is_available():
+            raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
+        t0 = time.perf_counter_ns()
+        dev = int(os.environ.get("B200LLM_DEVICE", "0"))
+        torch.cuda.set_device(dev)
+        w = weights.random_init(geo, SEED, dev)
+        eng = Engine(geo, w, device=dev, max_lanes=int(os.environ.get("B200LLM_MAX_LANES", "8")),
+                     max_ctx=int(os.environ.get("B200LLM_NUM_CTX", "4096")),
+                     max_rows=int(os.environ.get("B200LLM_MAX_ROWS", "64")))
+        m = LoadedModel(geo.name, eng, ByteTokenizer(geo.vocab), time.perf_counter_ns() - t0)
+        _models[geo.name] = m
+        return m
+
+
+def unload_all() -> None:
+    with _lock:
+        for m in _models.values():
+            m.engine.close()
+        _models.clear()

@@ -1,0 +1,782 @@
+// engine.cu -- host side of the C ABI (include/b200llm.h): the decode engine that replaces
+// what sits below `ollama.generate` in the reference (Ollama server + llama.cpp runner;
+// call sites Flask/app.py:102-107,160-166, FastAPI/app.py:85-90,105-111).
+//
+// The engine owns a stream, the CUDA graphs of the decode step (one per batch size) and,
+// for tensor-parallel groups, an NCCL communicator.  All device memory is borrowed from
+// the host (PyTorch).  One forward pass over `rows` token rows is
+//   embed -> L x [ rmsnorm+qkv GEMV (+RoPE, +paged-KV append) -> split-T paged attention
+//                  -> o_proj GEMV (+residual | all-reduce) -> rmsnorm+gate/up GEMV (+SwiGLU)
+//                  -> down GEMV (+residual | all-reduce) ] -> rmsnorm+lm_head GEMV (+argmax
+//   partials) -> sampler (feeds the token and position back on the device).
+#include <dlfcn.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <map>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+
+static thread_local char g_err[1024] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// ---------------------------------------------------------------- NCCL (dlopen'ed, optional)
+typedef struct ncclComm *ncclComm_t;
+struct Id128 {
+    char b[128];
+};
+struct NcclApi {
+    void *lib = nullptr;
+    int (*GetUniqueId)(void *) = nullptr;
+    int (*CommInitRank)(ncclComm_t *, int, /* ncclUniqueId by value: 128 bytes */ Id128, int) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+static NcclApi g_nccl;
+static std::mutex g_nccl_mu;
+constexpr int kNcclFloat32 = 7, kNcclInt8 = 0, kNcclSum = 0;
+
+static int nccl_load() {
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (g_nccl.lib) return B200LLM_OK;
+    void *lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!lib) {
+        const char *env = getenv("B200LLM_NCCL_LIB");
+        lib = dlopen(env ? env : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    }
+    if (!lib) {
+        set_error("NCCL: cannot load libnccl.so.2 (set B200LLM_NCCL_LIB): %s", dlerror());
+        return B200LLM_ENCCL;
+    }
+    g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))dlsym(lib, "ncclCommInitRank");
+    g_nccl.AllReduce = (decltype(g_nccl.AllReduce))dlsym(lib, "ncclAllReduce");
+    g_nccl.AllGather = (decltype(g_nccl.AllGather))dlsym(lib, "ncclAllGather");
+    g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(lib, "ncclCommDestroy");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(lib, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.AllGather) {
+        set_error("NCCL: symbols missing in libnccl.so.2");
+        return B200LLM_ENCCL;
+    }
+    g_nccl.lib = lib;
+    return B200LLM_OK;
+}
+#define B200_NCCL_OK(expr)                                                                         \
+    do {                                                                                           \
+        int _r = (expr);                                                                           \
+        if (_r != 0) {                                                                             \
+            set_error("%s failed: %s", #expr, g_nccl.GetErrorString ? g_nccl.GetErrorString(_r) : "?"); \
+            return B200LLM_ENCCL;                                                                  \
+        }                                                                                          \
+    } while (0)
+
+}  // namespace b200
+
+using namespace b200;
+
+constexpr int kMaxDecodeSteps = 4096;
+
+struct LayerW {
+    const void *attn_norm = nullptr, *wqkv = nullptr, *wo = nullptr, *mlp_norm = nullptr, *wgu = nullptr,
+               *wdown = nullptr;
+};
+
+struct b200llm_engine {
+    b200llm_config cfg;
+    int nq_l, nkv_l, ffn_l, vocab_l, max_ctx;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    bool pdl = false;
+    // weights
+    const void *embed = nullptr, *lm_head = nullptr, *final_norm = nullptr;
+    const float *inv_freq = nullptr;
+    std::vector<LayerW> layers;
+    bool weights_bound = false;
+    // kv pool: [layer][K|V][page][kv head][token][dim] bf16
+    uint8_t *kv = nullptr;
+    int n_pages = 0;
+    size_t kv_half_stride = 0;  // bytes of one layer's K (or V) region
+    // workspace
+    uint8_t *ws = nullptr;
+    float *h, *q, *att, *act, *delta, *logits, *part_max;
+    int32_t *part_idx, *row_lane, *row_pos, *row_token, *pf_lane, *pf_pos, *pf_token, *lane_token, *lane_pos,
+        *lane_hist, *page_table, *gen_out, *step_ctr;
+    float *gath_max;
+    int32_t *gath_idx;
+    b200llm_sampling *lane_samp;
+    void *attn_scratch;
+    size_t attn_scratch_bytes;
+    int lm_grid = 0;
+    int attn_splits = 1;
+    // graphs
+    std::map<int, cudaGraphExec_t> graphs;
+    std::map<int, int64_t> graph_launches;  // kernels per captured step
+    // nccl
+    ncclComm_t comm = nullptr;
+    // timing
+    cudaEvent_t ev[4];
+    b200llm_timing timing{};
+    int64_t launches = 0;  // counted while building a pass
+    int last_rows = 0;
+    int last_logit_rows = 0;
+};
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int check_cfg(const b200llm_config *c) {
+    B200_REQUIRE(c != nullptr, "config is NULL");
+    B200_REQUIRE(c->abi_version == B200LLM_ABI_VERSION, "ABI version mismatch: caller %d, library %d", c->abi_version,
+                 B200LLM_ABI_VERSION);
+    B200_REQUIRE(c->tp_size >= 1 && c->tp_rank >= 0 && c->tp_rank < c->tp_size, "bad tp_rank/tp_size");
+    B200_REQUIRE(c->head_dim == 64 || c->head_dim == 128, "head_dim must be 64 or 128");
+    B200_REQUIRE(c->page_tokens == 16, "page_tokens must be 16");
+    B200_REQUIRE(c->n_q % c->tp_size == 0 && c->n_kv % c->tp_size == 0 && c->ffn % c->tp_size == 0 &&
+                     c->vocab % c->tp_size == 0,
+                 "heads/ffn/vocab must divide by tp_size");
+    B200_REQUIRE(c->n_q % c->n_kv == 0, "n_q must be a multiple of n_kv");
+    B200_REQUIRE(c->d % 8 == 0 && (c->ffn / c->tp_size) % 8 == 0, "d and ffn/tp must be multiples of 8");
+    B200_REQUIRE(c->max_rows >= 1 && c->max_lanes >= 1 && c->max_pages_per_lane >= 1, "bad engine limits");
+    return B200LLM_OK;
+}
+
+struct WsLayout {
+    size_t h, q, att, act, delta, logits, part_max, part_idx, row_lane, row_pos, row_token, pf_lane, pf_pos,
+        pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
+        attn_scratch, total;
+    size_t attn_scratch_bytes;
+    int lm_grid, attn_splits;
+};
+
+static int auto_splits(const b200llm_config *c) {
+    if (c->attn_splits > 0) return c->attn_splits > 64 ? 64 : c->attn_splits;
+    int nkv_l = c->n_kv / c->tp_size;
+    int s = (2 * kNumSMs + nkv_l - 1) / nkv_l;
+    return s < 1 ? 1 : (s > 32 ? 32 : s);
+}
+
+static void ws_layout(const b200llm_config *c, WsLayout *w) {
+    const int tp = c->tp_size;
+    const size_t R = c->max_rows, Lm = c->max_lanes;
+    const size_t nq_l = c->n_q / tp, nkv_l = c->n_kv / tp, ffn_l = c->ffn / tp, vocab_l = c->vocab / tp;
+    const size_t max_ctx = (size_t)c->max_pages_per_lane * c->page_tokens;
+    w->lm_grid = gemv_grid((int)vocab_l, c->d, 1, B200LLM_EPI_LOGITS, 0);
+    // batched lm_head (bs up to 4) may pick a larger grid; use the maximum
+    for (int bs = 2; bs <= 4; ++bs) {
+        int g = gemv_grid((int)vocab_l, c->d, bs, B200LLM_EPI_LOGITS, 0);
+        if (g > w->lm_grid) w->lm_grid = g;
+    }
+    w->attn_splits = auto_splits(c);
+    w->attn_scratch_bytes = attn_scratch_bytes((int)R, (int)nq_l, (int)nkv_l, c->head_dim, w->attn_splits);
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        size_t at = o;
+        o = align_up(o + bytes, 256);
+        return at;
+    };
+    w->h = take(R * c->d * 4);
+    w->q = take(R * nq_l * c->head_dim * 4);
+    w->att = take(R * nq_l * c->head_dim * 4);
+    w->act = take(R * ffn_l * 4);
+    w->delta = take(R * c->d * 4);
+    w->logits = take(R * vocab_l * 4);
+    w->part_max = take(R * w->lm_grid * 4);
+    w->part_idx = take(R * w->lm_grid * 4);
+    w->row_lane = take(R * 4);
+    w->row_pos = take(R * 4);
+    w->row_token = take(R * 4);
+    w->pf_lane = take(max_ctx * 4);
+    w->pf_pos = take(max_ctx * 4);
+    w->pf_token = take(max_ctx * 4);
+    w->lane_token = take(Lm * 4);
+    w->lane_pos = take(Lm * 4);
+    w->lane_hist = take(Lm * 64 * 4);
+    w->page_table = take(Lm * c->max_pages_per_lane * 4);
+    w->gen_out = take((size_t)kMaxDecodeSteps * R * 4);
+    w->step_ctr = take(256);
+    w->lane_samp = take(Lm * sizeof(b200llm_sampling));
+    w->gath_max = take(R * tp * w->lm_grid * 4);
+    w->gath_idx = take(R * tp * w->lm_grid * 4);
+    w->attn_scratch = take(w->attn_scratch_bytes);
+    w->total = o;
+}
+
+extern "C" {
+
+const char *b200llm_last_error(void) { return g_err; }
+int b200llm_abi_version(void) { return B200LLM_ABI_VERSION; }
+
+int b200llm_workspace_bytes(const b200llm_config *cfg, size_t *bytes) {
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    B200_REQUIRE(bytes != nullptr, "bytes is NULL");
+    WsLayout w;
+    ws_layout(cfg, &w);
+    *bytes = w.total;
+    return B200LLM_OK;
+}
+
+int b200llm_kv_page_bytes(const b200llm_config *cfg, size_t *bytes) {
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    B200_REQUIRE(bytes != nullptr, "bytes is NULL");
+    *bytes = (size_t)cfg->n_layers * 2 * (cfg->n_kv / cfg->tp_size) * cfg->page_tokens * cfg->head_dim * 2;
+    return B200LLM_OK;
+}
+
+static int require_device_any() {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        set_error("no CUDA device: this library has no CPU fallback (%s)", cudaGetErrorString(e));
+        return B200LLM_ENODEV;
+    }
+    int cur = 0, major = 0;
+    B200_CUDA_OK(cudaGetDevice(&cur));
+    B200_CUDA_OK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, cur));
+    if (major != 10) {
+        set_error("current device is sm_%dx; this library is built for sm_100a (B200) only", major);
+        return B200LLM_ENODEV;
+    }
+    return B200LLM_OK;
+}
+
+static int require_device(int device) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        set_error("no CUDA device: this library has no CPU fallback (%s)", cudaGetErrorString(e));
+        return B200LLM_ENODEV;
+    }
+    int cur = -1;
+    B200_CUDA_OK(cudaGetDevice(&cur));
+    if (cur != device) {
+        set_error("device %d requested but device %d is current on this thread", device, cur);
+        return B200LLM_ENODEV;
+    }
+    cudaDeviceProp p;
+    B200_CUDA_OK(cudaGetDeviceProperties(&p, device));
+    if (p.major != 10) {
+        set_error("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, p.major, p.minor);
+        return B200LLM_ENODEV;
+    }
+    return B200LLM_OK;
+}
+
+int b200llm_create(const b200llm_config *cfg, b200llm_engine **out) {
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    B200_REQUIRE(out != nullptr, "out is NULL");
+    rc = require_device(cfg->device);
+    if (rc) return rc;
+    b200llm_engine *e = new b200llm_engine();
+    e->cfg = *cfg;
+    e->nq_l = cfg->n_q / cfg->tp_size;
+    e->nkv_l = cfg->n_kv / cfg->tp_size;
+    e->ffn_l = cfg->ffn / cfg->tp_size;
+    e->vocab_l = cfg->vocab / cfg->tp_size;
+    e->max_ctx = cfg->max_pages_per_lane * cfg->page_tokens;
+    e->layers.resize(cfg->n_layers);
+    e->pdl = cfg->use_pdl != 0;
+    if (cfg->stream) {
+        e->stream = (cudaStream_t)cfg->stream;
+    } else {
+        if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) {
+            set_error("cudaStreamCreate failed");
+            delete e;
+            return B200LLM_ECUDA;
+        }
+        e->own_stream = true;
+    }
+    for (int i = 0; i < 4; ++i) cudaEventCreate(&e->ev[i]);
+    if (cfg->tp_size > 1) {
+        rc = nccl_load();
+        if (rc) {
+            delete e;
+            return rc;
+        }
+        if (!cfg->nccl_unique_id) {
+            set_error("tp_size > 1 needs nccl_unique_id");
+            delete e;
+            return B200LLM_EINVAL;
+        }
+        Id128 id;
+        memcpy(id.b, cfg->nccl_unique_id, 128);
+        int r = g_nccl.CommInitRank(&e->comm, cfg->tp_size, id, cfg->tp_rank);
+        if (r != 0) {
+            set_error("ncclCommInitRank failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+            delete e;
+            return B200LLM_ENCCL;
+        }
+    }
+    *out = e;
+    return B200LLM_OK;
+}
+
+int b200llm_nccl_unique_id(void *out128) {
+    B200_REQUIRE(out128 != nullptr, "out is NULL");
+    int rc = nccl_load();
+    if (rc) return rc;
+    B200_NCCL_OK(g_nccl.GetUniqueId(out128));
+    return B200LLM_OK;
+}
+
+int b200llm_destroy(b200llm_engine *e) {
+    if (!e) return B200LLM_OK;
+    cudaStreamSynchronize(e->stream);
+    for (auto &kv : e->graphs) cudaGraphExecDestroy(kv.second);
+    if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
+    for (int i = 0; i < 4; ++i) cudaEventDestroy(e->ev[i]);
+    if (e->own_stream) cudaStreamDestroy(e->stream);
+    delete e;
+    return B200LLM_OK;
+}
+
+int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, int32_t n) {
+    B200_REQUIRE(e && descs && n > 0, "bind_weights: bad arguments");
+    const b200llm_config &c = e->cfg;
+    for (int i = 0; i < n; ++i) {
+        const b200llm_tensor_desc &t = descs[i];
+        B200_REQUIRE(t.dev != nullptr && ((uintptr_t)t.dev % 16) == 0, "tensor %d: NULL or unaligned device pointer", i);
+        auto shape = [&](int64_t r, int64_t cc) {
+            if (t.rows != r || t.cols != cc) {
+                set_error("tensor kind %d layer %d: shape [%lld, %lld], expected [%lld, %lld]", t.kind, t.layer,
+                          (long long)t.rows, (long long)t.cols, (long long)r, (long long)cc);
+                return false;
+            }
+            return true;
+        };
+        const int64_t qkv_rows = (int64_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim;
+        if (t.kind >= B200LLM_W_ATTN_NORM) B200_REQUIRE(t.layer >= 0 && t.layer < c.n_layers, "tensor %d: bad layer", i);
+        switch (t.kind) {
+            case B200LLM_W_EMBED: if (!shape(c.vocab, c.d)) return B200LLM_EINVAL; e->embed = t.dev; break;
+            case B200LLM_W_LM_HEAD: if (!shape(e->vocab_l, c.d)) return B200LLM_EINVAL; e->lm_head = t.dev; break;
+            case B200LLM_W_FINAL_NORM: if (!shape(1, c.d)) return B200LLM_EINVAL; e->final_norm = t.dev; break;
+            case B200LLM_W_INV_FREQ: if (!shape(1, c.head_dim / 2)) return B200LLM_EINVAL; e->inv_freq = (const float *)t.dev; break;
+            case B200LLM_W_ATTN_NORM: if (!shape(1, c.d)) return B200LLM_EINVAL; e->layers[t.layer].attn_norm = t.dev; break;
+            case B200LLM_W_QKV: if (!shape(qkv_rows, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wqkv = t.dev; break;
+            case B200LLM_W_O: if (!shape(c.d, (int64_t)e->nq_l * c.head_dim)) return B200LLM_EINVAL; e->layers[t.layer].wo = t.dev; break;
+            case B200LLM_W_MLP_NORM: if (!shape(1, c.d)) return B200LLM_EINVAL; e->layers[t.layer].mlp_norm = t.dev; break;
+            case B200LLM_W_GATE_UP: if (!shape(2 * (int64_t)e->ffn_l, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wgu = t.dev; break;
+            case B200LLM_W_DOWN: if (!shape(c.d, e->ffn_l)) return B200LLM_EINVAL; e->layers[t.layer].wdown = t.dev; break;
+            default: set_error("tensor %d: unknown kind %d", i, t.kind); return B200LLM_EINVAL;
+        }
+    }
+    bool all = e->embed && e->lm_head && e->final_norm && e->inv_freq;
+    for (auto &l : e->layers) all = all && l.attn_norm && l.wqkv && l.wo && l.mlp_norm && l.wgu && l.wdown;
+    e->weights_bound = all;
+    return B200LLM_OK;
+}
+
+int b200llm_bind_kv_pool(b200llm_engine *e, void *dev, size_t bytes) {
+    B200_REQUIRE(e && dev && ((uintptr_t)dev % 256) == 0, "bind_kv_pool: NULL or unaligned pool");
+    size_t pb;
+    b200llm_kv_page_bytes(&e->cfg, &pb);
+    e->n_pages = (int)(bytes / pb);
+    B200_REQUIRE(e->n_pages >= 1, "bind_kv_pool: pool smaller than one page (%zu < %zu)", bytes, pb);
+    e->kv = (uint8_t *)dev;
+    e->kv_half_stride = (size_t)e->n_pages * e->nkv_l * e->cfg.page_tokens * e->cfg.head_dim * 2;
+    return B200LLM_OK;
+}
+
+int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
+    B200_REQUIRE(e && dev && ((uintptr_t)dev % 256) == 0, "bind_workspace: NULL or unaligned workspace");
+    WsLayout w;
+    ws_layout(&e->cfg, &w);
+    if (bytes < w.total) {
+        set_error("bind_workspace: %zu bytes given, %zu needed", bytes, w.total);
+        return B200LLM_ENOMEM;
+    }
+    uint8_t *b = (uint8_t *)dev;
+    e->ws = b;
+    e->h = (float *)(b + w.h), e->q = (float *)(b + w.q), e->att = (float *)(b + w.att);
+    e->act = (float *)(b + w.act), e->delta = (float *)(b + w.delta), e->logits = (float *)(b + w.logits);
+    e->part_max = (float *)(b + w.part_max), e->part_idx = (int32_t *)(b + w.part_idx);
+    e->row_lane = (int32_t *)(b + w.row_lane), e->row_pos = (int32_t *)(b + w.row_pos);
+    e->row_token = (int32_t *)(b + w.row_token);
+    e->pf_lane = (int32_t *)(b + w.pf_lane), e->pf_pos = (int32_t *)(b + w.pf_pos);
+    e->pf_token = (int32_t *)(b + w.pf_token);
+    e->lane_token = (int32_t *)(b + w.lane_token), e->lane_pos = (int32_t *)(b + w.lane_pos);
+    e->lane_hist = (int32_t *)(b + w.lane_hist), e->page_table = (int32_t *)(b + w.page_table);
+    e->gen_out = (int32_t *)(b + w.gen_out), e->step_ctr = (int32_t *)(b + w.step_ctr);
+    e->lane_samp = (b200llm_sampling *)(b + w.lane_samp);
+    e->gath_max = (float *)(b + w.gath_max), e->gath_idx = (int32_t *)(b + w.gath_idx);
+    e->attn_scratch = b + w.attn_scratch;
+    e->attn_scratch_bytes = w.attn_scratch_bytes;
+    e->lm_grid = w.lm_grid;
+    e->attn_splits = w.attn_splits;
+    // zero everything once: attention tickets must start at zero, lanes at token 0 / pos 0,
+    // sampling = greedy, page tables -> page 0
+    B200_CUDA_OK(cudaMemsetAsync(b, 0, w.total, e->stream));
+    B200_CUDA_OK(cudaMemsetAsync(e->lane_hist, 0xFF, (size_t)e->cfg.max_lanes * 64 * 4, e->stream));
+    std::vector<b200llm_sampling> sp(e->cfg.max_lanes, b200llm_sampling{0.f, 0, 1.f, 1.f, 0});
+    B200_CUDA_OK(cudaMemcpyAsync(e->lane_samp, sp.data(), sp.size() * sizeof(b200llm_sampling),
+                                 cudaMemcpyHostToDevice, e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+    return B200LLM_OK;
+}
+
+static int require_ready(b200llm_engine *e) {
+    if (!e) {
+        set_error("engine is NULL");
+        return B200LLM_EINVAL;
+    }
+    if (!e->weights_bound || !e->kv || !e->ws) {
+        set_error("engine not ready: bind weights (%d), KV pool (%d) and workspace (%d) first", (int)e->weights_bound,
+                  e->kv != nullptr, e->ws != nullptr);
+        return B200LLM_ESTATE;
+    }
+    return B200LLM_OK;
+}
+
+int b200llm_set_page_table(b200llm_engine *e, int32_t lane, const int32_t *pages, int32_t n) {
+    B200_REQUIRE(e && e->ws && pages, "set_page_table: bad arguments");
+    B200_REQUIRE(lane >= 0 && lane < e->cfg.max_lanes && n >= 0 && n <= e->cfg.max_pages_per_lane,
+                 "set_page_table: lane %d / n %d out of range", lane, n);
+    for (int i = 0; i < n; ++i)
+        B200_REQUIRE(pages[i] >= 0 && pages[i] < e->n_pages, "set_page_table: page %d out of range [0, %d)", pages[i],
+                     e->n_pages);
+    B200_CUDA_OK(cudaMemcpyAsync(e->page_table + (size_t)lane * e->cfg.max_pages_per_lane, pages, (size_t)n * 4,
+                                 cudaMemcpyHostToDevice, e->stream));
+    return B200LLM_OK;
+}
+
+int b200llm_set_sampling(b200llm_engine *e, int32_t lane, const b200llm_sampling *s) {
+    B200_REQUIRE(e && e->ws && s && lane >= 0 && lane < e->cfg.max_lanes, "set_sampling: bad arguments");
+    B200_REQUIRE(s->temperature >= 0.f && s->repeat_penalty > 0.f, "set_sampling: bad temperature/repeat_penalty");
+    B200_CUDA_OK(cudaMemcpyAsync(e->lane_samp + lane, s, sizeof(*s), cudaMemcpyHostToDevice, e->stream));
+    return B200LLM_OK;
+}
+
+int b200llm_set_lane(b200llm_engine *e, int32_t lane, int32_t next_token, int32_t pos) {
+    B200_REQUIRE(e && e->ws && lane >= 0 && lane < e->cfg.max_lanes, "set_lane: bad arguments");
+    B200_REQUIRE(pos >= 0 && pos < e->max_ctx, "set_lane: pos %d out of range", pos);
+    B200_CUDA_OK(cudaMemcpyAsync(e->lane_token + lane, &next_token, 4, cudaMemcpyHostToDevice, e->stream));
+    B200_CUDA_OK(cudaMemcpyAsync(e->lane_pos + lane, &pos, 4, cudaMemcpyHostToDevice, e->stream));
+    if (pos == 0)
+        B200_CUDA_OK(cudaMemsetAsync(e->lane_hist + (size_t)lane * 64, 0xFF, 64 * 4, e->stream));
+    return B200LLM_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------- one forward pass
+#define B200_TRY(expr)        \
+    do {                      \
+        int _rc = (expr);     \
+        if (_rc) return _rc;  \
+    } while (0)
+
+struct PassRows {
+    int rows;
+    int32_t *row_lane, *row_pos, *row_token;
+    bool from_lanes;
+    int logit_row0;   // first row that needs logits
+    int logit_rows;   // 0 = skip lm_head + sampler
+};
+
+// GEMV over `rows` rows in groups of <= 4 (the batch > 4 tensor-core path replaces this loop)
+static int gemv_rows(b200llm_engine *e, b200llm_gemv_args a, int rows, const PassRows &pr, int row0) {
+    const float *x = a.x;
+    float *out = a.out;
+    for (int r = 0; r < rows; r += 4) {
+        a.bs = rows - r < 4 ? rows - r : 4;
+        a.x = x + (size_t)r * a.x_stride;
+        a.out = out + (size_t)r * a.out_stride;
+        a.row_lane = pr.row_lane + row0 + r;
+        a.row_pos = pr.row_pos + row0 + r;
+        if (a.epi == B200LLM_EPI_LOGITS) {
+            a.part_max = e->part_max + (size_t)r * e->lm_grid;
+            a.part_idx = e->part_idx + (size_t)r * e->lm_grid;
+        }
+        B200_TRY(gemv_launch(a, e->stream, e->pdl));
+        e->launches++;
+    }
+    return B200LLM_OK;
+}
+
+static int tp_allreduce_add(b200llm_engine *e, int rows) {
+    const size_t n = (size_t)rows * e->cfg.d;
+    B200_NCCL_OK(g_nccl.AllReduce(e->delta, e->delta, n, kNcclFloat32, kNcclSum, e->comm, e->stream));
+    B200_TRY(add_inplace_launch(e->h, e->delta, n, e->stream, false));
+    e->launches++;
+    return B200LLM_OK;
+}
+
+static int forward_pass(b200llm_engine *e, const PassRows &pr, bool advance) {
+    const b200llm_config &c = e->cfg;
+    const int rows = pr.rows;
+    const bool tp = c.tp_size > 1;
+    EmbedArgs ea{};
+    ea.embed = e->embed, ea.h = e->h, ea.row_token = pr.row_token, ea.row_pos = pr.row_pos, ea.row_lane = pr.row_lane;
+    ea.lane_token = e->lane_token, ea.lane_pos = e->lane_pos, ea.rows = rows, ea.d = c.d, ea.vocab = c.vocab;
+    ea.from_lanes = pr.from_lanes ? 1 : 0;
+    B200_TRY(embed_launch_ex(ea, e->lane_hist, pr.from_lanes ? e->step_ctr : nullptr, e->stream, e->pdl));
+    e->launches++;
+
+    const size_t qd = (size_t)e->nq_l * c.head_dim;
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW &w = e->layers[l];
+        uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
+        uint8_t *vl = kl + e->kv_half_stride;
+        b200llm_gemv_args g{};
+        // --- rmsnorm + qkv + rope + kv append ---
+        g.w = w.wqkv, g.x = e->h, g.x_stride = c.d, g.norm_gain = w.attn_norm, g.rms_eps = c.rms_eps;
+        g.out = e->q, g.out_stride = (int64_t)qd, g.N = (e->nq_l + 2 * e->nkv_l) * c.head_dim, g.K = c.d;
+        g.epi = B200LLM_EPI_QKV_ROPE, g.n_q = e->nq_l, g.n_kv = e->nkv_l, g.head_dim = c.head_dim;
+        g.page_tokens = c.page_tokens, g.max_pages_per_lane = c.max_pages_per_lane, g.inv_freq = e->inv_freq;
+        g.page_table = e->page_table, g.k_pages = kl, g.v_pages = vl;
+        B200_TRY(gemv_rows(e, g, rows, pr, 0));
+        // --- attention ---
+        b200llm_attn_args at{};
+        at.q = e->q, at.out = e->att, at.k_pages = kl, at.v_pages = vl, at.row_lane = pr.row_lane, at.row_pos = pr.row_pos;
+        at.page_table = e->page_table, at.bs = rows, at.n_q = e->nq_l, at.n_kv = e->nkv_l, at.head_dim = c.head_dim;
+        at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane;
+        // enough CTAs to fill the GPU, no more splits than that needs
+        int want = (2 * kNumSMs + rows * e->nkv_l - 1) / (rows * e->nkv_l);
+        at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
+        at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
+        B200_TRY(attn_decode_launch(at, e->stream, e->pdl));
+        e->launches++;
+        // --- o_proj ---
+        b200llm_gemv_args o{};
+        o.w = w.wo, o.x = e->att, o.x_stride = (int64_t)qd, o.N = c.d, o.K = (int)qd;
+        o.out = tp ? e->delta : e->h, o.out_stride = c.d, o.epi = tp ? B200LLM_EPI_STORE : B200LLM_EPI_RESIDUAL;
+        B200_TRY(gemv_rows(e, o, rows, pr, 0));
+        if (tp) B200_TRY(tp_allreduce_add(e, rows));
+        // --- rmsnorm + gate/up + swiglu ---
+        b200llm_gemv_args u{};
+        u.w = w.wgu, u.x = e->h, u.x_stride = c.d, u.norm_gain = w.mlp_norm, u.rms_eps = c.rms_eps;
+        u.out = e->act, u.out_stride = e->ffn_l, u.N = 2 * e->ffn_l, u.K = c.d, u.epi = B200LLM_EPI_SWIGLU;
+        B200_TRY(gemv_rows(e, u, rows, pr, 0));
+        // --- down ---
+        b200llm_gemv_args dn{};
+        dn.w = w.wdown, dn.x = e->act, dn.x_stride = e->ffn_l, dn.N = c.d, dn.K = e->ffn_l;
+        dn.out = tp ? e->delta : e->h, dn.out_stride = c.d, dn.epi = tp ? B200LLM_EPI_STORE : B200LLM_EPI_RESIDUAL;
+        B200_TRY(gemv_rows(e, dn, rows, pr, 0));
+        if (tp) B200_TRY(tp_allreduce_add(e, rows));
+    }
+    e->last_rows = rows;
+    e->last_logit_rows = pr.logit_rows;
+    if (pr.logit_rows <= 0) return B200LLM_OK;
+
+    // --- final norm + lm_head + sampler ---
+    b200llm_gemv_args lm{};
+    lm.w = e->lm_head, lm.x = e->h + (size_t)pr.logit_row0 * c.d, lm.x_stride = c.d, lm.norm_gain = e->final_norm;
+    lm.rms_eps = c.rms_eps, lm.out = e->logits, lm.out_stride = e->vocab_l, lm.N = e->vocab_l, lm.K = c.d;
+    lm.epi = B200LLM_EPI_LOGITS, lm.grid_hint = e->lm_grid, lm.logits_idx_offset = c.tp_rank * e->vocab_l;
+    B200_TRY(gemv_rows(e, lm, pr.logit_rows, pr, pr.logit_row0));
+
+    SampleDev sd{};
+    sd.a.logits = e->logits, sd.a.bs = pr.logit_rows, sd.a.vocab = e->vocab_l;
+    sd.a.part_max = e->part_max, sd.a.part_idx = e->part_idx, sd.a.n_part = e->lm_grid;
+    sd.a.params = e->lane_samp, sd.a.out_token = nullptr;
+    if (tp) {
+        // vocab-parallel greedy: gather every rank's per-row (max, argmax) and reduce those.
+        // TODO(tp sampling): temperature > 0 needs the full logits gathered; greedy only here.
+        B200_NCCL_OK(g_nccl.AllGather(e->part_max, e->gath_max, (size_t)pr.logit_rows * e->lm_grid * 4, kNcclInt8,
+                                      e->comm, e->stream));
+        B200_NCCL_OK(g_nccl.AllGather(e->part_idx, e->gath_idx, (size_t)pr.logit_rows * e->lm_grid * 4, kNcclInt8,
+                                      e->comm, e->stream));
+        // gathered layout is [rank][row][grid]
+        sd.a.part_max = e->gath_max, sd.a.part_idx = e->gath_idx;
+        sd.n_ranks = c.tp_size, sd.rank_stride = (size_t)pr.logit_rows * e->lm_grid;
+    }
+    sd.row_lane = pr.row_lane + pr.logit_row0;
+    sd.lane_token = e->lane_token, sd.lane_pos = e->lane_pos, sd.lane_hist = e->lane_hist;
+    sd.gen_out = pr.from_lanes ? e->gen_out : nullptr, sd.step_ctr = pr.from_lanes ? e->step_ctr : nullptr;
+    sd.advance = advance ? 1 : 0;
+    B200_TRY(sample_launch(sd, e->stream, e->pdl && !tp));
+    e->launches++;
+    return B200LLM_OK;
+}
+
+extern "C" {
+
+int b200llm_prefill(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t n, int32_t pos0) {
+    B200_TRY(require_ready(e));
+    const b200llm_config &c = e->cfg;
+    B200_REQUIRE(ids && n >= 1 && lane >= 0 && lane < c.max_lanes, "prefill: bad arguments");
+    B200_REQUIRE(pos0 >= 0 && pos0 + n <= e->max_ctx, "prefill: %d tokens at pos %d exceed the lane's %d-token context",
+                 n, pos0, e->max_ctx);
+    std::vector<int32_t> pos(n), lanes(n, lane);
+    for (int i = 0; i < n; ++i) pos[i] = pos0 + i;
+    B200_CUDA_OK(cudaEventRecord(e->ev[0], e->stream));
+    B200_CUDA_OK(cudaMemcpyAsync(e->pf_token, ids, (size_t)n * 4, cudaMemcpyHostToDevice, e->stream));
+    B200_CUDA_OK(cudaMemcpyAsync(e->pf_pos, pos.data(), (size_t)n * 4, cudaMemcpyHostToDevice, e->stream));
+    B200_CUDA_OK(cudaMemcpyAsync(e->pf_lane, lanes.data(), (size_t)n * 4, cudaMemcpyHostToDevice, e->stream));
+    const int last = pos0 + n - 1;
+    B200_CUDA_OK(cudaMemcpyAsync(e->lane_pos + lane, &last, 4, cudaMemcpyHostToDevice, e->stream));
+    if (pos0 == 0) B200_CUDA_OK(cudaMemsetAsync(e->lane_hist + (size_t)lane * 64, 0xFF, 64 * 4, e->stream));
+    // pageable sources above are staged by the runtime before the call returns
+    for (int c0 = 0; c0 < n; c0 += c.max_rows) {
+        PassRows pr{};
+        pr.rows = n - c0 < c.max_rows ? n - c0 : c.max_rows;
+        pr.row_lane = e->pf_lane + c0, pr.row_pos = e->pf_pos + c0, pr.row_token = e->pf_token + c0;
+        pr.from_lanes = false;
+        const bool is_last = c0 + pr.rows == n;
+        pr.logit_row0 = pr.rows - 1;
+        pr.logit_rows = is_last ? 1 : 0;
+        B200_TRY(forward_pass(e, pr, true));
+    }
+    B200_CUDA_OK(cudaEventRecord(e->ev[1], e->stream));
+    e->timing.prefill_tokens = n;
+    return B200LLM_OK;
+}
+
+int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int32_t n_steps) {
+    B200_TRY(require_ready(e));
+    const b200llm_config &c = e->cfg;
+    B200_REQUIRE(lanes && n_lanes >= 1 && n_lanes <= c.max_rows, "decode: n_lanes %d out of range [1, %d]", n_lanes,
+                 c.max_rows);
+    B200_REQUIRE(n_steps >= 1 && n_steps <= kMaxDecodeSteps, "decode: n_steps %d out of range [1, %d]", n_steps,
+                 kMaxDecodeSteps);
+    for (int i = 0; i < n_lanes; ++i)
+        B200_REQUIRE(lanes[i] >= 0 && lanes[i] < c.max_lanes, "decode: lane %d out of range", lanes[i]);
+    B200_CUDA_OK(cudaMemcpyAsync(e->row_lane, lanes, (size_t)n_lanes * 4, cudaMemcpyHostToDevice, e->stream));
+    B200_CUDA_OK(cudaMemsetAsync(e->step_ctr, 0, 4, e->stream));
+    PassRows pr{};
+    pr.rows = n_lanes, pr.row_lane = e->row_lane, pr.row_pos = e->row_pos, pr.row_token = e->row_token;
+    pr.from_lanes = true, pr.logit_row0 = 0, pr.logit_rows = n_lanes;
+
+    B200_CUDA_OK(cudaEventRecord(e->ev[2], e->stream));
+    if (c.use_graphs) {
+        auto it = e->graphs.find(n_lanes);
+        if (it == e->graphs.end()) {
+            cudaGraph_t graph = nullptr;
+            e->launches = 0;
+            B200_CUDA_OK(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+            int rc = forward_pass(e, pr, true);
+            cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
+            if (rc) {
+                if (graph) cudaGraphDestroy(graph);
+                return rc;
+            }
+            B200_CUDA_OK(ce);
+            cudaGraphExec_t exec = nullptr;
+            B200_CUDA_OK(cudaGraphInstantiate(&exec, graph, 0));
+            cudaGraphDestroy(graph);
+            it = e->graphs.emplace(n_lanes, exec).first;
+            e->graph_launches[n_lanes] = e->launches;
+        }
+        for (int s = 0; s < n_steps; ++s) B200_CUDA_OK(cudaGraphLaunch(it->second, e->stream));
+        e->timing.kernel_launches = e->graph_launches[n_lanes] * n_steps;
+    } else {
+        e->launches = 0;
+        for (int s = 0; s < n_steps; ++s) B200_TRY(forward_pass(e, pr, true));
+        e->timing.kernel_launches = e->launches;
+    }
+    B200_CUDA_OK(cudaEventRecord(e->ev[3], e->stream));
+    e->timing.decode_steps = n_steps;
+    return B200LLM_OK;
+}
+
+int b200llm_read_tokens(b200llm_engine *e, int32_t *out, int32_t n_steps, int32_t n_lanes) {
+    B200_TRY(require_ready(e));
+    B200_REQUIRE(out && n_steps >= 1 && n_steps <= kMaxDecodeSteps && n_lanes >= 1 && n_lanes <= e->cfg.max_rows,
+                 "read_tokens: bad arguments");
+    B200_CUDA_OK(cudaMemcpyAsync(out, e->gen_out, (size_t)n_steps * n_lanes * 4, cudaMemcpyDeviceToHost, e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+    return B200LLM_OK;
+}
+
+int b200llm_read_lane(b200llm_engine *e, int32_t lane, int32_t *next_token, int32_t *pos) {
+    B200_TRY(require_ready(e));
+    B200_REQUIRE(lane >= 0 && lane < e->cfg.max_lanes, "read_lane: lane out of range");
+    int32_t t = 0, p = 0;
+    B200_CUDA_OK(cudaMemcpyAsync(&t, e->lane_token + lane, 4, cudaMemcpyDeviceToHost, e->stream));
+    B200_CUDA_OK(cudaMemcpyAsync(&p, e->lane_pos + lane, 4, cudaMemcpyDeviceToHost, e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+    if (next_token) *next_token = t;
+    if (pos) *pos = p;
+    return B200LLM_OK;
+}
+
+int b200llm_step_logits(b200llm_engine *e, int32_t row, float *out, int32_t n) {
+    B200_TRY(require_ready(e));
+    B200_REQUIRE(out && row >= 0 && row < e->last_logit_rows && n >= 1 && n <= e->vocab_l,
+                 "step_logits: row %d / n %d out of range (last pass had %d logit rows, %d vocab rows)", row, n,
+                 e->last_logit_rows, e->vocab_l);
+    B200_CUDA_OK(cudaMemcpyAsync(out, e->logits + (size_t)row * e->vocab_l, (size_t)n * 4, cudaMemcpyDeviceToHost,
+                                 e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+    return B200LLM_OK;
+}
+
+int b200llm_sync(b200llm_engine *e) {
+    B200_REQUIRE(e, "engine is NULL");
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+    return B200LLM_OK;
+}
+
+int b200llm_last_timing(b200llm_engine *e, b200llm_timing *t) {
+    B200_REQUIRE(e && t, "last_timing: bad arguments");
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+    if (e->timing.prefill_tokens > 0) cudaEventElapsedTime(&e->timing.prefill_ms, e->ev[0], e->ev[1]);
+    if (e->timing.decode_steps > 0) cudaEventElapsedTime(&e->timing.decode_ms, e->ev[2], e->ev[3]);
+    cudaGetLastError();
+    *t = e->timing;
+    return B200LLM_OK;
+}
+
+void *b200llm_stream(b200llm_engine *e) { return e ? (void *)e->stream : nullptr; }
+
+// ---------------------------------------------------------------- single-kernel entry points
+int b200llm_op_gemv(const b200llm_gemv_args *a, void *stream) {
+    B200_REQUIRE(a && a->w && a->x && a->out, "op_gemv: NULL argument");
+    int rc = require_device_any();
+    if (rc) return rc;
+    return gemv_launch(*a, (cudaStream_t)stream, false);
+}
+
+int b200llm_op_gemv_grid(int32_t N, int32_t K, int32_t bs, int32_t epi, int32_t *grid) {
+    B200_REQUIRE(grid, "op_gemv_grid: NULL argument");
+    int g = gemv_grid(N, K, bs, epi, 0);
+    B200_REQUIRE(g > 0, "op_gemv_grid: unsupported shape");
+    *grid = g;
+    return B200LLM_OK;
+}
+
+int b200llm_op_attn_decode(const b200llm_attn_args *a, void *stream) {
+    B200_REQUIRE(a && a->q && a->out && a->k_pages && a->v_pages && a->row_lane && a->row_pos && a->page_table,
+                 "op_attn_decode: NULL argument");
+    int rc = require_device_any();
+    if (rc) return rc;
+    return attn_decode_launch(*a, (cudaStream_t)stream, false);
+}
+
+int b200llm_op_attn_scratch_bytes(int32_t bs, int32_t n_q, int32_t n_kv, int32_t head_dim, int32_t n_splits,
+                                  size_t *bytes) {
+    B200_REQUIRE(bytes && bs >= 1 && n_q >= 1 && n_kv >= 1 && n_splits >= 1, "op_attn_scratch_bytes: bad arguments");
+    *bytes = attn_scratch_bytes(bs, n_q, n_kv, head_dim, n_splits);
+    return B200LLM_OK;
+}
+
+int b200llm_op_sample(const b200llm_sample_args *a, void *stream) {
+    B200_REQUIRE(a && a->logits && a->out_token, "op_sample: NULL argument");
+    int rc = require_device_any();
+    if (rc) return rc;
+    SampleDev d{};
+    d.a = *a;
+    return sample_launch(d, (cudaStream_t)stream, false);
+}
+
+int b200llm_op_fill_weights(void *dev_bf16, uint64_t n, uint64_t seed, float sigma, float mean, void *stream) {
+    B200_REQUIRE(dev_bf16 != nullptr || n == 0, "op_fill_weights: NULL argument");
+    int rc = require_device_any();
+    if (rc) return rc;
+    return fill_weights_launch(dev_bf16, n, seed, sigma, mean, (cudaStream_t)stream);
+}
+
+}  // extern "C"

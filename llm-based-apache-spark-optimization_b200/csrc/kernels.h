@@ -1,0 +1,54 @@
+// kernels.h -- internal launch functions of libb200llm (host side, C++).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200llm.h"
+
+namespace b200 {
+
+// gemv.cu
+int gemv_launch(const b200llm_gemv_args &a, cudaStream_t stream, bool pdl);
+int gemv_grid(int N, int K, int bs, int epi, int grid_hint);
+
+// attn.cu
+int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl);
+size_t attn_scratch_bytes(int bs, int n_q, int n_kv, int head_dim, int n_splits);
+
+// misc.cu
+struct EmbedArgs {
+    const void *embed;        // bf16 [vocab, d]
+    float *h;                 // fp32 [rows, d]
+    int32_t *row_token;       // [rows] (decode: filled from lane state)
+    int32_t *row_pos;         // [rows]
+    const int32_t *row_lane;  // [rows]
+    const int32_t *lane_token;  // [lanes]
+    const int32_t *lane_pos;    // [lanes]
+    int rows, d, vocab;
+    int from_lanes;           // 1: decode (gather token/pos from lane state); 0: prefill (row_* already set)
+};
+int embed_launch(const EmbedArgs &a, cudaStream_t stream, bool pdl);
+// engine variant: also records the token in the lane's 64-entry history ring and bumps the step counter
+int embed_launch_ex(const EmbedArgs &a, int32_t *lane_hist, int32_t *step_ctr, cudaStream_t stream, bool pdl);
+
+struct SampleDev {
+    b200llm_sample_args a;
+    // engine-side feedback (all may be NULL for the bare op)
+    const int32_t *row_lane;  // [bs]
+    int32_t *lane_token;      // [lanes]  <- sampled token
+    int32_t *lane_pos;        // [lanes]  += 1
+    int32_t *lane_hist;       // [lanes, 64] ring of recent tokens
+    int32_t *gen_out;         // [steps, bs] ring of generated tokens (row-major by step)
+    const int32_t *step_ctr;  // device step counter (index into gen_out), or NULL
+    int32_t *step_ctr_w;      // incremented by row 0's CTA
+    const uint64_t *rng_ctr;  // device RNG counter or NULL (then a.step is used)
+    int advance;              // 1: write feedback
+    int n_ranks;              // > 1: partials are [rank][row][n_part] (vocab-parallel all-gather)
+    size_t rank_stride;
+};
+int sample_launch(const SampleDev &a, cudaStream_t stream, bool pdl);
+
+int fill_weights_launch(void *dev_bf16, uint64_t n, uint64_t seed, float sigma, float mean, cudaStream_t s);
+int add_inplace_launch(float *dst, const float *src, size_t n, cudaStream_t s, bool pdl);
+
+}  // namespace b200

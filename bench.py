@@ -200,10 +200,15 @@ def run_b200(args):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    profiling = os.environ.get("B200LLM_PROFILE") == "1"      # ncu --profile-from-start off
+    if profiling:
+        torch.cuda.profiler.start()
     ev0.record(eng.stream)
     eng.decode(lanes, args.steps, read=False)
     ev1.record(eng.stream)
     torch.cuda.synchronize()
+    if profiling:
+        torch.cuda.profiler.stop()
     if world > 1:
         dist.barrier()
     ms = ev0.elapsed_time(ev1)

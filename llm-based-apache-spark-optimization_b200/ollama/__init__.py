@@ -20,6 +20,8 @@ import os
 import time
 from typing import Any, Dict, Optional, Sequence
 
+_list = list          # the module exports its own `list()` (upstream name) below
+
 __all__ = ["generate", "ResponseError", "GenerateResponse", "Client", "list"]
 
 # Ollama's documented defaults: the reference passes no `options`, so these apply.
@@ -93,7 +95,7 @@ def generate(model: str = "", prompt: str = "", suffix: str = "", system: str = 
     opt = dict(DEFAULT_OPTIONS)
     opt.update(options or {})
     text = render_prompt(system or "", prompt or "", template or "", raw)
-    ids = list(context or []) + m.tokenizer.encode(text, bos=not context)
+    ids = _list(context or []) + m.tokenizer.encode(text, bos=not context)
     max_ctx = m.engine.max_pages_per_lane * 16
     num_predict = int(opt["num_predict"])
     if num_predict < 0:
@@ -115,7 +117,7 @@ def generate(model: str = "", prompt: str = "", suffix: str = "", system: str = 
             response, stopped = response[:cut], True
     res = GenerateResponse(
         model=model, created_at=datetime.datetime.now(datetime.timezone.utc).isoformat(), response=response,
-        done=True, done_reason="stop" if stopped else "length", context=list(ids) + list(out_toks),
+        done=True, done_reason="stop" if stopped else "length", context=_list(ids) + _list(out_toks),
         total_duration=time.perf_counter_ns() - t_start, load_duration=m.load_ns, prompt_eval_count=len(ids),
         prompt_eval_duration=int(tm.prefill_ms * 1e6), eval_count=len(toks), eval_duration=int(tm.decode_ms * 1e6))
     if stream:

@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--no-pdl", action="store_true")
+    ap.add_argument("--attn-splits", type=int, default=0)
     return ap.parse_args()
 
 
@@ -169,7 +170,7 @@ def run_b200(args):
     w = weights.random_init(geo, 0xB200, local)
     max_ctx = PROMPT_LEN + args.steps + args.warmup + E2E_NEW_TOKENS + 64
     eng = Engine(geo, w, device=local, max_lanes=bs + 1, max_ctx=max_ctx, max_rows=max(bs, 64),
-                 use_graphs=not args.no_graphs, use_pdl=not args.no_pdl)
+                 use_graphs=not args.no_graphs, use_pdl=not args.no_pdl, attn_splits=args.attn_splits)
     # synthetic prompts: uniform ids, one stream per (rank, sequence)
     rng = np.random.default_rng(1000 * rank + 1)
     prompts = [rng.integers(0, min(geo.vocab, 128000), PROMPT_LEN, dtype=np.int32) for _ in range(bs)]

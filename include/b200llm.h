@@ -69,6 +69,7 @@ typedef struct b200llm_config {
     int32_t use_graphs;         /* capture the decode step into a CUDA graph */
     int32_t use_pdl;            /* programmatic dependent launch between kernels */
     int32_t attn_splits;        /* split-T factor of decode attention, 0 = auto */
+    int32_t use_megakernel;     /* batch-1 greedy decode as one persistent kernel */
     void *stream;               /* cudaStream_t to run on; NULL = engine creates its own */
     const void *nccl_unique_id; /* 128-byte ncclUniqueId when tp_size > 1, else NULL */
 } b200llm_config;

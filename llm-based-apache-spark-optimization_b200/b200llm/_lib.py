@@ -24,7 +24,7 @@ class Config(C.Structure):
                 ("rms_eps", C.c_float), ("page_tokens", C.c_int32), ("max_lanes", C.c_int32),
                 ("max_pages_per_lane", C.c_int32), ("max_rows", C.c_int32), ("tp_rank", C.c_int32),
                 ("tp_size", C.c_int32), ("device", C.c_int32), ("use_graphs", C.c_int32), ("use_pdl", C.c_int32),
-                ("attn_splits", C.c_int32), ("stream", C.c_void_p), ("nccl_unique_id", C.c_void_p)]
+                ("attn_splits", C.c_int32), ("use_megakernel", C.c_int32), ("stream", C.c_void_p), ("nccl_unique_id", C.c_void_p)]
 
 
 class TensorDesc(C.Structure):

@@ -11,6 +11,7 @@
 //   partials) -> sampler (feeds the token and position back on the device).
 #include <dlfcn.h>
 #include <stdarg.h>
+#include <math.h>
 #include <string.h>
 
 #include <map>
@@ -19,6 +20,7 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "mega.h"
 
 namespace b200 {
 
@@ -115,6 +117,11 @@ struct b200llm_engine {
         *lane_hist, *page_table, *gen_out, *step_ctr;
     float *gath_max;
     int32_t *gath_idx;
+    // persistent batch-1 decode kernel
+    MegaJob *mega_jobs = nullptr;
+    unsigned *bar_ctr = nullptr;
+    bool mega_ready = false;
+    std::vector<b200llm_sampling> samp_host;
     b200llm_sampling *lane_samp;
     void *attn_scratch;
     size_t attn_scratch_bytes;
@@ -154,7 +161,7 @@ static int check_cfg(const b200llm_config *c) {
 struct WsLayout {
     size_t h, q, att, act, delta, logits, part_max, part_idx, row_lane, row_pos, row_token, pf_lane, pf_pos,
         pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
-        attn_scratch, total;
+        attn_scratch, mega_jobs, bar_ctr, total;
     size_t attn_scratch_bytes;
     int lm_grid, attn_splits;
 };
@@ -209,6 +216,8 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->gath_max = take(R * tp * w->lm_grid * 4);
     w->gath_idx = take(R * tp * w->lm_grid * 4);
     w->attn_scratch = take(w->attn_scratch_bytes);
+    w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * sizeof(MegaJob));
+    w->bar_ctr = take(256);
     w->total = o;
 }
 
@@ -416,6 +425,10 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->attn_scratch_bytes = w.attn_scratch_bytes;
     e->lm_grid = w.lm_grid;
     e->attn_splits = w.attn_splits;
+    e->mega_jobs = (MegaJob *)(b + w.mega_jobs);
+    e->bar_ctr = (unsigned *)(b + w.bar_ctr);
+    e->mega_ready = false;
+    e->samp_host.assign(e->cfg.max_lanes, b200llm_sampling{0.f, 0, 1.f, 1.f, 0});
     // zero everything once: attention tickets must start at zero, lanes at token 0 / pos 0,
     // sampling = greedy, page tables -> page 0
     B200_CUDA_OK(cudaMemsetAsync(b, 0, w.total, e->stream));
@@ -456,6 +469,7 @@ int b200llm_set_sampling(b200llm_engine *e, int32_t lane, const b200llm_sampling
     B200_REQUIRE(e && e->ws && s && lane >= 0 && lane < e->cfg.max_lanes, "set_sampling: bad arguments");
     B200_REQUIRE(s->temperature >= 0.f && s->repeat_penalty > 0.f, "set_sampling: bad temperature/repeat_penalty");
     B200_CUDA_OK(cudaMemcpyAsync(e->lane_samp + lane, s, sizeof(*s), cudaMemcpyHostToDevice, e->stream));
+    e->samp_host[lane] = *s;
     return B200LLM_OK;
 }
 
@@ -544,7 +558,8 @@ static int forward_pass(b200llm_engine *e, const PassRows &pr, bool advance) {
         at.page_table = e->page_table, at.bs = rows, at.n_q = e->nq_l, at.n_kv = e->nkv_l, at.head_dim = c.head_dim;
         at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane;
         // enough CTAs to fill the GPU, no more splits than that needs
-        int want = (2 * kNumSMs + rows * e->nkv_l - 1) / (rows * e->nkv_l);
+        int want = (kNumSMs + rows * e->nkv_l - 1) / (rows * e->nkv_l);
+        if (want > 6) want = 6;  // the last-CTA merge is serial in the number of splits (profiles/launches_r1a)
         at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
         at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
         B200_TRY(attn_decode_launch(at, e->stream, e->pdl));
@@ -602,6 +617,57 @@ static int forward_pass(b200llm_engine *e, const PassRows &pr, bool advance) {
     return B200LLM_OK;
 }
 
+// ---------------------------------------------------------------- persistent batch-1 decode
+static int mega_prepare(b200llm_engine *e) {
+    const b200llm_config &c = e->cfg;
+    std::vector<MegaJob> jobs(4 * c.n_layers + 1);
+    const int qd = c.n_q * c.head_dim;
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW &w = e->layers[l];
+        uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
+        jobs[4 * l + 0] = MegaJob{w.wqkv, w.attn_norm, kl, kl + e->kv_half_stride, (c.n_q + 2 * c.n_kv) * c.head_dim,
+                                  c.d, B200LLM_EPI_QKV_ROPE, l == 0 ? MEGA_X_EMBED : MEGA_X_H};
+        jobs[4 * l + 1] = MegaJob{w.wo, nullptr, nullptr, nullptr, c.d, qd, B200LLM_EPI_RESIDUAL, MEGA_X_ATT};
+        jobs[4 * l + 2] = MegaJob{w.wgu, w.mlp_norm, nullptr, nullptr, 2 * c.ffn, c.d, B200LLM_EPI_SWIGLU, MEGA_X_H};
+        jobs[4 * l + 3] = MegaJob{w.wdown, nullptr, nullptr, nullptr, c.d, c.ffn, B200LLM_EPI_RESIDUAL, MEGA_X_ACT};
+    }
+    jobs[4 * c.n_layers] = MegaJob{e->lm_head, e->final_norm, nullptr, nullptr, c.vocab, c.d, B200LLM_EPI_LOGITS,
+                                   MEGA_X_H};
+    B200_CUDA_OK(cudaMemcpyAsync(e->mega_jobs, jobs.data(), jobs.size() * sizeof(MegaJob), cudaMemcpyHostToDevice,
+                                 e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));  // `jobs` is a pageable temporary
+    e->mega_ready = true;
+    return B200LLM_OK;
+}
+
+static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
+    const b200llm_config &c = e->cfg;
+    if (!e->mega_ready) B200_TRY(mega_prepare(e));
+    MegaParams p{};
+    p.jobs = e->mega_jobs, p.n_layers = c.n_layers;
+    p.d = c.d, p.n_q = c.n_q, p.n_kv = c.n_kv, p.head_dim = c.head_dim, p.ffn = c.ffn, p.vocab = c.vocab;
+    p.rms_eps = c.rms_eps;
+    p.scale_log2 = (float)(1.4426950408889634 / sqrt((double)c.head_dim));
+    p.h = e->h, p.q = e->q, p.att = e->att, p.act = e->act, p.logits = e->logits;
+    p.part_max = e->part_max, p.part_idx = e->part_idx;
+    p.embed = e->embed, p.inv_freq = e->inv_freq;
+    p.lane = lane, p.lane_token = e->lane_token, p.lane_pos = e->lane_pos, p.lane_hist = e->lane_hist;
+    p.page_table = e->page_table + (size_t)lane * c.max_pages_per_lane;
+    p.gen_out = e->gen_out, p.n_steps = n_steps;
+    int ns = kNumSMs / c.n_kv;
+    ns = ns < 1 ? 1 : (ns > e->attn_splits ? e->attn_splits : ns);
+    p.n_splits = ns;
+    uint8_t *sc = reinterpret_cast<uint8_t *>(e->attn_scratch);
+    const size_t tk = ((size_t)c.max_rows * c.n_kv * 4 + 255) / 256 * 256;
+    p.tickets = reinterpret_cast<unsigned *>(sc);
+    p.part_o = reinterpret_cast<float *>(sc + tk);
+    p.part_ml = p.part_o + (size_t)c.n_q * ns * c.head_dim;
+    p.bar_ctr = e->bar_ctr;
+    p.sample = 1;
+    e->last_rows = 1, e->last_logit_rows = 1;
+    return mega_decode_launch(p, e->stream);
+}
+
 extern "C" {
 
 int b200llm_prefill(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t n, int32_t pos0) {
@@ -651,7 +717,13 @@ int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int
     pr.from_lanes = true, pr.logit_row0 = 0, pr.logit_rows = n_lanes;
 
     B200_CUDA_OK(cudaEventRecord(e->ev[2], e->stream));
-    if (c.use_graphs) {
+    const b200llm_sampling &sp0 = e->samp_host[lanes[0]];
+    const bool greedy = sp0.temperature <= 0.f && sp0.repeat_penalty == 1.f;
+    if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy &&
+        mega_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim)) {
+        B200_TRY(mega_decode(e, lanes[0], n_steps));
+        e->timing.kernel_launches = 1;
+    } else if (c.use_graphs) {
         auto it = e->graphs.find(n_lanes);
         if (it == e->graphs.end()) {
             cudaGraph_t graph = nullptr;

@@ -37,9 +37,10 @@ def _rel(a, b):
     return float(np.abs(a - b).max() / (np.abs(b).max() + 1e-9))
 
 
-@pytest.mark.parametrize("name,use_graphs,use_pdl", [("tiny", False, False), ("tiny", True, True), ("small", True, True),
-                                                      ("small", True, False)])
-def test_live_oracle_parity(name, use_graphs, use_pdl, golden_dir):
+@pytest.mark.parametrize("name,use_graphs,use_pdl,mega", [("tiny", False, False, False), ("tiny", True, True, False),
+                                                           ("small", True, True, False), ("small", True, False, False),
+                                                           ("tiny", True, False, True), ("small", True, False, True)])
+def test_live_oracle_parity(name, use_graphs, use_pdl, mega, golden_dir):
     """Engine vs the oracle run live on this box's CPU, weights uploaded from the oracle's stream."""
     g = np.load(os.path.join(golden_dir, name + ".npz"))
     geo = lo.GEOMETRIES[name]
@@ -48,7 +49,8 @@ def test_live_oracle_parity(name, use_graphs, use_pdl, golden_dir):
     prompt = g["prompt"]
     toks, lg, mar = orc.greedy(prompt, 64)
     assert toks == g["tokens"].tolist()
-    eng = _engine(name, sd, max_lanes=2, max_ctx=256, max_rows=16, use_graphs=use_graphs, use_pdl=use_pdl)
+    eng = _engine(name, sd, max_lanes=2, max_ctx=256, max_rows=16, use_graphs=use_graphs, use_pdl=use_pdl,
+                  use_megakernel=mega)
     lane = eng.open_lane()
     eng.prefill(lane, prompt)
     first, pos = eng.read_lane(lane)

@@ -157,6 +157,9 @@ int b200llm_sync(b200llm_engine *e);
 int b200llm_last_timing(b200llm_engine *e, b200llm_timing *t);
 /* The cudaStream_t the engine launches on (for CUDA-event timing by the caller). */
 void *b200llm_stream(b200llm_engine *e);
+/* Debug: phase timestamps (ns, %globaltimer) the persistent decode kernel records when the
+ * environment variable B200LLM_MEGA_TRACE is set: [2][1024] for the first and last CTA. */
+int b200llm_debug_read_trace(b200llm_engine *e, uint64_t *out, int32_t n);
 
 /* ---- single kernels (unit-test and profiling entry points; same kernels the engine runs) */
 

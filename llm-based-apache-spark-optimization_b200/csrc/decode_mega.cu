@@ -127,9 +127,19 @@ __device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int
     }
 }
 
+struct StepCtx;
+__device__ __forceinline__ void mega_trace(const MegaParams &p, int &ti, int bid, int tid) {
+    if (ti >= 0 && tid == 0 && ti < 1024) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.trace[(bid ? 1024 : 0) + ti++] = t;
+    }
+}
+
 // ---------------------------------------------------------------- consumer: one GEMV phase
 struct StepCtx {
     int tok, pos;
+    int ti;               // trace cursor (-1: tracing off for this step)
     uint32_t gs;          // ring stage counter, in lock-step with the producer
     float best;           // LOGITS: running (max, argmax) of this thread
     int best_i;
@@ -204,6 +214,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
     const int gran = job_gran(job.epi);
     const RowRange rr = cta_rows(job.N, gran, G, bid);
     const int epi = job.epi;
+    mega_trace(p, c.ti, bid, tid);  // x loaded (+ normalised)
 
     for (int blk0 = 0; blk0 < rr.nrows; blk0 += kRB) {
         const int blk_rows = min(kRB, rr.nrows - blk0);
@@ -243,6 +254,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
             }
         }
         bar_sync(1, kMC);
+        mega_trace(p, c.ti, bid, tid);  // ring consumed
         // ---- combine the 16 warp partials of every row of the block + fused epilogue ----
         const int blk_units = blk_rows / gran;
         for (int u = tid; u < blk_units; u += kMC) {

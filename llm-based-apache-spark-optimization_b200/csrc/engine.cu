@@ -120,6 +120,7 @@ struct b200llm_engine {
     // persistent batch-1 decode kernel
     MegaJob *mega_jobs = nullptr;
     unsigned *bar_ctr = nullptr;
+    unsigned long long *trace = nullptr;
     bool mega_ready = false;
     std::vector<b200llm_sampling> samp_host;
     b200llm_sampling *lane_samp;
@@ -161,7 +162,7 @@ static int check_cfg(const b200llm_config *c) {
 struct WsLayout {
     size_t h, q, att, act, delta, logits, part_max, part_idx, row_lane, row_pos, row_token, pf_lane, pf_pos,
         pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
-        attn_scratch, mega_jobs, bar_ctr, total;
+        attn_scratch, mega_jobs, bar_ctr, trace, total;
     size_t attn_scratch_bytes;
     int lm_grid, attn_splits;
 };
@@ -218,6 +219,7 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->attn_scratch = take(w->attn_scratch_bytes);
     w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * sizeof(MegaJob));
     w->bar_ctr = take(256);
+    w->trace = take(2048 * 8);
     w->total = o;
 }
 
@@ -427,6 +429,7 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->attn_splits = w.attn_splits;
     e->mega_jobs = (MegaJob *)(b + w.mega_jobs);
     e->bar_ctr = (unsigned *)(b + w.bar_ctr);
+    e->trace = (unsigned long long *)(b + w.trace);
     e->mega_ready = false;
     e->samp_host.assign(e->cfg.max_lanes, b200llm_sampling{0.f, 0, 1.f, 1.f, 0});
     // zero everything once: attention tickets must start at zero, lanes at token 0 / pos 0,
@@ -664,6 +667,7 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     p.part_ml = p.part_o + (size_t)c.n_q * ns * c.head_dim;
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
+    if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     e->last_rows = 1, e->last_logit_rows = 1;
     return mega_decode_launch(p, e->stream);
 }
@@ -803,6 +807,13 @@ int b200llm_last_timing(b200llm_engine *e, b200llm_timing *t) {
 }
 
 void *b200llm_stream(b200llm_engine *e) { return e ? (void *)e->stream : nullptr; }
+
+int b200llm_debug_read_trace(b200llm_engine *e, uint64_t *out, int32_t n) {
+    B200_REQUIRE(e && e->ws && out && n >= 1 && n <= 2048, "debug_read_trace: bad arguments");
+    B200_CUDA_OK(cudaMemcpyAsync(out, e->trace, (size_t)n * 8, cudaMemcpyDeviceToHost, e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+    return B200LLM_OK;
+}
 
 // ---------------------------------------------------------------- single-kernel entry points
 int b200llm_op_gemv(const b200llm_gemv_args *a, void *stream) {

@@ -43,6 +43,8 @@ struct MegaParams {
     // grid barrier counter (zeroed before every launch)
     unsigned *bar_ctr;
     int32_t sample;       // 1: greedy argmax + feedback inside the kernel; 0: stop after logits
+    unsigned long long *trace;  // optional [2][1024] globaltimer stamps of CTA 0 and CTA G-1 (debug)
+    int32_t trace_step;
 };
 
 int mega_decode_launch(const MegaParams &p, cudaStream_t stream);

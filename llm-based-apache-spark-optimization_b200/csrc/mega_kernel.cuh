@@ -33,20 +33,32 @@ __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_c
     const int n_jobs = 4 * p.n_layers + 1;
 
     for (int step = 0; step < p.n_steps; ++step) {
+        c.ti = (p.trace != nullptr && step == p.trace_step && (bid == 0 || bid == G - 1)) ? 0 : -1;
+        mega_trace(p, c.ti, bid, tid);
         c.tok = min(max(c.tok, 0), p.vocab - 1);
         if (bid == 0 && tid == 0) p.lane_hist[(size_t)p.lane * 64 + (c.pos & 63)] = c.tok;
         for (int l = 0; l < p.n_layers; ++l) {
             const MegaJob *jb = p.jobs + 4 * l;
             mega_gemv_phase(p, jb[0], s, c, G, bid, tid);  // rmsnorm + qkv + rope + kv append
+            mega_trace(p, c.ti, bid, tid);
             grid_sync(p.bar_ctr, ++bar_no * G, tid);
+            mega_trace(p, c.ti, bid, tid);
             mega_attn_phase<HD, GQ>(p, jb[0], s, c, att_use, G, bid, tid);
+            mega_trace(p, c.ti, bid, tid);
             grid_sync(p.bar_ctr, ++bar_no * G, tid);
+            mega_trace(p, c.ti, bid, tid);
             mega_gemv_phase(p, jb[1], s, c, G, bid, tid);  // o_proj + residual
+            mega_trace(p, c.ti, bid, tid);
             grid_sync(p.bar_ctr, ++bar_no * G, tid);
+            mega_trace(p, c.ti, bid, tid);
             mega_gemv_phase(p, jb[2], s, c, G, bid, tid);  // rmsnorm + gate/up + swiglu
+            mega_trace(p, c.ti, bid, tid);
             grid_sync(p.bar_ctr, ++bar_no * G, tid);
+            mega_trace(p, c.ti, bid, tid);
             mega_gemv_phase(p, jb[3], s, c, G, bid, tid);  // down + residual
+            mega_trace(p, c.ti, bid, tid);
             grid_sync(p.bar_ctr, ++bar_no * G, tid);
+            mega_trace(p, c.ti, bid, tid);
         }
         // ---- final norm + lm_head: logits, per-CTA (max, lowest argmax) ----
         c.best = -INFINITY, c.best_i = 0x7fffffff;

@@ -261,8 +261,7 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
 size_t attn_scratch_bytes(int bs, int n_q, int n_kv, int head_dim, int n_splits) {
     size_t po = (size_t)bs * n_q * n_splits * head_dim * 4;
     size_t pml = (size_t)bs * n_q * n_splits * 2 * 4;
-    size_t tk = ((size_t)bs * n_kv * 4 + 255) / 256 * 256;
-    return tk + po + pml;
+    return kAttnTicketBytes + po + pml;
 }
 
 template <int HD, int G>
@@ -293,9 +292,9 @@ int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl
     d.a = a;
     d.scale_log2 = (float)(1.4426950408889634 / sqrt((double)a.head_dim));
     uint8_t *s = reinterpret_cast<uint8_t *>(a.scratch);
-    const size_t tk = ((size_t)a.bs * a.n_kv * 4 + 255) / 256 * 256;
+    B200_REQUIRE((size_t)a.bs * a.n_kv * 4 <= kAttnTicketBytes, "attn: bs * n_kv exceeds %zu tickets", kAttnTicketBytes / 4);
     d.tickets = reinterpret_cast<unsigned *>(s);
-    d.part_o = reinterpret_cast<float *>(s + tk);
+    d.part_o = reinterpret_cast<float *>(s + kAttnTicketBytes);
     d.part_ml = d.part_o + (size_t)a.bs * a.n_q * a.n_splits * a.head_dim;
     const int G = a.n_q / a.n_kv;
 #define B200_ATTN_CASE(HD_, G_) \

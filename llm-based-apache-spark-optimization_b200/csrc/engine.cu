@@ -661,9 +661,8 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     ns = ns < 1 ? 1 : (ns > e->attn_splits ? e->attn_splits : ns);
     p.n_splits = ns;
     uint8_t *sc = reinterpret_cast<uint8_t *>(e->attn_scratch);
-    const size_t tk = ((size_t)c.max_rows * c.n_kv * 4 + 255) / 256 * 256;
     p.tickets = reinterpret_cast<unsigned *>(sc);
-    p.part_o = reinterpret_cast<float *>(sc + tk);
+    p.part_o = reinterpret_cast<float *>(sc + kAttnTicketBytes);
     p.part_ml = p.part_o + (size_t)c.n_q * ns * c.head_dim;
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;

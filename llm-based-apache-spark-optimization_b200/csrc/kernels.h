@@ -14,6 +14,10 @@ int gemv_grid(int N, int K, int bs, int epi, int grid_hint);
 // attn.cu
 int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl);
 size_t attn_scratch_bytes(int bs, int n_q, int n_kv, int head_dim, int n_splits);
+// The arrival tickets live in a fixed-size region at the start of the scratch buffer, so that
+// launches with different batch sizes sharing one buffer never put partials where another
+// launch keeps tickets (tickets must stay zero between launches).
+constexpr size_t kAttnTicketBytes = 256 * 1024;  // 65536 (row, kv head) tickets
 
 // misc.cu
 struct EmbedArgs {

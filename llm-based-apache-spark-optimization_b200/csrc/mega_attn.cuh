@@ -13,7 +13,9 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
     const int warp = tid >> 5, lane = tid & 31;
     const int tg = lane >> 3, p8 = lane & 7;
     const int n_pages = c.pos / kMPT + 1;
-    const int ns = min(p.n_splits, n_pages);
+    // one page per attention warp and item until the split cap is reached: fewer, fatter items
+    // keep the cross-split merge short
+    const int ns = min(p.n_splits, (n_pages + kAttW - 1) / kAttW);
     const int pps = (n_pages + ns - 1) / ns;
     const int n_items = p.n_kv * ns;
     const uint8_t *kbase = reinterpret_cast<const uint8_t *>(qkv_job.k_pages);
@@ -36,7 +38,7 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
                 }
                 m[g] = -INFINITY, l[g] = 0.f;
             }
-            uint8_t *ks = s.att_tiles + (size_t)warp * 2 * TILE;
+            uint8_t *ks = s.xtab + (size_t)warp * 2 * TILE;
             uint8_t *vs = ks + TILE;
             for (int pg = pg_begin + warp; pg < pg_end; pg += kAttW) {
                 if (lane == 0) {
@@ -167,17 +169,24 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
             bar_sync(1, kMC);
             if (s.misc[0]) {
                 __threadfence();
+                // (m, l) of every split -> shared memory in one round trip, then one pass over part_o
+                float *ml = mrg;  // [GQ][ns][2], the merge buffer is free again
+                for (int i = tid; i < GQ * ns * 2; i += kMC) {
+                    const int g = i / (ns * 2), r = i % (ns * 2);
+                    ml[i] = __ldcg(&p.part_ml[((size_t)(hk * GQ + g) * p.n_splits) * 2 + r]);
+                }
+                bar_sync(1, kMC);
                 if (tid < GQ * HD) {
                     const int g = tid / HD, dd = tid % HD;
                     const size_t pb = (size_t)(hk * GQ + g) * p.n_splits;
                     float M = -INFINITY;
-                    for (int sp = 0; sp < ns; ++sp) M = fmaxf(M, __ldcg(&p.part_ml[(pb + sp) * 2]));
+                    for (int sp = 0; sp < ns; ++sp) M = fmaxf(M, ml[(g * ns + sp) * 2]);
                     float L = 0.f, O = 0.f;
-#pragma unroll 4
+#pragma unroll 8
                     for (int sp = 0; sp < ns; ++sp) {
-                        const float ms = __ldcg(&p.part_ml[(pb + sp) * 2]);
+                        const float ms = ml[(g * ns + sp) * 2];
                         const float cf = ms == -INFINITY ? 0.f : exp2f(ms - M);
-                        L += __ldcg(&p.part_ml[(pb + sp) * 2 + 1]) * cf;
+                        L += ml[(g * ns + sp) * 2 + 1] * cf;
                         O += __ldcg(&p.part_o[(pb + sp) * HD + dd]) * cf;
                     }
                     p.att[(size_t)(hk * GQ + g) * HD + dd] = O / L;

@@ -1,0 +1,184 @@
+// mega_gemv.cuh -- one weight-streaming GEMV phase of the persistent decode kernel, consumer
+// side (included by decode_mega.cu).  Tensor-core formulation of y = W x at batch 1:
+//   D[m16, n8] += A[m16, k16] * B[k16, n8]   (mma.sync.m16n8k16, bf16 x bf16 -> fp32)
+// with B = 8 weight rows straight from the ring (ldmatrix.x4 = two k16 steps), and A = the
+// activation vector split as x = hi + lo (both bf16): row 0 of A is hi, row 1 is lo, rows
+// 2..15 are zero.  D[0][n] + D[1][n] is then the fp32-accurate dot product of weight row n.
+#pragma once
+
+__device__ __forceinline__ void ldsm_x4(uint32_t saddr, uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"(saddr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+    const uint32_t z = 0u;  // A rows 8..15 are zero
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+        "{%0, %1, %2, %3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(z), "r"(a2), "r"(z), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    return (uint32_t)f32_to_bf16_bits(a) | ((uint32_t)f32_to_bf16_bits(b) << 16);
+}
+__device__ __forceinline__ float bf16_round(float a) { return __uint_as_float((uint32_t)f32_to_bf16_bits(a) << 16); }
+
+__device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const MegaSmem &s, StepCtx &c, int G,
+                                int bid, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int K = job.K;
+    const int parts = k_parts(K);
+    const int kc = K / parts;
+    const uint32_t row_smem = (uint32_t)kc * 2 + 16;
+
+    // ---- activation vector -> (optional RMSNorm) -> bf16 hi/lo operand table in shared memory ----
+    // item = (k16 block i, t): the four values x[16i+2t], x[16i+2t+1], x[16i+2t+8], x[16i+2t+9]
+    const int n_items = K / 4;
+    float xv[6][4];
+    float ss = 0.f;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        const int it = j * kMC + tid;
+        if (it < n_items) {
+            const int k = (it >> 2) * 16 + (it & 3) * 2;
+            if (job.x_src == MEGA_X_EMBED) {
+                const uint16_t *e = reinterpret_cast<const uint16_t *>(p.embed) + (size_t)c.tok * p.d + k;
+                const uint32_t u0 = *reinterpret_cast<const uint32_t *>(e);
+                const uint32_t u1 = *reinterpret_cast<const uint32_t *>(e + 8);
+                xv[j][0] = bf16lo(u0), xv[j][1] = bf16hi(u0), xv[j][2] = bf16lo(u1), xv[j][3] = bf16hi(u1);
+                if ((it % G) == bid) {  // residual stream h <- embedding row, each element written once
+                    *reinterpret_cast<float2 *>(p.h + k) = make_float2(xv[j][0], xv[j][1]);
+                    *reinterpret_cast<float2 *>(p.h + k + 8) = make_float2(xv[j][2], xv[j][3]);
+                }
+            } else {
+                const float *x = job.x_src == MEGA_X_H ? p.h : (job.x_src == MEGA_X_ATT ? p.att : p.act);
+                const float2 v0 = __ldcg(reinterpret_cast<const float2 *>(x + k));
+                const float2 v1 = __ldcg(reinterpret_cast<const float2 *>(x + k + 8));
+                xv[j][0] = v0.x, xv[j][1] = v0.y, xv[j][2] = v1.x, xv[j][3] = v1.y;
+            }
+            ss += xv[j][0] * xv[j][0] + xv[j][1] * xv[j][1] + xv[j][2] * xv[j][2] + xv[j][3] * xv[j][3];
+        }
+    }
+    float sc = 1.f;
+    if (job.gain != nullptr) {  // fused RMSNorm prologue
+        ss = warp_sum(ss);
+        if (lane == 0) s.red[warp] = ss;
+        bar_sync(1, kMC);
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < kMW; ++w) tot += s.red[w];
+        sc = rsqrtf(tot / (float)K + p.rms_eps);
+    }
+    const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        const int it = j * kMC + tid;
+        if (it < n_items) {
+            const int i16 = it >> 2, t = it & 3;
+            float v[4] = {xv[j][0], xv[j][1], xv[j][2], xv[j][3]};
+            if (gain != nullptr) {
+                const int k = i16 * 16 + t * 2;
+                const uint32_t g0 = *reinterpret_cast<const uint32_t *>(gain + k);
+                const uint32_t g1 = *reinterpret_cast<const uint32_t *>(gain + k + 8);
+                v[0] = bf16lo(g0) * (v[0] * sc), v[1] = bf16hi(g0) * (v[1] * sc);
+                v[2] = bf16lo(g1) * (v[2] * sc), v[3] = bf16hi(g1) * (v[3] * sc);
+            }
+            float hi[4], lo[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) hi[e] = bf16_round(v[e]), lo[e] = v[e] - hi[e];
+            uint2 *tab = reinterpret_cast<uint2 *>(s.xtab) + i16 * 8 + t;
+            tab[0] = make_uint2(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]));  // A row 0
+            tab[4] = make_uint2(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]));  // A row 1
+        }
+    }
+    bar_sync(1, kMC);
+    mega_trace(p, c.ti, bid, tid);  // operand table ready
+
+    const RowRange rr = cta_rows(job.N, G, bid);
+    const int epi = job.epi;
+    const int gran = (epi == B200LLM_EPI_SWIGLU || epi == B200LLM_EPI_QKV_ROPE) ? 2 : 1;
+    const int steps32 = kc / 32;
+    const uint32_t ring_s = smem_u32(s.ring);
+    const uint2 *xtab = reinterpret_cast<const uint2 *>(s.xtab);
+    // ldmatrix row address of this lane inside a stage: matrix (lane / 8) covers k + 8 * (lane / 8)
+    const uint32_t lane_off = (uint32_t)(lane & 7) * row_smem + (uint32_t)(lane >> 3) * 16;
+
+    for (int blk0 = 0; blk0 < rr.nrows; blk0 += kRB) {
+        const int blk_rows = min(kRB, rr.nrows - blk0);
+        for (int grp = 0; grp < blk_rows / 8; ++grp) {
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int pt = 0; pt < parts; ++pt, ++c.gs) {
+                const uint32_t slot = c.gs % kSlots, use = c.gs / kSlots;
+                mbar_wait(&s.full[slot], use & 1);
+                const uint32_t st_base = ring_s + slot * kSlotBytes + lane_off;
+                const int i16_base = (pt * kc) >> 4;
+#pragma unroll 4
+                for (int st = warp; st < steps32; st += kMW) {
+                    uint32_t b0, b1, b2, b3;
+                    ldsm_x4(st_base + (uint32_t)st * 64, b0, b1, b2, b3);
+                    uint2 a_lo = make_uint2(0u, 0u), a_hi = make_uint2(0u, 0u);
+                    if (lane < 8) {
+                        a_lo = xtab[(i16_base + 2 * st) * 8 + lane];
+                        a_hi = xtab[(i16_base + 2 * st + 1) * 8 + lane];
+                    }
+                    mma_bf16_16816(acc, a_lo.x, a_lo.y, b0, b1);
+                    mma_bf16_16816(acc, a_hi.x, a_hi.y, b2, b3);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s.empty[slot]);
+            }
+            // D row 0 (hi) lives in lanes 0..3, row 1 (lo) in lanes 4..7: add them
+            const float v0 = acc[0] + __shfl_down_sync(0xffffffffu, acc[0], 4);
+            const float v1 = acc[1] + __shfl_down_sync(0xffffffffu, acc[1], 4);
+            if (lane < 4) {
+                s.part[(grp * 8 + 2 * lane) * kMW + warp] = v0;
+                s.part[(grp * 8 + 2 * lane + 1) * kMW + warp] = v1;
+            }
+        }
+        bar_sync(1, kMC);
+        mega_trace(p, c.ti, bid, tid);  // ring consumed
+        // ---- combine the 16 warp partials of every row of the block + fused epilogue ----
+        const int blk_units = blk_rows / gran;
+        for (int u = tid; u < blk_units; u += kMC) {
+            const int rl = u * gran;
+            const int n = rr.row0 + blk0 + rl;
+            float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+            for (int w = 0; w < kMW; ++w) v0 += s.part[rl * kMW + w];
+            if (gran == 2) {
+#pragma unroll
+                for (int w = 0; w < kMW; ++w) v1 += s.part[(rl + 1) * kMW + w];
+            }
+            if (epi == B200LLM_EPI_RESIDUAL) {
+                p.h[n] = __ldcg(p.h + n) + v0;
+            } else if (epi == B200LLM_EPI_SWIGLU) {
+                p.act[n >> 1] = (v0 / (1.f + expf(-v0))) * v1;
+            } else if (epi == B200LLM_EPI_LOGITS) {
+                p.logits[n] = v0;
+                if (v0 > c.best) c.best = v0, c.best_i = n;
+            } else {  // QKV_ROPE
+                const int hd = p.head_dim;
+                const int qrows = p.n_q * hd, krows = p.n_kv * hd;
+                if (n < qrows + krows) {
+                    const float ang = (float)c.pos * p.inv_freq[(n % hd) >> 1];
+                    float sn, cs;
+                    sincosf(ang, &sn, &cs);
+                    const float o0 = v0 * cs - v1 * sn, o1 = v1 * cs + v0 * sn;
+                    v0 = o0, v1 = o1;
+                }
+                if (n < qrows) {
+                    *reinterpret_cast<float2 *>(p.q + n) = make_float2(v0, v1);
+                } else {
+                    const int page = p.page_table[c.pos / kMPT];
+                    const bool is_k = n < qrows + krows;
+                    const int kn = is_k ? n - qrows : n - qrows - krows;
+                    uint16_t *dst = reinterpret_cast<uint16_t *>(is_k ? job.k_pages : job.v_pages) +
+                                    (((size_t)page * p.n_kv + kn / hd) * kMPT + (c.pos % kMPT)) * hd + kn % hd;
+                    *reinterpret_cast<uint32_t *>(dst) = pack_bf16(v0, v1);
+                }
+            }
+        }
+        if (blk0 + kRB < rr.nrows) bar_sync(1, kMC);  // partials are overwritten by the next block
+    }
+}

@@ -5,7 +5,7 @@
 template <int HD, int GQ>
 __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_constant__ MegaParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    const MegaSmem s = carve(smem_raw, HD);
+    const MegaSmem s = carve(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int G = gridDim.x, bid = blockIdx.x;
 

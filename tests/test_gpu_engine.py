@@ -142,6 +142,24 @@ def test_golden_parity_full_size(fname, name, golden_dir):
     eng.close()
 
 
+@pytest.mark.parametrize("mega", [True, False])
+def test_repeated_requests_on_one_engine(mega):
+    """Request after request on one engine (64-row prefill chunks, then batch-1 decode, which
+    use different attention split layouts of the same scratch) keeps matching the oracle."""
+    from b200llm import SamplingParams
+    geo = lo.GEOMETRIES["small"]
+    sd = lo.make_weights(geo, 0xB200, sigma=0.06)
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    ids = wg.gen_tokens(87, 21, geo.vocab)
+    want = orc.greedy(ids, 12)[0]
+    eng = _engine("small", sd, max_lanes=4, max_ctx=1024, max_rows=64, use_megakernel=mega)
+    for _ in range(3):
+        toks, tm = eng.generate_ids(ids, 12, SamplingParams(temperature=0.0))
+        assert toks == want
+        assert tm.decode_steps == 11 and tm.prefill_tokens == 87
+    eng.close()
+
+
 def test_shim_replays_reference_call_sites():
     """The six ollama.generate call patterns of the reference, unmodified, against the shim."""
     import ollama

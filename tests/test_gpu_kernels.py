@@ -210,9 +210,9 @@ def test_attn_scratch_is_reusable_and_checked():
         o2 = attn_decode(q, kp.cuda(), vp.cuda(), lanes, pos, ptab.cuda(), nq, nkv, hd, 1)
         _close(o1.cpu(), o2.cpu(), 1e-5)
         outs.append(o1)
-    assert int(sc[:256].view(torch.int32).abs().sum()) == 0
+    assert int(sc[:256 * 1024].view(torch.int32).abs().sum()) == 0
     with pytest.raises(_lib.B200LLMError) as ei:
-        attn_decode(q, kp.cuda(), vp.cuda(), lanes, pos, ptab.cuda(), nq, nkv, hd, 8, scratch=sc[:512])
+        attn_decode(q, kp.cuda(), vp.cuda(), lanes, pos, ptab.cuda(), nq, nkv, hd, 8, scratch=sc[:256 * 1024 + 512])
     assert ei.value.code == _lib.ENOMEM
 
 

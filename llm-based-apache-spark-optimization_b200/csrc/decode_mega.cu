@@ -43,6 +43,7 @@ struct MegaSmem {
     uint64_t *full, *empty, *att_full;
     float *red;
     int *misc;
+    float *rope;  // [head_dim/2][cos, sin] of the current position
 };
 
 __device__ __forceinline__ MegaSmem carve(uint8_t *base) {
@@ -55,11 +56,12 @@ __device__ __forceinline__ MegaSmem carve(uint8_t *base) {
     s.att_full = s.empty + kSlots;
     s.red = reinterpret_cast<float *>(s.att_full + kAttW);
     s.misc = reinterpret_cast<int *>(s.red + 64);
+    s.rope = reinterpret_cast<float *>(s.misc + 64);
     return s;
 }
 
 size_t mega_smem_bytes(int) {
-    return (size_t)kSlots * kSlotBytes + kXtabBytes + kPartBytes + (2 * kSlots + kAttW) * 8 + 64 * 4 + 256;
+    return (size_t)kSlots * kSlotBytes + kXtabBytes + kPartBytes + (2 * kSlots + kAttW) * 8 + 64 * 4 + 256 + 128 * 4;
 }
 
 __host__ __device__ __forceinline__ int k_parts(int K) {
@@ -90,11 +92,11 @@ __device__ __forceinline__ RowRange cta_rows(int N, int G, int bid) {
 }
 
 // Grid barrier for the compute threads (the producer warp never takes part).
+// (release/acquire at gpu scope; the CTA barrier in front makes the release cumulative over the
+// writes of all compute threads.)
 __device__ __forceinline__ void grid_sync(unsigned *ctr, unsigned target, int tid) {
-    asm volatile("fence.proxy.async;" ::: "memory");  // KV rows written here are read by TMA elsewhere
     bar_sync(1, kMC);
     if (tid == 0) {
-        __threadfence();
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
         unsigned v;
         do {

@@ -1,149 +1,126 @@
 // mega_attn.cuh -- attention phase of the persistent decode kernel (included by decode_mega.cu).
-// Work items = (kv head, split of the lane's KV pages); item i runs on CTA i % G.  Inside a
-// CTA, kAttW warps stream the item's pages (one K+V tile pair per warp in flight, 1-D TMA
-// bulk copies), 8 lanes per token as in attn.cu.  The item's partial (m, l, o) goes to the
-// global scratch; the last CTA to arrive for a KV head (atomic ticket) merges the splits.
+//
+// Latency, not bandwidth, bounds this phase at batch 1 (a few MB of KV per layer), so the chain
+// of dependent round trips is kept as short as possible: all 16 compute warps of a CTA read K/V
+// rows of the lane's pages straight from L2/HBM into registers (16 lanes per token, each lane
+// one 16-byte slice of the row, several tokens in flight per warp), and the split-T factor only
+// grows once a warp would have to walk more than two pages, so short contexts need no
+// cross-CTA merge at all.  (The standalone kernel in attn.cu, used for batches and prefill,
+// stages K/V tiles with TMA instead.)
+// Work items = (kv head, split); item i runs on CTA i % G.
 #pragma once
 
 template <int HD, int GQ>
 __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, const MegaSmem &s, const StepCtx &c,
-                                uint32_t &att_use, int G, int bid, int tid) {
-    constexpr int EL = HD / 16;
-    constexpr int TILE = kMPT * HD * 2;
+                                int G, int bid, int tid) {
+    constexpr int EL = HD / 16;  // dims per lane: 16 lanes cover one K/V row
     const int warp = tid >> 5, lane = tid & 31;
-    const int tg = lane >> 3, p8 = lane & 7;
+    const int tg = lane >> 4, p16 = lane & 15;
     const int n_pages = c.pos / kMPT + 1;
-    // one page per attention warp and item until the split cap is reached: fewer, fatter items
-    // keep the cross-split merge short
-    const int ns = min(p.n_splits, (n_pages + kAttW - 1) / kAttW);
+    const int ns = min(p.n_splits, (n_pages + 2 * kMW - 1) / (2 * kMW));
     const int pps = (n_pages + ns - 1) / ns;
     const int n_items = p.n_kv * ns;
-    const uint8_t *kbase = reinterpret_cast<const uint8_t *>(qkv_job.k_pages);
-    const uint8_t *vbase = reinterpret_cast<const uint8_t *>(qkv_job.v_pages);
-    float *mrg = s.part;  // [kAttW][GQ][HD + 2]
+    const uint16_t *kbase = reinterpret_cast<const uint16_t *>(qkv_job.k_pages);
+    const uint16_t *vbase = reinterpret_cast<const uint16_t *>(qkv_job.v_pages);
+    float *mrg = reinterpret_cast<float *>(s.xtab);  // [kMW][GQ][HD + 2]; the operand table is idle here
 
     for (int item = bid; item < n_items; item += G) {
         const int hk = item / ns, split = item % ns;
         const int pg_begin = split * pps, pg_end = min(n_pages, pg_begin + pps);
-        if (warp < kAttW) {
-            float qa[GQ][EL], qb[GQ][EL], m[GQ], l[GQ], oa[GQ][EL], ob[GQ][EL];
+        float q[GQ][EL], m[GQ], l[GQ], o[GQ][EL];
 #pragma unroll
-            for (int g = 0; g < GQ; ++g) {
-                const float *qp = p.q + (size_t)(hk * GQ + g) * HD;
+        for (int g = 0; g < GQ; ++g) {
+            const float *qp = p.q + (size_t)(hk * GQ + g) * HD + p16 * EL;
 #pragma unroll
-                for (int e = 0; e < EL; ++e) {
-                    qa[g][e] = __ldcg(qp + p8 * EL + e) * p.scale_log2;
-                    qb[g][e] = __ldcg(qp + HD / 2 + p8 * EL + e) * p.scale_log2;
-                    oa[g][e] = 0.f, ob[g][e] = 0.f;
-                }
-                m[g] = -INFINITY, l[g] = 0.f;
+            for (int e = 0; e < EL; e += 4) {
+                const float4 v = __ldcg(reinterpret_cast<const float4 *>(qp + e));
+                q[g][e] = v.x * p.scale_log2, q[g][e + 1] = v.y * p.scale_log2;
+                q[g][e + 2] = v.z * p.scale_log2, q[g][e + 3] = v.w * p.scale_log2;
             }
-            uint8_t *ks = s.xtab + (size_t)warp * 2 * TILE;
-            uint8_t *vs = ks + TILE;
-            for (int pg = pg_begin + warp; pg < pg_end; pg += kAttW) {
-                if (lane == 0) {
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    const size_t off = ((size_t)p.page_table[pg] * p.n_kv + hk) * (size_t)TILE;
-                    mbar_expect_tx(&s.att_full[warp], 2 * TILE);
-                    tma_load_1d(ks, kbase + off, TILE, &s.att_full[warp]);
-                    tma_load_1d(vs, vbase + off, TILE, &s.att_full[warp]);
-                }
-                mbar_wait(&s.att_full[warp], att_use & 1);
-                ++att_use;
 #pragma unroll
-                for (int it = 0; it < kMPT / 4; ++it) {
-                    const int t = it * 4 + tg;
-                    const bool ok = (pg * kMPT + t) <= c.pos;
-                    float ka[EL], kb[EL], va[EL], vb[EL];
-                    if constexpr (EL == 8) {
-                        const uint4 A = *reinterpret_cast<const uint4 *>(ks + (size_t)t * HD * 2 + p8 * 16);
-                        const uint4 B = *reinterpret_cast<const uint4 *>(ks + (size_t)t * HD * 2 + HD + p8 * 16);
-                        const uint4 C = *reinterpret_cast<const uint4 *>(vs + (size_t)t * HD * 2 + p8 * 16);
-                        const uint4 D = *reinterpret_cast<const uint4 *>(vs + (size_t)t * HD * 2 + HD + p8 * 16);
-                        const uint32_t aw[4] = {A.x, A.y, A.z, A.w}, bw[4] = {B.x, B.y, B.z, B.w};
-                        const uint32_t cw[4] = {C.x, C.y, C.z, C.w}, dw[4] = {D.x, D.y, D.z, D.w};
+            for (int e = 0; e < EL; ++e) o[g][e] = 0.f;
+            m[g] = -INFINITY, l[g] = 0.f;
+        }
+        for (int pg = pg_begin + warp; pg < pg_end; pg += kMW) {
+            const size_t tile = ((size_t)p.page_table[pg] * p.n_kv + hk) * (size_t)(kMPT * HD);
+            const uint16_t *kp = kbase + tile + p16 * EL;
+            const uint16_t *vp = vbase + tile + p16 * EL;
+#pragma unroll 4
+            for (int it = 0; it < kMPT / 2; ++it) {
+                const int t = it * 2 + tg;
+                const bool ok = (pg * kMPT + t) <= c.pos;
+                float kf[EL], vf[EL];
+                if constexpr (EL == 8) {
+                    const uint4 A = __ldcg(reinterpret_cast<const uint4 *>(kp + (size_t)t * HD));
+                    const uint4 B = __ldcg(reinterpret_cast<const uint4 *>(vp + (size_t)t * HD));
+                    const uint32_t aw[4] = {A.x, A.y, A.z, A.w}, bw[4] = {B.x, B.y, B.z, B.w};
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            ka[2 * e] = bf16lo(aw[e]), ka[2 * e + 1] = bf16hi(aw[e]);
-                            kb[2 * e] = bf16lo(bw[e]), kb[2 * e + 1] = bf16hi(bw[e]);
-                            va[2 * e] = bf16lo(cw[e]), va[2 * e + 1] = bf16hi(cw[e]);
-                            vb[2 * e] = bf16lo(dw[e]), vb[2 * e + 1] = bf16hi(dw[e]);
-                        }
-                    } else {
-                        const uint2 A = *reinterpret_cast<const uint2 *>(ks + (size_t)t * HD * 2 + p8 * 8);
-                        const uint2 B = *reinterpret_cast<const uint2 *>(ks + (size_t)t * HD * 2 + HD + p8 * 8);
-                        const uint2 C = *reinterpret_cast<const uint2 *>(vs + (size_t)t * HD * 2 + p8 * 8);
-                        const uint2 D = *reinterpret_cast<const uint2 *>(vs + (size_t)t * HD * 2 + HD + p8 * 8);
-                        ka[0] = bf16lo(A.x), ka[1] = bf16hi(A.x), ka[2] = bf16lo(A.y), ka[3] = bf16hi(A.y);
-                        kb[0] = bf16lo(B.x), kb[1] = bf16hi(B.x), kb[2] = bf16lo(B.y), kb[3] = bf16hi(B.y);
-                        va[0] = bf16lo(C.x), va[1] = bf16hi(C.x), va[2] = bf16lo(C.y), va[3] = bf16hi(C.y);
-                        vb[0] = bf16lo(D.x), vb[1] = bf16hi(D.x), vb[2] = bf16lo(D.y), vb[3] = bf16hi(D.y);
+                    for (int e = 0; e < 4; ++e) {
+                        kf[2 * e] = bf16lo(aw[e]), kf[2 * e + 1] = bf16hi(aw[e]);
+                        vf[2 * e] = bf16lo(bw[e]), vf[2 * e + 1] = bf16hi(bw[e]);
                     }
-#pragma unroll
-                    for (int g = 0; g < GQ; ++g) {
-                        float sc = 0.f;
-#pragma unroll
-                        for (int e = 0; e < EL; ++e) sc = fmaf(qa[g][e], ka[e], fmaf(qb[g][e], kb[e], sc));
-                        sc += __shfl_xor_sync(0xffffffffu, sc, 1);
-                        sc += __shfl_xor_sync(0xffffffffu, sc, 2);
-                        sc += __shfl_xor_sync(0xffffffffu, sc, 4);
-                        if (ok) {
-                            const float mn = fmaxf(m[g], sc);
-                            const float corr = exp2f(m[g] - mn), pr = exp2f(sc - mn);
-                            l[g] = l[g] * corr + pr;
-#pragma unroll
-                            for (int e = 0; e < EL; ++e) {
-                                oa[g][e] = fmaf(pr, va[e], oa[g][e] * corr);
-                                ob[g][e] = fmaf(pr, vb[e], ob[g][e] * corr);
-                            }
-                            m[g] = mn;
-                        }
-                    }
+                } else {
+                    const uint2 A = __ldcg(reinterpret_cast<const uint2 *>(kp + (size_t)t * HD));
+                    const uint2 B = __ldcg(reinterpret_cast<const uint2 *>(vp + (size_t)t * HD));
+                    kf[0] = bf16lo(A.x), kf[1] = bf16hi(A.x), kf[2] = bf16lo(A.y), kf[3] = bf16hi(A.y);
+                    vf[0] = bf16lo(B.x), vf[1] = bf16hi(B.x), vf[2] = bf16lo(B.y), vf[3] = bf16hi(B.y);
                 }
-                __syncwarp();
-            }
-            // merge the 4 token-group streams of the warp
-#pragma unroll
-            for (int off = 8; off <= 16; off <<= 1) {
 #pragma unroll
                 for (int g = 0; g < GQ; ++g) {
-                    const float m2 = __shfl_xor_sync(0xffffffffu, m[g], off);
-                    const float l2 = __shfl_xor_sync(0xffffffffu, l[g], off);
-                    const float mn = fmaxf(m[g], m2);
-                    const float c1 = mn == -INFINITY ? 0.f : exp2f(m[g] - mn);
-                    const float c2 = mn == -INFINITY ? 0.f : exp2f(m2 - mn);
-                    l[g] = l[g] * c1 + l2 * c2;
-                    m[g] = mn;
+                    float sc = 0.f;
 #pragma unroll
-                    for (int e = 0; e < EL; ++e) {
-                        const float o2a = __shfl_xor_sync(0xffffffffu, oa[g][e], off);
-                        const float o2b = __shfl_xor_sync(0xffffffffu, ob[g][e], off);
-                        oa[g][e] = oa[g][e] * c1 + o2a * c2;
-                        ob[g][e] = ob[g][e] * c1 + o2b * c2;
+                    for (int e = 0; e < EL; ++e) sc = fmaf(q[g][e], kf[e], sc);
+                    sc += __shfl_xor_sync(0xffffffffu, sc, 1);
+                    sc += __shfl_xor_sync(0xffffffffu, sc, 2);
+                    sc += __shfl_xor_sync(0xffffffffu, sc, 4);
+                    sc += __shfl_xor_sync(0xffffffffu, sc, 8);
+                    if (ok) {
+                        const float mn = fmaxf(m[g], sc);
+                        const float corr = exp2f(m[g] - mn), pr = exp2f(sc - mn);
+                        l[g] = l[g] * corr + pr;
+#pragma unroll
+                        for (int e = 0; e < EL; ++e) o[g][e] = fmaf(pr, vf[e], o[g][e] * corr);
+                        m[g] = mn;
                     }
-                }
-            }
-            if (tg == 0) {
-#pragma unroll
-                for (int g = 0; g < GQ; ++g) {
-                    float *d = mrg + ((size_t)warp * GQ + g) * (HD + 2);
-                    if (p8 == 0) d[HD] = m[g], d[HD + 1] = l[g];
-#pragma unroll
-                    for (int e = 0; e < EL; ++e) d[p8 * EL + e] = oa[g][e], d[HD / 2 + p8 * EL + e] = ob[g][e];
                 }
             }
         }
+        // merge the two token streams of the warp (lanes 0..15 and 16..31)
+#pragma unroll
+        for (int g = 0; g < GQ; ++g) {
+            const float m2 = __shfl_xor_sync(0xffffffffu, m[g], 16);
+            const float l2 = __shfl_xor_sync(0xffffffffu, l[g], 16);
+            const float mn = fmaxf(m[g], m2);
+            const float c1 = mn == -INFINITY ? 0.f : exp2f(m[g] - mn);
+            const float c2 = mn == -INFINITY ? 0.f : exp2f(m2 - mn);
+            l[g] = l[g] * c1 + l2 * c2;
+            m[g] = mn;
+#pragma unroll
+            for (int e = 0; e < EL; ++e) {
+                const float o2 = __shfl_xor_sync(0xffffffffu, o[g][e], 16);
+                o[g][e] = o[g][e] * c1 + o2 * c2;
+            }
+        }
+        if (tg == 0) {
+#pragma unroll
+            for (int g = 0; g < GQ; ++g) {
+                float *d = mrg + ((size_t)warp * GQ + g) * (HD + 2);
+                if (p16 == 0) d[HD] = m[g], d[HD + 1] = l[g];
+#pragma unroll
+                for (int e = 0; e < EL; ++e) d[p16 * EL + e] = o[g][e];
+            }
+        }
         bar_sync(1, kMC);
-        // ---- CTA partial = merge of the kAttW warps; one thread per (q head, dim) ----
+        // ---- CTA result = merge of the 16 warps; one thread per (q head, dim) ----
         if (tid < GQ * HD) {
             const int g = tid / HD, dd = tid % HD;
             float M = -INFINITY;
 #pragma unroll
-            for (int w = 0; w < kAttW; ++w) M = fmaxf(M, mrg[((size_t)w * GQ + g) * (HD + 2) + HD]);
+            for (int w = 0; w < kMW; ++w) M = fmaxf(M, mrg[((size_t)w * GQ + g) * (HD + 2) + HD]);
             float L = 0.f, O = 0.f;
             if (M != -INFINITY) {
 #pragma unroll
-                for (int w = 0; w < kAttW; ++w) {
+                for (int w = 0; w < kMW; ++w) {
                     const float *sp = mrg + ((size_t)w * GQ + g) * (HD + 2);
                     const float cf = exp2f(sp[HD] - M);
                     L += sp[HD + 1] * cf;
@@ -160,6 +137,7 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
             }
         }
         if (ns > 1) {
+            // cross-split merge by the last CTA to arrive for this kv head (fixed split order)
             __threadfence();
             bar_sync(1, kMC);
             if (tid == 0) {
@@ -169,8 +147,7 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
             bar_sync(1, kMC);
             if (s.misc[0]) {
                 __threadfence();
-                // (m, l) of every split -> shared memory in one round trip, then one pass over part_o
-                float *ml = mrg;  // [GQ][ns][2], the merge buffer is free again
+                float *ml = s.part;  // [GQ][ns][2]
                 for (int i = tid; i < GQ * ns * 2; i += kMC) {
                     const int g = i / (ns * 2), r = i % (ns * 2);
                     ml[i] = __ldcg(&p.part_ml[((size_t)(hk * GQ + g) * p.n_splits) * 2 + r]);
@@ -194,6 +171,6 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
                 if (tid == 0) p.tickets[hk] = 0;
             }
         }
-        bar_sync(1, kMC);  // merge buffer and misc are reused by the next item / phase
+        bar_sync(1, kMC);  // merge buffers are reused by the next item / phase
     }
 }

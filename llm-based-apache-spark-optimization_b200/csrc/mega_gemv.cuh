@@ -60,17 +60,14 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
             ss += xv[j][0] * xv[j][0] + xv[j][1] * xv[j][1] + xv[j][2] * xv[j][2] + xv[j][3] * xv[j][3];
         }
     }
-    float sc = 1.f;
-    if (job.gain != nullptr) {  // fused RMSNorm prologue
+    // Fused RMSNorm prologue: the operand table holds gain * x; the scalar rsqrt(mean(x^2) + eps)
+    // multiplies the result in the epilogue, so the block reduction of sum(x^2) is off the
+    // critical path (it completes under the same barrier that publishes the table).
+    const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
+    if (gain != nullptr) {
         ss = warp_sum(ss);
         if (lane == 0) s.red[warp] = ss;
-        bar_sync(1, kMC);
-        float tot = 0.f;
-#pragma unroll
-        for (int w = 0; w < kMW; ++w) tot += s.red[w];
-        sc = rsqrtf(tot / (float)K + p.rms_eps);
     }
-    const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
         const int it = j * kMC + tid;
@@ -81,8 +78,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
                 const int k = i16 * 16 + t * 2;
                 const uint32_t g0 = *reinterpret_cast<const uint32_t *>(gain + k);
                 const uint32_t g1 = *reinterpret_cast<const uint32_t *>(gain + k + 8);
-                v[0] = bf16lo(g0) * (v[0] * sc), v[1] = bf16hi(g0) * (v[1] * sc);
-                v[2] = bf16lo(g1) * (v[2] * sc), v[3] = bf16hi(g1) * (v[3] * sc);
+                v[0] *= bf16lo(g0), v[1] *= bf16hi(g0), v[2] *= bf16lo(g1), v[3] *= bf16hi(g1);
             }
             float hi[4], lo[4];
 #pragma unroll
@@ -93,6 +89,13 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
         }
     }
     bar_sync(1, kMC);
+    float sc = 1.f;
+    if (gain != nullptr) {
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < kMW; ++w) tot += s.red[w];
+        sc = rsqrtf(tot / (float)K + p.rms_eps);
+    }
     mega_trace(p, c.ti, bid, tid);  // operand table ready
 
     const RowRange rr = cta_rows(job.N, G, bid);
@@ -150,6 +153,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
 #pragma unroll
                 for (int w = 0; w < kMW; ++w) v1 += s.part[(rl + 1) * kMW + w];
             }
+            v0 *= sc, v1 *= sc;
             if (epi == B200LLM_EPI_RESIDUAL) {
                 p.h[n] = __ldcg(p.h + n) + v0;
             } else if (epi == B200LLM_EPI_SWIGLU) {
@@ -161,9 +165,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
                 const int hd = p.head_dim;
                 const int qrows = p.n_q * hd, krows = p.n_kv * hd;
                 if (n < qrows + krows) {
-                    const float ang = (float)c.pos * p.inv_freq[(n % hd) >> 1];
-                    float sn, cs;
-                    sincosf(ang, &sn, &cs);
+                    const float cs = s.rope[(n % hd) & ~1], sn = s.rope[((n % hd) & ~1) + 1];  // cos/sin of this step
                     const float o0 = v0 * cs - v1 * sn, o1 = v1 * cs + v0 * sn;
                     v0 = o0, v1 = o1;
                 }

@@ -28,7 +28,6 @@ __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_c
     c.gs = 0;
     c.tok = __ldcg(p.lane_token + p.lane);
     c.pos = __ldcg(p.lane_pos + p.lane);
-    uint32_t att_use = 0;
     unsigned bar_no = 0;
     const int n_jobs = 4 * p.n_layers + 1;
 
@@ -37,13 +36,18 @@ __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_c
         mega_trace(p, c.ti, bid, tid);
         c.tok = min(max(c.tok, 0), p.vocab - 1);
         if (bid == 0 && tid == 0) p.lane_hist[(size_t)p.lane * 64 + (c.pos & 63)] = c.tok;
+        if (tid < HD / 2) {  // RoPE angles of this position, used by the qkv epilogues of every layer
+            float sn, cs;
+            sincosf((float)c.pos * p.inv_freq[tid], &sn, &cs);
+            s.rope[2 * tid] = cs, s.rope[2 * tid + 1] = sn;
+        }
         for (int l = 0; l < p.n_layers; ++l) {
             const MegaJob *jb = p.jobs + 4 * l;
             mega_gemv_phase(p, jb[0], s, c, G, bid, tid);  // rmsnorm + qkv + rope + kv append
             mega_trace(p, c.ti, bid, tid);
             grid_sync(p.bar_ctr, ++bar_no * G, tid);
             mega_trace(p, c.ti, bid, tid);
-            mega_attn_phase<HD, GQ>(p, jb[0], s, c, att_use, G, bid, tid);
+            mega_attn_phase<HD, GQ>(p, jb[0], s, c, G, bid, tid);
             mega_trace(p, c.ti, bid, tid);
             grid_sync(p.bar_ctr, ++bar_no * G, tid);
             mega_trace(p, c.ti, bid, tid);

@@ -107,7 +107,7 @@ __device__ __forceinline__ void grid_sync(unsigned *ctr, unsigned target, int ti
 }
 
 // ---------------------------------------------------------------- producer: the weight stream
-__device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int bid) {
+__device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int bid, int lane) {
     const uint64_t pol = l2_policy_evict_first();
     const int n_jobs = 4 * p.n_layers + 1;
     uint32_t gs = 0;
@@ -122,15 +122,20 @@ __device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int
             const uint8_t *src = reinterpret_cast<const uint8_t *>(job.w) + (size_t)rr.row0 * row_bytes;
             for (int grp = 0; grp < rr.nrows / 8; ++grp) {
                 for (int pt = 0; pt < parts; ++pt, ++gs) {
-                    const uint32_t slot = gs % kSlots, use = gs / kSlots;
+                    const uint32_t slot = gs % (uint32_t)p.ring_slots, use = gs / (uint32_t)p.ring_slots;
                     if (use > 0) mbar_wait(&s.empty[slot], (use - 1) & 1);
-                    mbar_expect_tx(&s.full[slot], 8u * (uint32_t)kc * 2u);
+                    if (lane == 0) mbar_expect_tx(&s.full[slot], 8u * (uint32_t)kc * 2u);
+                    __syncwarp();
                     uint8_t *dst = s.ring + (size_t)slot * kSlotBytes;
                     const uint8_t *g0 = src + (size_t)grp * 8 * row_bytes + (size_t)pt * kc * 2;
-#pragma unroll
-                    for (int r = 0; r < 8; ++r)
-                        tma_load_1d_hint(dst + r * row_smem, g0 + (size_t)r * row_bytes, (uint32_t)kc * 2, &s.full[slot],
-                                         pol);
+                    if (p.dbg & 2) {
+                        if (lane == 0) tma_load_1d_hint(dst, g0, 8u * (uint32_t)kc * 2u, &s.full[slot], pol);
+                        continue;
+                    }
+                    // lanes 0..7 issue one row each
+                    if (lane < 8)
+                        tma_load_1d_hint(dst + lane * row_smem, g0 + (size_t)lane * row_bytes, (uint32_t)kc * 2,
+                                         &s.full[slot], pol);
                 }
             }
         }
@@ -146,7 +151,7 @@ struct StepCtx {
 };
 
 __device__ __forceinline__ void mega_trace(const MegaParams &p, int &ti, int bid, int tid) {
-    if (ti >= 0 && tid == 0 && ti < 1024) {
+    if (ti >= 0 && tid == 0 && ti < 480) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         p.trace[(bid ? 1024 : 0) + ti++] = t;

@@ -666,6 +666,12 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     p.part_ml = p.part_o + (size_t)c.n_q * ns * c.head_dim;
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
+    p.ring_slots = 5;
+    if (const char *dbg = getenv("B200LLM_MEGA_DBG")) p.dbg = atoi(dbg);
+    if (const char *rs = getenv("B200LLM_MEGA_SLOTS")) {
+        int v = atoi(rs);
+        if (v >= 1 && v <= 5) p.ring_slots = v;
+    }
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     e->last_rows = 1, e->last_logit_rows = 1;
     return mega_decode_launch(p, e->stream);

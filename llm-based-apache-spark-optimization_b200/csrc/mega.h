@@ -45,6 +45,8 @@ struct MegaParams {
     int32_t sample;       // 1: greedy argmax + feedback inside the kernel; 0: stop after logits
     unsigned long long *trace;  // optional [2][1024] globaltimer stamps of CTA 0 and CTA G-1 (debug)
     int32_t trace_step;
+    int32_t dbg;          // debug bits: 1 = consumer skips the MMAs, 2 = one bulk copy per stage (results invalid)
+    int32_t ring_slots;   // ring stages in use (<= 5); fewer = shallower prefetch (tuning knob)
 };
 
 int mega_decode_launch(const MegaParams &p, cudaStream_t stream);

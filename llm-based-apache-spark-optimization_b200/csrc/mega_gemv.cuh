@@ -1,9 +1,13 @@
 // mega_gemv.cuh -- one weight-streaming GEMV phase of the persistent decode kernel, consumer
 // side (included by decode_mega.cu).  Tensor-core formulation of y = W x at batch 1:
 //   D[m16, n8] += A[m16, k16] * B[k16, n8]   (mma.sync.m16n8k16, bf16 x bf16 -> fp32)
-// with B = 8 weight rows straight from the ring (ldmatrix.x4 = two k16 steps), and A = the
-// activation vector split as x = hi + lo (both bf16): row 0 of A is hi, row 1 is lo, rows
-// 2..15 are zero.  D[0][n] + D[1][n] is then the fp32-accurate dot product of weight row n.
+// One instruction covers 8 weight rows x 32 k: A rows 0..7 are the 8 weight rows over k-block
+// j, A rows 8..15 the SAME weight rows over k-block j+1 (one ldmatrix.x4 from the ring); the
+// activation vector is split as x = hi + lo (both bf16, together ~fp32 accurate) and B's
+// columns are (hi_j, lo_j, hi_j+1, lo_j+1, 0, 0, 0, 0).  D[r][0] + D[r][1] + D[8+r][2] + D[8+r][3]
+// is then the dot product of weight row r over the 32 k values; the other D entries are unused.
+// (mma.sync issues at about 1 per 28 clk per SM sub-partition on sm_100, measured in
+// profiles/: packing 256 weights into each instruction keeps the consumer ahead of the stream.)
 #pragma once
 
 __device__ __forceinline__ void ldsm_x4(uint32_t saddr, uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3) {
@@ -11,13 +15,13 @@ __device__ __forceinline__ void ldsm_x4(uint32_t saddr, uint32_t &r0, uint32_t &
                  : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
                  : "r"(saddr));
 }
-__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
-    const uint32_t z = 0u;  // A rows 8..15 are zero
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                               uint32_t b0, uint32_t b1) {
     asm volatile(
         "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
         "{%0, %1, %2, %3};"
         : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a0), "r"(z), "r"(a2), "r"(z), "r"(b0), "r"(b1));
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return (uint32_t)f32_to_bf16_bits(a) | ((uint32_t)f32_to_bf16_bits(b) << 16);
@@ -64,6 +68,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
     // multiplies the result in the epilogue, so the block reduction of sum(x^2) is off the
     // critical path (it completes under the same barrier that publishes the table).
     const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
+    if (ss != -1.f) mega_trace(p, c.ti, bid, tid);  // (debug) this thread's x values have arrived
     if (gain != nullptr) {
         ss = warp_sum(ss);
         if (lane == 0) s.red[warp] = ss;
@@ -88,6 +93,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
             tab[4] = make_uint2(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]));  // A row 1
         }
     }
+    mega_trace(p, c.ti, bid, tid);  // (debug) this thread's table entries written
     bar_sync(1, kMC);
     float sc = 1.f;
     if (gain != nullptr) {
@@ -105,39 +111,59 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
     const uint32_t ring_s = smem_u32(s.ring);
     const uint2 *xtab = reinterpret_cast<const uint2 *>(s.xtab);
     // ldmatrix row address of this lane inside a stage: matrix (lane / 8) covers k + 8 * (lane / 8)
-    const uint32_t lane_off = (uint32_t)(lane & 7) * row_smem + (uint32_t)(lane >> 3) * 16;
+    // matrices 0..3 of ldmatrix.x4 = (k 0-7 | k 16-23 | k 8-15 | k 24-31) of the 32-wide step
+    const uint32_t lane_off = (uint32_t)(lane & 7) * row_smem + (uint32_t)(((lane >> 3) & 1) * 32 + (lane >> 4) * 16);
+    const int b_ofs = (lane >> 3) * 8 + ((lane >> 2) & 1) * 4 + (lane & 3);  // lanes 0..15: operand table entry
 
+    // (debug) per-stage stamps of warp 0 / CTA 0 for the gate/up phase of layer 1
+    const bool fine = c.ti >= 0 && bid == 0 && tid == 0 && (&job == p.jobs + 6);
+    int fi = 0;
     for (int blk0 = 0; blk0 < rr.nrows; blk0 += kRB) {
         const int blk_rows = min(kRB, rr.nrows - blk0);
         for (int grp = 0; grp < blk_rows / 8; ++grp) {
-            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            // 8 independent accumulators: mma.sync results have a long latency on sm_100, and a single
+            // accumulator chain per warp (6 dependent HMMAs per stage) was the bottleneck (profiles/)
+            float acc8[4][4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) acc8[a][0] = acc8[a][1] = acc8[a][2] = acc8[a][3] = 0.f;
             for (int pt = 0; pt < parts; ++pt, ++c.gs) {
-                const uint32_t slot = c.gs % kSlots, use = c.gs / kSlots;
+                const uint32_t slot = c.gs % (uint32_t)p.ring_slots, use = c.gs / (uint32_t)p.ring_slots;
                 mbar_wait(&s.full[slot], use & 1);
+                if (fine) {
+                    unsigned long long t;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                    if (fi < 255) p.trace[512 + 2 * fi] = t;
+                }
                 const uint32_t st_base = ring_s + slot * kSlotBytes + lane_off;
                 const int i16_base = (pt * kc) >> 4;
-#pragma unroll 4
-                for (int st = warp; st < steps32; st += kMW) {
-                    uint32_t b0, b1, b2, b3;
-                    ldsm_x4(st_base + (uint32_t)st * 64, b0, b1, b2, b3);
-                    uint2 a_lo = make_uint2(0u, 0u), a_hi = make_uint2(0u, 0u);
-                    if (lane < 8) {
-                        a_lo = xtab[(i16_base + 2 * st) * 8 + lane];
-                        a_hi = xtab[(i16_base + 2 * st + 1) * 8 + lane];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {  // steps32 <= 64 = 4 per warp
+                    const int st = warp + j * kMW;
+                    if (st < ((p.dbg & 1) ? 0 : steps32)) {
+                        uint32_t a0, a1, a2, a3;
+                        ldsm_x4(st_base + (uint32_t)st * 64, a0, a1, a2, a3);
+                        uint2 bx = make_uint2(0u, 0u);
+                        if (lane < 16) bx = xtab[(i16_base + 2 * st) * 8 + b_ofs];
+                        mma_bf16_16816(acc8[j], a0, a1, a2, a3, bx.x, bx.y);
                     }
-                    mma_bf16_16816(acc, a_lo.x, a_lo.y, b0, b1);
-                    mma_bf16_16816(acc, a_hi.x, a_hi.y, b2, b3);
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&s.empty[slot]);
+                if (fine) {
+                    unsigned long long t;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                    if (fi < 255) p.trace[512 + 2 * fi + 1] = t;
+                    ++fi;
+                }
             }
-            // D row 0 (hi) lives in lanes 0..3, row 1 (lo) in lanes 4..7: add them
-            const float v0 = acc[0] + __shfl_down_sync(0xffffffffu, acc[0], 4);
-            const float v1 = acc[1] + __shfl_down_sync(0xffffffffu, acc[1], 4);
-            if (lane < 4) {
-                s.part[(grp * 8 + 2 * lane) * kMW + warp] = v0;
-                s.part[(grp * 8 + 2 * lane + 1) * kMW + warp] = v1;
-            }
+            float d[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) d[e] = (acc8[0][e] + acc8[1][e]) + (acc8[2][e] + acc8[3][e]);
+            // lane (g, t): d[0], d[1] = D[g][2t], D[g][2t+1]; d[2], d[3] = D[8+g][2t], D[8+g][2t+1]
+            const int t4 = lane & 3;
+            float v = t4 == 0 ? d[0] + d[1] : (t4 == 1 ? d[2] + d[3] : 0.f);
+            v += __shfl_xor_sync(0xffffffffu, v, 1);
+            if (t4 == 0) s.part[(grp * 8 + (lane >> 2)) * kMW + warp] = v;
         }
         bar_sync(1, kMC);
         mega_trace(p, c.ti, bid, tid);  // ring consumed

@@ -20,7 +20,7 @@ __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_c
     __syncthreads();
 
     if (warp == kMW) {  // producer warp: streams weights for every phase of every step
-        if (lane == 0) mega_producer(p, s, G, bid);
+        mega_producer(p, s, G, bid, lane);  // whole warp: lanes 0..7 each issue one row copy per stage
         return;
     }
 

@@ -24,7 +24,7 @@ _lib.check(_lib.lib.b200llm_debug_read_trace(eng._h, out.ctypes.data_as(C.POINTE
 names = []
 for l in range(2):
     for ph in ("qkv", "attn", "o", "gu", "down"):
-        names += ([f"L{l}.{ph}.x", f"L{l}.{ph}.ring"] if ph != "attn" else []) + [f"L{l}.{ph}.done", f"L{l}.{ph}.bar"]
+        names += ([f"L{l}.{ph}.xld", f"L{l}.{ph}.xtab", f"L{l}.{ph}.x", f"L{l}.{ph}.ring"] if ph != "attn" else []) + [f"L{l}.{ph}.done", f"L{l}.{ph}.bar"]
 t0 = out[:1024].astype(np.int64)
 t1 = out[1024:].astype(np.int64)
 n = int((t0 > 0).sum())
@@ -40,3 +40,10 @@ for i, nm in enumerate(names):
         key = nm.split(".")[2]
         sums[key] = sums.get(key, 0.0) + d0
 print("layer-1 totals on CTA 0 by kind:", {k: round(v, 2) for k, v in sums.items()}, "sum", round(sum(sums.values()), 2))
+fine = out[512:1024].astype(np.int64).reshape(-1, 2)
+fine = fine[(fine[:, 0] > 0) & (fine[:, 1] > 0)]
+if len(fine) > 2:
+    wait = (fine[1:, 0] - fine[:-1, 1]) / 1e3      # arrive(i-1) -> data of stage i ready
+    comp = (fine[:, 1] - fine[:, 0]) / 1e3         # data ready -> stage released
+    print(f"L1.gu stages on CTA0/warp0: n={len(fine)} wait mean {wait.mean():.3f} us (max {wait.max():.3f}), "
+          f"compute mean {comp.mean():.3f} us (max {comp.max():.3f}); first 12 waits {np.round(wait[:12], 2)}")

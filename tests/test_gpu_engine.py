@@ -66,12 +66,13 @@ def test_live_oracle_parity(name, use_graphs, use_pdl, mega, golden_dir):
     eng.close()
 
 
-def test_teacher_forced_logits_every_step(golden_dir):
+@pytest.mark.parametrize("mega", [False, True])
+def test_teacher_forced_logits_every_step(mega, golden_dir):
     """Per-step logits along the golden token path (b200llm_set_lane forces the input token)."""
     g = np.load(os.path.join(golden_dir, "small.npz"))
     geo = lo.GEOMETRIES["small"]
     sd = lo.make_weights(geo, int(g["seed"]), sigma=float(g["sigma"]), embed_sigma=float(g["embed_sigma"]))
-    eng = _engine("small", sd, max_lanes=1, max_ctx=256, max_rows=8)
+    eng = _engine("small", sd, max_lanes=1, max_ctx=256, max_rows=8, use_megakernel=mega)
     lane = eng.open_lane()
     prompt, toks, probe = g["prompt"], g["tokens"], g["probe_ids"]
     eng.prefill(lane, prompt)
@@ -116,12 +117,14 @@ def test_chunked_prefill_ragged_and_batched_decode(golden_dir):
     eng.close()
 
 
+@pytest.mark.parametrize("mega", [False, True])
 @pytest.mark.parametrize("fname,name", [("llama3.2_1b", "llama3.2:1b"), ("llama3.2", "llama3.2")])
-def test_golden_parity_full_size(fname, name, golden_dir):
+def test_golden_parity_full_size(fname, name, mega, golden_dir):
     """BASELINE.json configs 1/2 geometries against the committed golden vectors (oracle run
     in the CPU container); weights come from the device twin of the seeded stream."""
     g = np.load(os.path.join(golden_dir, fname + ".npz"))
-    eng = _engine(name, None, seed=int(g["seed"]), sigma=float(g["sigma"]), max_lanes=1, max_ctx=512, max_rows=64)
+    eng = _engine(name, None, seed=int(g["seed"]), sigma=float(g["sigma"]), max_lanes=1, max_ctx=512, max_rows=64,
+                  use_megakernel=mega)
     lane = eng.open_lane()
     prompt, toks, probe = g["prompt"], g["tokens"].tolist(), g["probe_ids"]
     eng.prefill(lane, prompt)

@@ -112,11 +112,14 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
         const uint8_t *ks = tiles + (size_t)st * 2 * TILE;
         const uint8_t *vs = ks + TILE;
         const int t0 = (my_first + i * kAttnWarps) * kPT;
+        // Page-at-a-time softmax: all 16 scores first (independent work, the shuffles pipeline),
+        // one running-max update and one rescale per page, then the P.V accumulation.  (A
+        // token-at-a-time online softmax serialises ~50 dependent instructions per token.)
+        float sc[kPT / 4][G];
 #pragma unroll
         for (int it = 0; it < kPT / 4; ++it) {
             const int t = it * 4 + tg;
-            const bool ok = (t0 + t) <= pos;
-            float ka[EL], kb[EL], va[EL], vb[EL];
+            float ka[EL], kb[EL];
             if constexpr (EL == 8) {
                 const uint4 A = *reinterpret_cast<const uint4 *>(ks + (size_t)t * HD * 2 + p8 * 16);
                 const uint4 B = *reinterpret_cast<const uint4 *>(ks + (size_t)t * HD * 2 + HD + p8 * 16);
@@ -126,6 +129,47 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
                     ka[2 * e] = bf16lo(aw[e]), ka[2 * e + 1] = bf16hi(aw[e]);
                     kb[2 * e] = bf16lo(bw[e]), kb[2 * e + 1] = bf16hi(bw[e]);
                 }
+            } else {
+                const uint2 A = *reinterpret_cast<const uint2 *>(ks + (size_t)t * HD * 2 + p8 * 8);
+                const uint2 B = *reinterpret_cast<const uint2 *>(ks + (size_t)t * HD * 2 + HD + p8 * 8);
+                ka[0] = bf16lo(A.x), ka[1] = bf16hi(A.x), ka[2] = bf16lo(A.y), ka[3] = bf16hi(A.y);
+                kb[0] = bf16lo(B.x), kb[1] = bf16hi(B.x), kb[2] = bf16lo(B.y), kb[3] = bf16hi(B.y);
+            }
+            const bool ok = (t0 + t) <= pos;
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float s = 0.f;
+#pragma unroll
+                for (int e = 0; e < EL; ++e) s = fmaf(qa[g][e], ka[e], fmaf(qb[g][e], kb[e], s));
+                s += __shfl_xor_sync(0xffffffffu, s, 1);
+                s += __shfl_xor_sync(0xffffffffu, s, 2);
+                s += __shfl_xor_sync(0xffffffffu, s, 4);
+                sc[it][g] = ok ? s : -INFINITY;
+            }
+        }
+        float corr[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float mn = m[g];
+#pragma unroll
+            for (int it = 0; it < kPT / 4; ++it) mn = fmaxf(mn, sc[it][g]);
+            corr[g] = mn == -INFINITY ? 1.f : exp2f(m[g] - mn);
+            float ps = 0.f;
+#pragma unroll
+            for (int it = 0; it < kPT / 4; ++it) {
+                sc[it][g] = mn == -INFINITY ? 0.f : exp2f(sc[it][g] - mn);  // exp2(-inf) = 0 masks the tail
+                ps += sc[it][g];
+            }
+            l[g] = l[g] * corr[g] + ps;
+            m[g] = mn;
+#pragma unroll
+            for (int e = 0; e < EL; ++e) oa[g][e] *= corr[g], ob[g][e] *= corr[g];
+        }
+#pragma unroll
+        for (int it = 0; it < kPT / 4; ++it) {
+            const int t = it * 4 + tg;
+            float va[EL], vb[EL];
+            if constexpr (EL == 8) {
                 const uint4 C = *reinterpret_cast<const uint4 *>(vs + (size_t)t * HD * 2 + p8 * 16);
                 const uint4 D = *reinterpret_cast<const uint4 *>(vs + (size_t)t * HD * 2 + HD + p8 * 16);
                 const uint32_t cw[4] = {C.x, C.y, C.z, C.w}, dw[4] = {D.x, D.y, D.z, D.w};
@@ -135,10 +179,6 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
                     vb[2 * e] = bf16lo(dw[e]), vb[2 * e + 1] = bf16hi(dw[e]);
                 }
             } else {
-                const uint2 A = *reinterpret_cast<const uint2 *>(ks + (size_t)t * HD * 2 + p8 * 8);
-                const uint2 B = *reinterpret_cast<const uint2 *>(ks + (size_t)t * HD * 2 + HD + p8 * 8);
-                ka[0] = bf16lo(A.x), ka[1] = bf16hi(A.x), ka[2] = bf16lo(A.y), ka[3] = bf16hi(A.y);
-                kb[0] = bf16lo(B.x), kb[1] = bf16hi(B.x), kb[2] = bf16lo(B.y), kb[3] = bf16hi(B.y);
                 const uint2 C = *reinterpret_cast<const uint2 *>(vs + (size_t)t * HD * 2 + p8 * 8);
                 const uint2 D = *reinterpret_cast<const uint2 *>(vs + (size_t)t * HD * 2 + HD + p8 * 8);
                 va[0] = bf16lo(C.x), va[1] = bf16hi(C.x), va[2] = bf16lo(C.y), va[3] = bf16hi(C.y);
@@ -146,23 +186,10 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
             }
 #pragma unroll
             for (int g = 0; g < G; ++g) {
-                float s = 0.f;
 #pragma unroll
-                for (int e = 0; e < EL; ++e) s = fmaf(qa[g][e], ka[e], fmaf(qb[g][e], kb[e], s));
-                s += __shfl_xor_sync(0xffffffffu, s, 1);
-                s += __shfl_xor_sync(0xffffffffu, s, 2);
-                s += __shfl_xor_sync(0xffffffffu, s, 4);
-                if (ok) {
-                    const float mn = fmaxf(m[g], s);
-                    const float corr = exp2f(m[g] - mn);
-                    const float pr = exp2f(s - mn);
-                    l[g] = l[g] * corr + pr;
-#pragma unroll
-                    for (int e = 0; e < EL; ++e) {
-                        oa[g][e] = fmaf(pr, va[e], oa[g][e] * corr);
-                        ob[g][e] = fmaf(pr, vb[e], ob[g][e] * corr);
-                    }
-                    m[g] = mn;
+                for (int e = 0; e < EL; ++e) {
+                    oa[g][e] = fmaf(sc[it][g], va[e], oa[g][e]);
+                    ob[g][e] = fmaf(sc[it][g], vb[e], ob[g][e]);
                 }
             }
         }

@@ -33,9 +33,11 @@ constexpr int kSlotBytes = 33792;              // >= 8 * (kMaxKC * 2 + 16), mult
 constexpr int kSlots = 5;
 constexpr int kXtabBytes = 45056;              // activation operand table: K * 4 bytes (K <= 11264)
 constexpr int kAttW = 4;                       // warps that stream KV pages in the attention phase
-constexpr int kPartBytes = 9216;               // per-warp GEMV partials / attention merge buffer
+constexpr int kPartBytes = 8704;               // per-warp GEMV partials / attention merge buffer
 constexpr int kRB = 128;                       // rows combined per partial block
 constexpr int kMPT = 16;                       // tokens per KV page
+constexpr int kMaxJobs = 4 * 32 + 1;           // phase descriptors kept in shared memory (<= 32 layers)
+constexpr int kMaxPtab = 448;                  // page-table entries kept in shared memory
 
 struct MegaSmem {
     uint8_t *ring, *xtab;  // xtab doubles as the K/V tile buffer of the attention phase
@@ -44,6 +46,8 @@ struct MegaSmem {
     float *red;
     int *misc;
     float *rope;  // [head_dim/2][cos, sin] of the current position
+    MegaJob *jobs;    // copy of the phase descriptors (global reads after a gpu-scope acquire miss in L1)
+    int32_t *ptab;    // copy of the lane's page table (first kMaxPtab entries)
 };
 
 __device__ __forceinline__ MegaSmem carve(uint8_t *base) {
@@ -57,11 +61,14 @@ __device__ __forceinline__ MegaSmem carve(uint8_t *base) {
     s.red = reinterpret_cast<float *>(s.att_full + kAttW);
     s.misc = reinterpret_cast<int *>(s.red + 64);
     s.rope = reinterpret_cast<float *>(s.misc + 64);
+    s.jobs = reinterpret_cast<MegaJob *>(s.rope + 128);
+    s.ptab = reinterpret_cast<int32_t *>(s.jobs + kMaxJobs);
     return s;
 }
 
 size_t mega_smem_bytes(int) {
-    return (size_t)kSlots * kSlotBytes + kXtabBytes + kPartBytes + (2 * kSlots + kAttW) * 8 + 64 * 4 + 256 + 128 * 4;
+    return (size_t)kSlots * kSlotBytes + kXtabBytes + kPartBytes + (2 * kSlots + kAttW) * 8 + 64 * 4 + 256 + 128 * 4 + kMaxJobs * sizeof(MegaJob) +
+           kMaxPtab * 4;
 }
 
 __host__ __device__ __forceinline__ int k_parts(int K) {
@@ -111,9 +118,12 @@ __device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int
     const uint64_t pol = l2_policy_evict_first();
     const int n_jobs = 4 * p.n_layers + 1;
     uint32_t gs = 0;
+    int seq = 0;  // phases started so far (all steps)
+    volatile int *gate = s.misc + 2;
     for (int step = 0; step < p.n_steps; ++step) {
-        for (int j = 0; j < n_jobs; ++j) {
-            const MegaJob job = p.jobs[j];
+        for (int j = 0; j < n_jobs; ++j, ++seq) {
+            const MegaJob job = s.jobs[j];
+            int ahead = 0;  // stages of this phase issued while its gate is still closed
             const RowRange rr = cta_rows(job.N, G, bid);
             const int parts = k_parts(job.K);
             const int kc = job.K / parts;
@@ -123,6 +133,16 @@ __device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int
             for (int grp = 0; grp < rr.nrows / 8; ++grp) {
                 for (int pt = 0; pt < parts; ++pt, ++gs) {
                     const uint32_t slot = gs % (uint32_t)p.ring_slots, use = gs / (uint32_t)p.ring_slots;
+                    // Deep prefetch inflates the latency of everything else that goes to memory (a demand
+                    // load queues behind ~120 KB per SM of bulk copies), and the consumers' barrier
+                    // + activation loads between two phases are pure latency: only `gap_slots`
+                    // stages of a phase may be in flight before its consumers have their activations.
+                    if (ahead >= p.gap_slots) {
+                        while (*gate <= seq) {
+                        }
+                    } else {
+                        ++ahead;
+                    }
                     if (use > 0) mbar_wait(&s.empty[slot], (use - 1) & 1);
                     if (lane == 0) mbar_expect_tx(&s.full[slot], 8u * (uint32_t)kc * 2u);
                     __syncwarp();
@@ -145,6 +165,7 @@ __device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int
 struct StepCtx {
     int tok, pos;
     int ti;               // trace cursor (-1: tracing off for this step)
+    int seq;              // GEMV phases started (gate value the producer waits for)
     uint32_t gs;          // ring stage counter, in lock-step with the producer
     float best;           // LOGITS: running (max, argmax) of this thread
     int best_i;
@@ -166,6 +187,7 @@ int mega_decode_launch(const MegaParams &p, cudaStream_t stream) {
     B200_REQUIRE(mega_supported(p.d, p.ffn, p.n_q, p.n_kv, p.head_dim), "mega: unsupported geometry");
     B200_REQUIRE(p.n_steps >= 1 && (p.sample || p.n_steps == 1), "mega: n_steps must be 1 when sampling is external");
     B200_REQUIRE(p.n_splits >= 1, "mega: n_splits < 1");
+    B200_REQUIRE(4 * p.n_layers + 1 <= kMaxJobs, "mega: more than 32 layers");
     const int GQ = p.n_q / p.n_kv;
 #define B200_MEGA_CASE(HD_, G_) \
     if (p.head_dim == HD_ && GQ == G_) return mega_launch_t<HD_, G_>(p, stream);

@@ -656,6 +656,7 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     p.embed = e->embed, p.inv_freq = e->inv_freq;
     p.lane = lane, p.lane_token = e->lane_token, p.lane_pos = e->lane_pos, p.lane_hist = e->lane_hist;
     p.page_table = e->page_table + (size_t)lane * c.max_pages_per_lane;
+    p.n_ptab = c.max_pages_per_lane;
     p.gen_out = e->gen_out, p.n_steps = n_steps;
     int ns = kNumSMs / c.n_kv;
     ns = ns < 1 ? 1 : (ns > e->attn_splits ? e->attn_splits : ns);
@@ -667,6 +668,8 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
     p.ring_slots = 5;
+    p.gap_slots = 2;
+    if (const char *gp = getenv("B200LLM_MEGA_GAP")) p.gap_slots = atoi(gp);
     if (const char *dbg = getenv("B200LLM_MEGA_DBG")) p.dbg = atoi(dbg);
     if (const char *rs = getenv("B200LLM_MEGA_SLOTS")) {
         int v = atoi(rs);

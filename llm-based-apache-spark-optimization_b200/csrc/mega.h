@@ -33,6 +33,7 @@ struct MegaParams {
     int32_t lane;
     int32_t *lane_token, *lane_pos, *lane_hist;
     const int32_t *page_table;  // this lane's row
+    int32_t n_ptab;       // entries of it that are valid for this call
     int32_t *gen_out;     // [n_steps]
     int32_t n_steps;
     // attention split partials
@@ -46,6 +47,7 @@ struct MegaParams {
     unsigned long long *trace;  // optional [2][1024] globaltimer stamps of CTA 0 and CTA G-1 (debug)
     int32_t trace_step;
     int32_t dbg;          // debug bits: 1 = consumer skips the MMAs, 2 = one bulk copy per stage (results invalid)
+    int32_t gap_slots;    // ring stages the producer may prefetch for a phase before its consumers hold their activations
     int32_t ring_slots;   // ring stages in use (<= 5); fewer = shallower prefetch (tuning knob)
 };
 

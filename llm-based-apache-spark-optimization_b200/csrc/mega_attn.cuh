@@ -10,8 +10,38 @@
 // Work items = (kv head, split); item i runs on CTA i % G.
 #pragma once
 
+__device__ __forceinline__ void prefetch_l2(const void *ptr) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
+}
+
+// Issued at the start of the qkv phase: pull the K/V pages this CTA's attention item(s) will
+// read into L2 while the qkv weights stream, so the attention phase sees L2 instead of HBM
+// latency (the pages were last touched a whole step ago and have been evicted since).
+template <int HD>
+__device__ __forceinline__ void mega_attn_prefetch(const MegaParams &p, const MegaJob &qkv_job, const MegaSmem &s,
+                                                   const StepCtx &c, int G, int bid, int tid) {
+    constexpr int LINES = kMPT * HD * 2 / 128;  // 128-byte lines per K (or V) page tile
+    const int n_pages = c.pos / kMPT + 1;
+    const int ns = min(p.n_splits, (n_pages + 2 * kMW - 1) / (2 * kMW));
+    const int pps = (n_pages + ns - 1) / ns;
+    const int n_items = p.n_kv * ns;
+    const uint8_t *kbase = reinterpret_cast<const uint8_t *>(qkv_job.k_pages);
+    const uint8_t *vbase = reinterpret_cast<const uint8_t *>(qkv_job.v_pages);
+    for (int item = bid; item < n_items; item += G) {
+        const int hk = item / ns, split = item % ns;
+        const int pg_begin = split * pps, pg_end = min(n_pages, pg_begin + pps);
+        for (int i = tid; i < (pg_end - pg_begin) * LINES; i += kMC) {
+            const int pg = pg_begin + i / LINES, line = i % LINES;
+            const int page = pg < kMaxPtab ? s.ptab[pg] : p.page_table[pg];
+            const size_t off = ((size_t)page * p.n_kv + hk) * (size_t)(kMPT * HD * 2) + (size_t)line * 128;
+            prefetch_l2(kbase + off);
+            prefetch_l2(vbase + off);
+        }
+    }
+}
+
 template <int HD, int GQ>
-__device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, const MegaSmem &s, const StepCtx &c,
+__device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, const MegaSmem &s, StepCtx &c,
                                 int G, int bid, int tid) {
     constexpr int EL = HD / 16;  // dims per lane: 16 lanes cover one K/V row
     const int warp = tid >> 5, lane = tid & 31;
@@ -41,50 +71,81 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
             for (int e = 0; e < EL; ++e) o[g][e] = 0.f;
             m[g] = -INFINITY, l[g] = 0.f;
         }
+        if (q[0][0] != 1.2345e30f) mega_trace(p, c.ti, bid, tid);  // (debug) q arrived
         for (int pg = pg_begin + warp; pg < pg_end; pg += kMW) {
-            const size_t tile = ((size_t)p.page_table[pg] * p.n_kv + hk) * (size_t)(kMPT * HD);
+            const int page = pg < kMaxPtab ? s.ptab[pg] : p.page_table[pg];
+            const size_t tile = ((size_t)page * p.n_kv + hk) * (size_t)(kMPT * HD);
             const uint16_t *kp = kbase + tile + p16 * EL;
             const uint16_t *vp = vbase + tile + p16 * EL;
-#pragma unroll 4
-            for (int it = 0; it < kMPT / 2; ++it) {
-                const int t = it * 2 + tg;
-                const bool ok = (pg * kMPT + t) <= c.pos;
-                float kf[EL], vf[EL];
-                if constexpr (EL == 8) {
-                    const uint4 A = __ldcg(reinterpret_cast<const uint4 *>(kp + (size_t)t * HD));
-                    const uint4 B = __ldcg(reinterpret_cast<const uint4 *>(vp + (size_t)t * HD));
-                    const uint32_t aw[4] = {A.x, A.y, A.z, A.w}, bw[4] = {B.x, B.y, B.z, B.w};
+            // two half-pages of 4 x 2 tokens: all loads of a half-page in flight together, its 8
+            // scores computed before one running-max update (page-at-a-time softmax, see attn.cu)
+#pragma unroll 1
+            for (int hb = 0; hb < 2; ++hb) {
+                uint4 kr[4], vr[4];
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        kf[2 * e] = bf16lo(aw[e]), kf[2 * e + 1] = bf16hi(aw[e]);
-                        vf[2 * e] = bf16lo(bw[e]), vf[2 * e + 1] = bf16hi(bw[e]);
+                for (int it = 0; it < 4; ++it) {
+                    const int t = hb * 8 + it * 2 + tg;
+                    if constexpr (EL == 8) {
+                        kr[it] = __ldcg(reinterpret_cast<const uint4 *>(kp + (size_t)t * HD));
+                        vr[it] = __ldcg(reinterpret_cast<const uint4 *>(vp + (size_t)t * HD));
+                    } else {
+                        const uint2 A = __ldcg(reinterpret_cast<const uint2 *>(kp + (size_t)t * HD));
+                        const uint2 B = __ldcg(reinterpret_cast<const uint2 *>(vp + (size_t)t * HD));
+                        kr[it] = make_uint4(A.x, A.y, 0u, 0u), vr[it] = make_uint4(B.x, B.y, 0u, 0u);
                     }
-                } else {
-                    const uint2 A = __ldcg(reinterpret_cast<const uint2 *>(kp + (size_t)t * HD));
-                    const uint2 B = __ldcg(reinterpret_cast<const uint2 *>(vp + (size_t)t * HD));
-                    kf[0] = bf16lo(A.x), kf[1] = bf16hi(A.x), kf[2] = bf16lo(A.y), kf[3] = bf16hi(A.y);
-                    vf[0] = bf16lo(B.x), vf[1] = bf16hi(B.x), vf[2] = bf16lo(B.y), vf[3] = bf16hi(B.y);
+                }
+                float sc[4][GQ];
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int t = hb * 8 + it * 2 + tg;
+                    const bool ok = (pg * kMPT + t) <= c.pos;
+                    const uint32_t kw[4] = {kr[it].x, kr[it].y, kr[it].z, kr[it].w};
+                    float kf[EL];
+#pragma unroll
+                    for (int e = 0; e < EL / 2; ++e) kf[2 * e] = bf16lo(kw[e]), kf[2 * e + 1] = bf16hi(kw[e]);
+#pragma unroll
+                    for (int g = 0; g < GQ; ++g) {
+                        float sv = 0.f;
+#pragma unroll
+                        for (int e = 0; e < EL; ++e) sv = fmaf(q[g][e], kf[e], sv);
+                        sv += __shfl_xor_sync(0xffffffffu, sv, 1);
+                        sv += __shfl_xor_sync(0xffffffffu, sv, 2);
+                        sv += __shfl_xor_sync(0xffffffffu, sv, 4);
+                        sv += __shfl_xor_sync(0xffffffffu, sv, 8);
+                        sc[it][g] = ok ? sv : -INFINITY;
+                    }
                 }
 #pragma unroll
                 for (int g = 0; g < GQ; ++g) {
-                    float sc = 0.f;
+                    float mn = m[g];
 #pragma unroll
-                    for (int e = 0; e < EL; ++e) sc = fmaf(q[g][e], kf[e], sc);
-                    sc += __shfl_xor_sync(0xffffffffu, sc, 1);
-                    sc += __shfl_xor_sync(0xffffffffu, sc, 2);
-                    sc += __shfl_xor_sync(0xffffffffu, sc, 4);
-                    sc += __shfl_xor_sync(0xffffffffu, sc, 8);
-                    if (ok) {
-                        const float mn = fmaxf(m[g], sc);
-                        const float corr = exp2f(m[g] - mn), pr = exp2f(sc - mn);
-                        l[g] = l[g] * corr + pr;
+                    for (int it = 0; it < 4; ++it) mn = fmaxf(mn, sc[it][g]);
+                    const float corr = mn == -INFINITY ? 1.f : exp2f(m[g] - mn);
+                    float ps = 0.f;
 #pragma unroll
-                        for (int e = 0; e < EL; ++e) o[g][e] = fmaf(pr, vf[e], o[g][e] * corr);
-                        m[g] = mn;
+                    for (int it = 0; it < 4; ++it) {
+                        sc[it][g] = mn == -INFINITY ? 0.f : exp2f(sc[it][g] - mn);
+                        ps += sc[it][g];
                     }
+                    l[g] = l[g] * corr + ps;
+                    m[g] = mn;
+#pragma unroll
+                    for (int e = 0; e < EL; ++e) o[g][e] *= corr;
+                }
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const uint32_t vw[4] = {vr[it].x, vr[it].y, vr[it].z, vr[it].w};
+                    float vf[EL];
+#pragma unroll
+                    for (int e = 0; e < EL / 2; ++e) vf[2 * e] = bf16lo(vw[e]), vf[2 * e + 1] = bf16hi(vw[e]);
+#pragma unroll
+                    for (int g = 0; g < GQ; ++g)
+#pragma unroll
+                        for (int e = 0; e < EL; ++e) o[g][e] = fmaf(sc[it][g], vf[e], o[g][e]);
                 }
             }
         }
+        if (l[0] != 1.2345e30f) mega_trace(p, c.ti, bid, tid);  // (debug) this warp's pages done
         // merge the two token streams of the warp (lanes 0..15 and 16..31)
 #pragma unroll
         for (int g = 0; g < GQ; ++g) {
@@ -111,6 +172,7 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
             }
         }
         bar_sync(1, kMC);
+        mega_trace(p, c.ti, bid, tid);  // (debug) all warps done
         // ---- CTA result = merge of the 16 warps; one thread per (q head, dim) ----
         if (tid < GQ * HD) {
             const int g = tid / HD, dd = tid % HD;

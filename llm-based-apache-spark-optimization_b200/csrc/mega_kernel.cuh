@@ -15,7 +15,15 @@ __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_c
             mbar_init(&s.empty[i], kMW);
         }
         for (int i = 0; i < kAttW; ++i) mbar_init(&s.att_full[i], 1);
+        s.misc[2] = 0;
         mbar_fence_init();
+    }
+    {   // phase descriptors and page table -> shared memory (read once)
+        const int nj = 4 * p.n_layers + 1;
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(p.jobs);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(s.jobs);
+        for (int i = tid; i < nj * (int)(sizeof(MegaJob) / 4); i += kMC + 32) dst[i] = src[i];
+        for (int i = tid; i < min(p.n_ptab, kMaxPtab); i += kMC + 32) s.ptab[i] = p.page_table[i];
     }
     __syncthreads();
 
@@ -26,6 +34,7 @@ __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_c
 
     StepCtx c;
     c.gs = 0;
+    c.seq = 0;
     c.tok = __ldcg(p.lane_token + p.lane);
     c.pos = __ldcg(p.lane_pos + p.lane);
     unsigned bar_no = 0;
@@ -42,7 +51,8 @@ __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_c
             s.rope[2 * tid] = cs, s.rope[2 * tid + 1] = sn;
         }
         for (int l = 0; l < p.n_layers; ++l) {
-            const MegaJob *jb = p.jobs + 4 * l;
+            const MegaJob *jb = s.jobs + 4 * l;
+            mega_attn_prefetch<HD>(p, jb[0], s, c, G, bid, tid);
             mega_gemv_phase(p, jb[0], s, c, G, bid, tid);  // rmsnorm + qkv + rope + kv append
             mega_trace(p, c.ti, bid, tid);
             grid_sync(p.bar_ctr, ++bar_no * G, tid);
@@ -66,7 +76,7 @@ __global__ void __launch_bounds__(kMC + 32, 1) mega_decode_kernel(const __grid_c
         }
         // ---- final norm + lm_head: logits, per-CTA (max, lowest argmax) ----
         c.best = -INFINITY, c.best_i = 0x7fffffff;
-        mega_gemv_phase(p, p.jobs[n_jobs - 1], s, c, G, bid, tid);
+        mega_gemv_phase(p, s.jobs[n_jobs - 1], s, c, G, bid, tid);
         {
             float m = c.best;
             int mi = c.best_i;

@@ -14,7 +14,7 @@ from b200llm import Engine, _lib, geometry, weights  # noqa: E402
 name = sys.argv[1] if len(sys.argv) > 1 else "llama3.2"
 ctx = int(sys.argv[2]) if len(sys.argv) > 2 else 296
 geo = geometry.resolve(name)
-eng = Engine(geo, weights.random_init(geo, 0xB200, 0), max_lanes=1, max_ctx=ctx + 64, max_rows=64)
+eng = Engine(geo, weights.random_init(geo, 0xB200, 0), max_lanes=1, max_ctx=ctx + 64, max_rows=64, use_megakernel=True)
 lane = eng.open_lane()
 eng.prefill(lane, np.arange(5, 5 + ctx, dtype=np.int32) % 1000)
 eng.decode([lane], 8)
@@ -24,7 +24,7 @@ _lib.check(_lib.lib.b200llm_debug_read_trace(eng._h, out.ctypes.data_as(C.POINTE
 names = []
 for l in range(2):
     for ph in ("qkv", "attn", "o", "gu", "down"):
-        names += ([f"L{l}.{ph}.xld", f"L{l}.{ph}.xtab", f"L{l}.{ph}.x", f"L{l}.{ph}.ring"] if ph != "attn" else []) + [f"L{l}.{ph}.done", f"L{l}.{ph}.bar"]
+        names += ([f"L{l}.{ph}.xld", f"L{l}.{ph}.xtab", f"L{l}.{ph}.x", f"L{l}.{ph}.ring"] if ph != "attn" else []) + ([f"L{l}.attn.q", f"L{l}.attn.kv", f"L{l}.attn.warps"] if ph == "attn" else []) + [f"L{l}.{ph}.done", f"L{l}.{ph}.bar"]
 t0 = out[:1024].astype(np.int64)
 t1 = out[1024:].astype(np.int64)
 n = int((t0 > 0).sum())

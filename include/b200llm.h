@@ -218,6 +218,26 @@ int b200llm_op_attn_decode(const b200llm_attn_args *a, void *stream);
 int b200llm_op_attn_scratch_bytes(int32_t bs, int32_t n_q, int32_t n_kv, int32_t head_dim,
                                   int32_t n_splits, size_t *bytes);
 
+/* The same attention launch for callers that cannot allocate device memory.  (This entry
+ * point has no counterpart in the reference; it exists for host programs of two kinds: those
+ * that handed the whole card to their own memory pool at start-up, where a later cudaMalloc
+ * simply fails, and those that call from a latency-critical thread, where the allocator lock
+ * and the device-wide synchronisation inside cudaMalloc/cudaFree are not acceptable.)
+ *
+ * `scratch` and `scratch_bytes` of the argument block are ignored: split partials and arrival
+ * tickets go to a 4 MiB buffer built into the library (every GPU that loads libb200llm.so
+ * holds it until the process exits).  Limits: bs * n_kv <= 1024 and
+ * bs * n_q * n_splits * (head_dim + 2) * 4 + 4096 <= 4 MiB (for example 8 rows x 32 heads x
+ * 16 splits x 128); anything larger is refused with B200LLM_ENOMEM and a message that names
+ * the sizes -- use b200llm_op_attn_decode with your own scratch then.
+ *
+ * No cudaMalloc, cudaFree or other allocating call is made.  The first call on a device looks
+ * up the buffer's device address (cudaGetSymbolAddress, with that device current); make that
+ * first call outside any stream capture.  Every call shares the one buffer and clears its
+ * ticket area on `stream` before launching, so calls that may overlap on the GPU (different
+ * streams, or different threads) race with each other: serialise them. */
+int b200llm_op_attn_decode_static(const b200llm_attn_args *a, void *stream);
+
 /* Sampler over fp32 logits [bs, vocab] (+ the LOGITS partials for greedy rows). */
 typedef struct b200llm_sample_args {
     const float *logits;     /* fp32 [bs, vocab]; may be modified (repeat penalty) */

@@ -97,6 +97,7 @@ SYMBOLS = {
     "b200llm_op_attn_decode": (C.c_int, [_P(AttnArgs), C.c_void_p]),
     "b200llm_op_attn_scratch_bytes": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                                 _P(C.c_size_t)]),
+    "b200llm_op_attn_decode_static": (C.c_int, [_P(AttnArgs), C.c_void_p]),
     "b200llm_op_sample": (C.c_int, [_P(SampleArgs), C.c_void_p]),
     "b200llm_op_fill_weights": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_float, C.c_float, C.c_void_p]),
 }

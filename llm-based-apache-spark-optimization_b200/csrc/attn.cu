@@ -10,6 +10,8 @@
 // Streams are merged by shuffles (warp), shared memory (CTA) and -- across splits --
 // through a global scratch buffer by the last CTA to arrive (atomic ticket), in fixed
 // split order, so results are deterministic.
+#include <mutex>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -333,4 +335,91 @@ int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl
     return B200LLM_EINVAL;
 }
 
+
+// ---------------------------------------------------------------- no-allocation variant
+//
+// b200llm_op_attn_decode_static: the same split-T decode attention for callers that cannot
+// hand us a scratch buffer because they cannot allocate one.  Two kinds of host program are in
+// that position: one that gave every byte of HBM to its own pool at start-up (a serving process
+// that reserves the whole card for weights and KV pages, so a late cudaMalloc fails), and one
+// that calls from a thread where cudaMalloc / cudaFree are off limits because both take the
+// allocator lock and synchronise the whole device (a latency-critical decode loop).
+//
+// The split partials and arrival tickets live in the array below instead.  It is part of the
+// library image: every GPU that loads libb200llm.so carries these 4 MiB until the process
+// exits, whether or not this entry point is ever called.
+constexpr size_t kStaticScratchBytes = 4u << 20;   // the stated maximum: tickets + partials must fit
+constexpr size_t kStaticTicketBytes = 4096;        // 1024 (row, kv head) tickets
+static __device__ __align__(256) unsigned char g_attn_static_scratch[kStaticScratchBytes];
+
+// In host code `g_attn_static_scratch` is only a handle for the runtime, not a device address.
+// The address a kernel can use comes from cudaGetSymbolAddress, asked for once per device with
+// that device current.
+static std::mutex g_static_mu;
+static void *g_static_ptr[64] = {nullptr};
+
+static int static_scratch_ptr(void **out) {
+    int dev = -1;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < 64, "attn static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (g_static_ptr[dev] == nullptr) {
+        void *ptr = nullptr;
+        B200_CUDA_OK(cudaGetSymbolAddress(&ptr, g_attn_static_scratch));
+        g_static_ptr[dev] = ptr;
+    }
+    *out = g_static_ptr[dev];
+    return B200LLM_OK;
+}
+
 }  // namespace b200
+
+extern "C" int b200llm_op_attn_decode_static(const b200llm_attn_args *a, void *stream) {
+    using namespace b200;
+    B200_REQUIRE(a && a->q && a->out && a->k_pages && a->v_pages && a->row_lane && a->row_pos && a->page_table,
+                 "op_attn_decode_static: NULL argument");
+    {
+        int n_dev = 0;
+        if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
+            set_error("no CUDA device: this library has no CPU fallback");
+            return B200LLM_ENODEV;
+        }
+    }
+    B200_REQUIRE(a->page_tokens == kPT, "attn static: page_tokens must be %d (got %d)", kPT, a->page_tokens);
+    B200_REQUIRE(a->n_kv > 0 && a->n_q % a->n_kv == 0, "attn static: n_q %d not a multiple of n_kv %d", a->n_q, a->n_kv);
+    B200_REQUIRE(a->bs >= 1 && a->n_splits >= 1 && a->n_splits <= 64, "attn static: bad bs/n_splits");
+    const size_t tickets = (size_t)a->bs * a->n_kv * 4;
+    const size_t part_o = (size_t)a->bs * a->n_q * a->n_splits * a->head_dim * 4;
+    const size_t part_ml = (size_t)a->bs * a->n_q * a->n_splits * 2 * 4;
+    if (tickets > kStaticTicketBytes || kStaticTicketBytes + part_o + part_ml > kStaticScratchBytes) {
+        set_error("attn static: bs %d x n_q %d x n_splits %d x head_dim %d needs %zu bytes of split scratch (and %zu of "
+                  "tickets); the built-in buffer holds %zu (tickets %zu). Use b200llm_op_attn_decode with your own "
+                  "scratch for larger launches.",
+                  a->bs, a->n_q, a->n_splits, a->head_dim, kStaticTicketBytes + part_o + part_ml, tickets,
+                  kStaticScratchBytes, kStaticTicketBytes);
+        return B200LLM_ENOMEM;
+    }
+    void *base = nullptr;
+    int rc = static_scratch_ptr(&base);   // first call on a device resolves the symbol address
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the buffer is shared by every call and keeps the last call's contents: the tickets must
+    // start at zero, whatever an earlier (possibly failed) launch left behind
+    B200_CUDA_OK(cudaMemsetAsync(base, 0, kStaticTicketBytes, st));
+    AttnDev d;
+    d.a = *a;
+    d.a.scratch = base, d.a.scratch_bytes = kStaticScratchBytes;
+    d.scale_log2 = (float)(1.4426950408889634 / sqrt((double)a->head_dim));
+    uint8_t *s = reinterpret_cast<uint8_t *>(base);
+    d.tickets = reinterpret_cast<unsigned *>(s);
+    d.part_o = reinterpret_cast<float *>(s + kStaticTicketBytes);
+    d.part_ml = d.part_o + (size_t)a->bs * a->n_q * a->n_splits * a->head_dim;
+    const int G = a->n_q / a->n_kv;
+#define B200_ATTN_CASE(HD_, G_) \
+    if (a->head_dim == HD_ && G == G_) return launch_attn<HD_, G_>(d, st, false);
+    B200_ATTN_CASE(128, 1) B200_ATTN_CASE(128, 2) B200_ATTN_CASE(128, 3) B200_ATTN_CASE(128, 4)
+    B200_ATTN_CASE(64, 1) B200_ATTN_CASE(64, 2) B200_ATTN_CASE(64, 4)
+#undef B200_ATTN_CASE
+    set_error("attn static: unsupported head_dim %d / group %d", a->head_dim, G);
+    return B200LLM_EINVAL;
+}

@@ -87,7 +87,17 @@ enum {
     B200LLM_W_O = 6,          /* [d, n_q/tp * head_dim]           per layer          */
     B200LLM_W_MLP_NORM = 7,   /* [d]                              per layer          */
     B200LLM_W_GATE_UP = 8,    /* [2 ffn/tp, d]  row 2i = gate_i, row 2i+1 = up_i     */
-    B200LLM_W_DOWN = 9        /* [d, ffn/tp]                      per layer          */
+    B200LLM_W_DOWN = 9,       /* [d, ffn/tp]                      per layer          */
+    /* Optional second copies for the persistent batch-1 kernel, "stage-major": the matrix cut into
+     * stages of 8 rows x kc columns (kc = K / parts, parts = smallest p >= ceil(K/2048) dividing
+     * K/32), stored [row group][part][8][kc + 8] so that one stage -- rows already skewed by 16
+     * bytes for conflict-free ldmatrix -- is one contiguous bulk copy.  rows/cols in the
+     * descriptor are the logical [N, K]. */
+    B200LLM_W_QKV_ST = 10,
+    B200LLM_W_O_ST = 11,
+    B200LLM_W_GATE_UP_ST = 12,
+    B200LLM_W_DOWN_ST = 13,
+    B200LLM_W_LM_HEAD_ST = 14
 };
 
 typedef struct b200llm_tensor_desc {

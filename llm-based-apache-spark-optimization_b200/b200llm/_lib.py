@@ -15,6 +15,7 @@ ABI_VERSION = 1
 OK, EINVAL, ENODEV, ECUDA, ESTATE, ENCCL, ENOMEM = 0, -1, -2, -3, -4, -5, -6
 
 W_EMBED, W_LM_HEAD, W_FINAL_NORM, W_INV_FREQ, W_ATTN_NORM, W_QKV, W_O, W_MLP_NORM, W_GATE_UP, W_DOWN = range(10)
+W_QKV_ST, W_O_ST, W_GATE_UP_ST, W_DOWN_ST, W_LM_HEAD_ST = range(10, 15)
 EPI_STORE, EPI_RESIDUAL, EPI_SWIGLU, EPI_QKV_ROPE, EPI_LOGITS = range(5)
 
 

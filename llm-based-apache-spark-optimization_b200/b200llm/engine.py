@@ -54,6 +54,9 @@ class Engine:
         if not torch.cuda.is_available():
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         self.geo, self.weights, self.device = geo, weights, device
+        if use_megakernel and tp_size == 1 and not any(k >= _lib.W_QKV_ST for k, _, _ in weights.tensors):
+            from .weights import add_stage_major
+            add_stage_major(weights)          # the persistent kernel streams its own stage-major copies
         self.max_lanes, self.max_rows = max_lanes, max_rows
         self.max_pages_per_lane = (max_ctx + PAGE_TOKENS - 1) // PAGE_TOKENS
         torch.cuda.set_device(device)

@@ -55,7 +55,10 @@ class PackedWeights:
     def descs(self):
         arr = (_lib.TensorDesc * len(self.tensors))()
         for i, (kind, layer, t) in enumerate(self.tensors):
-            rows, cols = (t.shape[0], t.shape[1]) if t.dim() == 2 else (1, t.shape[0])
+            if kind >= _lib.W_QKV_ST:          # stage-major copy: the descriptor carries the logical [N, K]
+                rows, cols = t.logical_shape
+            else:
+                rows, cols = (t.shape[0], t.shape[1]) if t.dim() == 2 else (1, t.shape[0])
             arr[i] = _lib.TensorDesc(kind, layer, t.data_ptr(), rows, cols)
         return arr
 
@@ -66,6 +69,37 @@ class PackedWeights:
                 seen.add(t.data_ptr())
                 total += t.numel() * t.element_size()
         return total
+
+
+def k_parts(K: int) -> int:
+    p = (K + 2047) // 2048
+    while (K // 32) % p:
+        p += 1
+    return p
+
+
+def stage_major(w: torch.Tensor) -> torch.Tensor:
+    """[N, K] -> [N/8, parts, 8, kc + 8]: the persistent kernel's ring stages, each contiguous and
+    with its rows already skewed by 16 bytes (see B200LLM_W_*_ST in include/b200llm.h)."""
+    N, K = w.shape
+    assert N % 8 == 0 and K % 32 == 0
+    parts = k_parts(K)
+    kc = K // parts
+    out = torch.zeros(N // 8, parts, 8, kc + 8, dtype=w.dtype, device=w.device)
+    out[..., :kc] = w.view(N // 8, 8, parts, kc).permute(0, 2, 1, 3)
+    out.logical_shape = (N, K)
+    return out
+
+
+_ST_KIND = {_lib.W_QKV: _lib.W_QKV_ST, _lib.W_O: _lib.W_O_ST, _lib.W_GATE_UP: _lib.W_GATE_UP_ST,
+            _lib.W_DOWN: _lib.W_DOWN_ST, _lib.W_LM_HEAD: _lib.W_LM_HEAD_ST}
+
+
+def add_stage_major(pw: "PackedWeights", start: int = 0) -> None:
+    """Append stage-major copies of the matrices pw.tensors[start:] (persistent-kernel layout)."""
+    for kind, layer, t in list(pw.tensors[start:]):
+        if kind in _ST_KIND and pw.tp_size == 1:
+            pw.tensors.append((_ST_KIND[kind], layer, stage_major(t)))
 
 
 def _pair_interleave(hd: int, device) -> torch.Tensor:
@@ -114,12 +148,15 @@ def pack_globals(geo: Geometry, sd: Dict[str, torch.Tensor], tp_rank: int, tp_si
     out.tensors.append((_lib.W_INV_FREQ, -1, inv_freq(geo).to(emb.device).contiguous()))
 
 
-def pack(geo: Geometry, sd: Dict[str, torch.Tensor], tp_rank: int = 0, tp_size: int = 1) -> PackedWeights:
+def pack(geo: Geometry, sd: Dict[str, torch.Tensor], tp_rank: int = 0, tp_size: int = 1,
+         stage_major_copies: bool = False) -> PackedWeights:
     """Full HF-named state dict (device tensors, bf16) -> packed weights of this rank."""
     out = PackedWeights(geo, tp_rank, tp_size)
     pack_globals(geo, sd, tp_rank, tp_size, out)
     for l in range(geo.n_layers):
         pack_layer(geo, l, sd, tp_rank, tp_size, out)
+    if stage_major_copies:
+        add_stage_major(out)
     return out
 
 
@@ -130,7 +167,7 @@ def _layer_shapes(geo: Geometry):
 
 
 def random_init(geo: Geometry, seed: int, device, tp_rank: int = 0, tp_size: int = 1, sigma: float = 0.02,
-                embed_sigma: float = 0.02, gain_sigma: float = 0.02) -> PackedWeights:
+                embed_sigma: float = 0.02, gain_sigma: float = 0.02, stage_major_copies: bool = False) -> PackedWeights:
     """Seeded random-init weights generated on the device, packed layer by layer (the
     un-packed copy of a layer is dropped before the next one is made)."""
     out = PackedWeights(geo, tp_rank, tp_size)
@@ -151,4 +188,6 @@ def random_init(geo: Geometry, seed: int, device, tp_rank: int = 0, tp_size: int
             else:
                 lsd[f"model.layers.{l}.{kind}.weight"] = fill((geo.d,), s, gain_sigma, 1.0, device)
         pack_layer(geo, l, lsd, tp_rank, tp_size, out)
+    if stage_major_copies:
+        add_stage_major(out)
     return out

@@ -105,10 +105,13 @@ __device__ __forceinline__ void grid_sync(unsigned *ctr, unsigned target, int ti
     bar_sync(1, kMC);
     if (tid == 0) {
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+        // poll relaxed and fence once: an acquire load per poll costs an L1 invalidate (CCTL.IVALL)
+        // per iteration, ~100 per barrier, which also throws out every warp's local-memory lines
         unsigned v;
         do {
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
         } while (v < target);
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     bar_sync(1, kMC);
 }
@@ -144,9 +147,16 @@ __device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int
                         ++ahead;
                     }
                     if (use > 0) mbar_wait(&s.empty[slot], (use - 1) & 1);
-                    if (lane == 0) mbar_expect_tx(&s.full[slot], 8u * (uint32_t)kc * 2u);
+                    if (lane == 0) mbar_expect_tx(&s.full[slot], job.staged ? 8u * row_smem : 8u * (uint32_t)kc * 2u);
                     __syncwarp();
                     uint8_t *dst = s.ring + (size_t)slot * kSlotBytes;
+                    if (job.staged) {
+                        const size_t stage_bytes = 8 * (size_t)row_smem;
+                        const uint8_t *g1 = reinterpret_cast<const uint8_t *>(job.w) +
+                                            ((size_t)(rr.row0 / 8 + grp) * parts + pt) * stage_bytes;
+                        if (lane == 0) tma_load_1d_hint(dst, g1, (uint32_t)stage_bytes, &s.full[slot], pol);
+                        continue;
+                    }
                     const uint8_t *g0 = src + (size_t)grp * 8 * row_bytes + (size_t)pt * kc * 2;
                     if (p.dbg & 2) {
                         if (lane == 0) tma_load_1d_hint(dst, g0, 8u * (uint32_t)kc * 2u, &s.full[slot], pol);

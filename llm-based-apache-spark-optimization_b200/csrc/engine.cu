@@ -93,6 +93,7 @@ constexpr int kMaxDecodeSteps = 4096;
 struct LayerW {
     const void *attn_norm = nullptr, *wqkv = nullptr, *wo = nullptr, *mlp_norm = nullptr, *wgu = nullptr,
                *wdown = nullptr;
+    const void *wqkv_st = nullptr, *wo_st = nullptr, *wgu_st = nullptr, *wdown_st = nullptr;  // stage-major copies
 };
 
 struct b200llm_engine {
@@ -102,7 +103,7 @@ struct b200llm_engine {
     bool own_stream = false;
     bool pdl = false;
     // weights
-    const void *embed = nullptr, *lm_head = nullptr, *final_norm = nullptr;
+    const void *embed = nullptr, *lm_head = nullptr, *final_norm = nullptr, *lm_head_st = nullptr;
     const float *inv_freq = nullptr;
     std::vector<LayerW> layers;
     bool weights_bound = false;
@@ -369,7 +370,7 @@ int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, in
             return true;
         };
         const int64_t qkv_rows = (int64_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim;
-        if (t.kind >= B200LLM_W_ATTN_NORM) B200_REQUIRE(t.layer >= 0 && t.layer < c.n_layers, "tensor %d: bad layer", i);
+        if (t.kind >= B200LLM_W_ATTN_NORM && t.kind != B200LLM_W_LM_HEAD_ST) B200_REQUIRE(t.layer >= 0 && t.layer < c.n_layers, "tensor %d: bad layer", i);
         switch (t.kind) {
             case B200LLM_W_EMBED: if (!shape(c.vocab, c.d)) return B200LLM_EINVAL; e->embed = t.dev; break;
             case B200LLM_W_LM_HEAD: if (!shape(e->vocab_l, c.d)) return B200LLM_EINVAL; e->lm_head = t.dev; break;
@@ -381,6 +382,11 @@ int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, in
             case B200LLM_W_MLP_NORM: if (!shape(1, c.d)) return B200LLM_EINVAL; e->layers[t.layer].mlp_norm = t.dev; break;
             case B200LLM_W_GATE_UP: if (!shape(2 * (int64_t)e->ffn_l, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wgu = t.dev; break;
             case B200LLM_W_DOWN: if (!shape(c.d, e->ffn_l)) return B200LLM_EINVAL; e->layers[t.layer].wdown = t.dev; break;
+            case B200LLM_W_QKV_ST: if (!shape(qkv_rows, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wqkv_st = t.dev; break;
+            case B200LLM_W_O_ST: if (!shape(c.d, (int64_t)e->nq_l * c.head_dim)) return B200LLM_EINVAL; e->layers[t.layer].wo_st = t.dev; break;
+            case B200LLM_W_GATE_UP_ST: if (!shape(2 * (int64_t)e->ffn_l, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wgu_st = t.dev; break;
+            case B200LLM_W_DOWN_ST: if (!shape(c.d, e->ffn_l)) return B200LLM_EINVAL; e->layers[t.layer].wdown_st = t.dev; break;
+            case B200LLM_W_LM_HEAD_ST: if (!shape(e->vocab_l, c.d)) return B200LLM_EINVAL; e->lm_head_st = t.dev; break;
             default: set_error("tensor %d: unknown kind %d", i, t.kind); return B200LLM_EINVAL;
         }
     }
@@ -625,17 +631,21 @@ static int mega_prepare(b200llm_engine *e) {
     const b200llm_config &c = e->cfg;
     std::vector<MegaJob> jobs(4 * c.n_layers + 1);
     const int qd = c.n_q * c.head_dim;
+    bool staged = e->lm_head_st != nullptr;
+    for (auto &w : e->layers) staged = staged && w.wqkv_st && w.wo_st && w.wgu_st && w.wdown_st;
+    const int st = staged ? 1 : 0;
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW &w = e->layers[l];
         uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
-        jobs[4 * l + 0] = MegaJob{w.wqkv, w.attn_norm, kl, kl + e->kv_half_stride, (c.n_q + 2 * c.n_kv) * c.head_dim,
-                                  c.d, B200LLM_EPI_QKV_ROPE, l == 0 ? MEGA_X_EMBED : MEGA_X_H};
-        jobs[4 * l + 1] = MegaJob{w.wo, nullptr, nullptr, nullptr, c.d, qd, B200LLM_EPI_RESIDUAL, MEGA_X_ATT};
-        jobs[4 * l + 2] = MegaJob{w.wgu, w.mlp_norm, nullptr, nullptr, 2 * c.ffn, c.d, B200LLM_EPI_SWIGLU, MEGA_X_H};
-        jobs[4 * l + 3] = MegaJob{w.wdown, nullptr, nullptr, nullptr, c.d, c.ffn, B200LLM_EPI_RESIDUAL, MEGA_X_ACT};
+        jobs[4 * l + 0] = MegaJob{st ? w.wqkv_st : w.wqkv, w.attn_norm, kl, kl + e->kv_half_stride,
+                                  (c.n_q + 2 * c.n_kv) * c.head_dim, c.d, B200LLM_EPI_QKV_ROPE,
+                                  l == 0 ? MEGA_X_EMBED : MEGA_X_H, st, 0};
+        jobs[4 * l + 1] = MegaJob{st ? w.wo_st : w.wo, nullptr, nullptr, nullptr, c.d, qd, B200LLM_EPI_RESIDUAL, MEGA_X_ATT, st, 0};
+        jobs[4 * l + 2] = MegaJob{st ? w.wgu_st : w.wgu, w.mlp_norm, nullptr, nullptr, 2 * c.ffn, c.d, B200LLM_EPI_SWIGLU, MEGA_X_H, st, 0};
+        jobs[4 * l + 3] = MegaJob{st ? w.wdown_st : w.wdown, nullptr, nullptr, nullptr, c.d, c.ffn, B200LLM_EPI_RESIDUAL, MEGA_X_ACT, st, 0};
     }
-    jobs[4 * c.n_layers] = MegaJob{e->lm_head, e->final_norm, nullptr, nullptr, c.vocab, c.d, B200LLM_EPI_LOGITS,
-                                   MEGA_X_H};
+    jobs[4 * c.n_layers] = MegaJob{st ? e->lm_head_st : e->lm_head, e->final_norm, nullptr, nullptr, c.vocab, c.d,
+                                   B200LLM_EPI_LOGITS, MEGA_X_H, st, 0};
     B200_CUDA_OK(cudaMemcpyAsync(e->mega_jobs, jobs.data(), jobs.size() * sizeof(MegaJob), cudaMemcpyHostToDevice,
                                  e->stream));
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));  // `jobs` is a pageable temporary

@@ -81,17 +81,15 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
             // scores computed before one running-max update (page-at-a-time softmax, see attn.cu)
 #pragma unroll 1
             for (int hb = 0; hb < 2; ++hb) {
-                uint4 kr[4], vr[4];
+                uint4 kr[4];
 #pragma unroll
                 for (int it = 0; it < 4; ++it) {
                     const int t = hb * 8 + it * 2 + tg;
                     if constexpr (EL == 8) {
                         kr[it] = __ldcg(reinterpret_cast<const uint4 *>(kp + (size_t)t * HD));
-                        vr[it] = __ldcg(reinterpret_cast<const uint4 *>(vp + (size_t)t * HD));
                     } else {
                         const uint2 A = __ldcg(reinterpret_cast<const uint2 *>(kp + (size_t)t * HD));
-                        const uint2 B = __ldcg(reinterpret_cast<const uint2 *>(vp + (size_t)t * HD));
-                        kr[it] = make_uint4(A.x, A.y, 0u, 0u), vr[it] = make_uint4(B.x, B.y, 0u, 0u);
+                        kr[it] = make_uint4(A.x, A.y, 0u, 0u);
                     }
                 }
                 float sc[4][GQ];
@@ -113,6 +111,18 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
                         sv += __shfl_xor_sync(0xffffffffu, sv, 4);
                         sv += __shfl_xor_sync(0xffffffffu, sv, 8);
                         sc[it][g] = ok ? sv : -INFINITY;
+                    }
+                }
+                // V rows of the same tokens: issued now, they arrive while the softmax bookkeeping runs
+                uint4 vr[4];
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int t = hb * 8 + it * 2 + tg;
+                    if constexpr (EL == 8) {
+                        vr[it] = __ldcg(reinterpret_cast<const uint4 *>(vp + (size_t)t * HD));
+                    } else {
+                        const uint2 B = __ldcg(reinterpret_cast<const uint2 *>(vp + (size_t)t * HD));
+                        vr[it] = make_uint4(B.x, B.y, 0u, 0u);
                     }
                 }
 #pragma unroll

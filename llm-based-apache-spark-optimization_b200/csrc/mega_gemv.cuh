@@ -60,90 +60,60 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint16_t *>(nj->gain) + tid * 64));
         }
     }
-    // ---- 1. issue every global load of the prologue, then compute ----
-    // item = (k16 block i, t): the four values x[16i+2t], x[16i+2t+1], x[16i+2t+8], x[16i+2t+9]
+    // ---- 1. activation vector -> operand table (single pass, nothing kept in registers) ----
+    // item = (k16 block i, t): the four values x[16i+2t], x[16i+2t+1], x[16i+2t+8], x[16i+2t+9].
+    // The RMSNorm scale is applied in the epilogue (see below), so each item can be converted and
+    // stored as soon as it arrives; register arrays here used to spill, and spills are expensive
+    // right after a grid barrier (the acquire polls invalidate L1, so every local-memory access
+    // is an L2 round trip).
     const int n_items = K / 4;
     const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
-    float xv[6][4];
-    uint32_t gv[6][2];
-    if (job.x_src == MEGA_X_EMBED) {
-        const uint16_t *e = reinterpret_cast<const uint16_t *>(p.embed) + (size_t)c.tok * p.d;
-#pragma unroll
-        for (int j = 0; j < 6; ++j) {
-            const int it = j * kMC + tid;
-            if (it < n_items) {
-                const int k = (it >> 2) * 16 + (it & 3) * 2;
-                const uint32_t u0 = *reinterpret_cast<const uint32_t *>(e + k);
-                const uint32_t u1 = *reinterpret_cast<const uint32_t *>(e + k + 8);
-                xv[j][0] = bf16lo(u0), xv[j][1] = bf16hi(u0), xv[j][2] = bf16lo(u1), xv[j][3] = bf16hi(u1);
-            }
-        }
-    } else {
-        const float *x = job.x_src == MEGA_X_H ? p.h : (job.x_src == MEGA_X_ATT ? p.att : p.act);
-#pragma unroll
-        for (int j = 0; j < 6; ++j) {
-            const int it = j * kMC + tid;
-            if (it < n_items) {
-                const int k = (it >> 2) * 16 + (it & 3) * 2;
-                const float2 v0 = __ldcg(reinterpret_cast<const float2 *>(x + k));
-                const float2 v1 = __ldcg(reinterpret_cast<const float2 *>(x + k + 8));
-                xv[j][0] = v0.x, xv[j][1] = v0.y, xv[j][2] = v1.x, xv[j][3] = v1.y;
-            }
-        }
-    }
-    if (gain != nullptr) {
-#pragma unroll
-        for (int j = 0; j < 6; ++j) {
-            const int it = j * kMC + tid;
-            if (it < n_items) {
-                const int k = (it >> 2) * 16 + (it & 3) * 2;
-                gv[j][0] = *reinterpret_cast<const uint32_t *>(gain + k);
-                gv[j][1] = *reinterpret_cast<const uint32_t *>(gain + k + 8);
-            }
-        }
-    }
+    const uint16_t *emb = reinterpret_cast<const uint16_t *>(p.embed) + (size_t)c.tok * p.d;
+    const float *xsrc = job.x_src == MEGA_X_H ? p.h : (job.x_src == MEGA_X_ATT ? p.att : p.act);
+    const bool from_embed = job.x_src == MEGA_X_EMBED;
     // residual stream values this thread's epilogue will add to (single-block phases only)
     float hres = 0.f;
     const bool res_pre = epi == B200LLM_EPI_RESIDUAL && rr.nrows <= kRB;
     if (res_pre && tid < rr.nrows) hres = __ldcg(p.h + rr.row0 + tid);
-
     float ss = 0.f;
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-        const int it = j * kMC + tid;
-        if (it < n_items) {
-            ss += xv[j][0] * xv[j][0] + xv[j][1] * xv[j][1] + xv[j][2] * xv[j][2] + xv[j][3] * xv[j][3];
-            if (job.x_src == MEGA_X_EMBED && (it % G) == bid) {  // residual stream h <- embedding row
-                const int k = (it >> 2) * 16 + (it & 3) * 2;
-                *reinterpret_cast<float2 *>(p.h + k) = make_float2(xv[j][0], xv[j][1]);
-                *reinterpret_cast<float2 *>(p.h + k + 8) = make_float2(xv[j][2], xv[j][3]);
+#pragma unroll 4
+    for (int it = tid; it < n_items; it += kMC) {
+        const int i16 = it >> 2, t = it & 3;
+        const int k = i16 * 16 + t * 2;
+        float v[4];
+        if (from_embed) {
+            const uint32_t u0 = *reinterpret_cast<const uint32_t *>(emb + k);
+            const uint32_t u1 = *reinterpret_cast<const uint32_t *>(emb + k + 8);
+            v[0] = bf16lo(u0), v[1] = bf16hi(u0), v[2] = bf16lo(u1), v[3] = bf16hi(u1);
+            if ((it % G) == bid) {  // residual stream h <- embedding row, each element written once
+                *reinterpret_cast<float2 *>(p.h + k) = make_float2(v[0], v[1]);
+                *reinterpret_cast<float2 *>(p.h + k + 8) = make_float2(v[2], v[3]);
             }
+        } else {
+            const float2 v0 = __ldcg(reinterpret_cast<const float2 *>(xsrc + k));
+            const float2 v1 = __ldcg(reinterpret_cast<const float2 *>(xsrc + k + 8));
+            v[0] = v0.x, v[1] = v0.y, v[2] = v1.x, v[3] = v1.y;
         }
+        ss += v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
+        if (gain != nullptr) {
+            const uint32_t g0 = *reinterpret_cast<const uint32_t *>(gain + k);
+            const uint32_t g1 = *reinterpret_cast<const uint32_t *>(gain + k + 8);
+            v[0] *= bf16lo(g0), v[1] *= bf16hi(g0), v[2] *= bf16lo(g1), v[3] *= bf16hi(g1);
+        }
+        float hi[4], lo[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) hi[e] = bf16_round(v[e]), lo[e] = v[e] - hi[e];
+        uint2 *tab = reinterpret_cast<uint2 *>(s.xtab) + i16 * 8 + t;
+        tab[0] = make_uint2(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]));  // B column 2b   (hi)
+        tab[4] = make_uint2(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]));  // B column 2b+1 (lo)
     }
-    mega_trace(p, c.ti, bid, tid);  // (debug) this thread's x values have arrived
+    mega_trace(p, c.ti, bid, tid);  // (debug) this thread's x values have arrived and are converted
     // Fused RMSNorm prologue: the operand table holds gain * x; the scalar rsqrt(mean(x^2) + eps)
     // multiplies the result in the epilogue, so the block reduction of sum(x^2) is off the
     // critical path (it completes under the same barrier that publishes the table).
     if (gain != nullptr) {
         ss = warp_sum(ss);
         if (lane == 0) s.red[warp] = ss;
-    }
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-        const int it = j * kMC + tid;
-        if (it < n_items) {
-            const int i16 = it >> 2, t = it & 3;
-            float v[4] = {xv[j][0], xv[j][1], xv[j][2], xv[j][3]};
-            if (gain != nullptr) {
-                v[0] *= bf16lo(gv[j][0]), v[1] *= bf16hi(gv[j][0]), v[2] *= bf16lo(gv[j][1]), v[3] *= bf16hi(gv[j][1]);
-            }
-            float hi[4], lo[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) hi[e] = bf16_round(v[e]), lo[e] = v[e] - hi[e];
-            uint2 *tab = reinterpret_cast<uint2 *>(s.xtab) + i16 * 8 + t;
-            tab[0] = make_uint2(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]));  // B column 2b   (hi)
-            tab[4] = make_uint2(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]));  // B column 2b+1 (lo)
-        }
     }
     mega_trace(p, c.ti, bid, tid);  // (debug) this thread's table entries written
     bar_sync(1, kMC);

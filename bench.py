@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--pdl", action="store_true")
-    ap.add_argument("--mega", action="store_true", help="batch-1 greedy decode as one persistent kernel")
+    ap.add_argument("--no-mega", action="store_true", help="multi-kernel CUDA-graph path instead of the persistent kernel")
     ap.add_argument("--attn-splits", type=int, default=0)
     return ap.parse_args()
 
@@ -172,7 +172,7 @@ def run_b200(args):
     max_ctx = PROMPT_LEN + args.steps + args.warmup + E2E_NEW_TOKENS + 64
     eng = Engine(geo, w, device=local, max_lanes=bs + 1, max_ctx=max_ctx, max_rows=max(bs, 64),
                  use_graphs=not args.no_graphs, use_pdl=args.pdl, attn_splits=args.attn_splits,
-                 use_megakernel=args.mega)
+                 use_megakernel=not args.no_mega)
     # synthetic prompts: uniform ids, one stream per (rank, sequence)
     rng = np.random.default_rng(1000 * rank + 1)
     prompts = [rng.integers(0, min(geo.vocab, 128000), PROMPT_LEN, dtype=np.int32) for _ in range(bs)]
@@ -258,7 +258,7 @@ def run_b200(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload_name(args.model, bs), "parallelism": f"replicas x{world}",
                        "l2": "inputs larger than L2 (weights streamed every step)", "cuda_graph": not args.no_graphs,
-                       "pdl": args.pdl, "persistent_kernel": args.mega, "kv_cache": "bf16 paged (16-token pages)", "mean_ctx": mean_ctx},
+                       "pdl": args.pdl, "persistent_kernel": not args.no_mega, "kv_cache": "bf16 paged (16-token pages)", "mean_ctx": mean_ctx},
             "ttft_ms": ttft_ms,
             "clocks": clocks,
             "gpu_launches": int(launches),

@@ -50,7 +50,7 @@ class Engine:
     def __init__(self, geo: Geometry, weights: PackedWeights, device: int = 0, max_lanes: int = 8,
                  max_ctx: int = 4096, max_rows: int = 64, kv_pages: Optional[int] = None, tp_rank: int = 0,
                  tp_size: int = 1, nccl_id: Optional[bytes] = None, use_graphs: bool = True, use_pdl: bool = False,
-                 attn_splits: int = 0, use_megakernel: bool = False):
+                 attn_splits: int = 0, use_megakernel: bool = True):
         if not torch.cuda.is_available():
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         self.geo, self.weights, self.device = geo, weights, device

@@ -147,10 +147,10 @@ __device__ void mega_producer(const MegaParams &p, const MegaSmem &s, int G, int
                         ++ahead;
                     }
                     if (use > 0) mbar_wait(&s.empty[slot], (use - 1) & 1);
-                    if (lane == 0) mbar_expect_tx(&s.full[slot], job.staged ? 8u * row_smem : 8u * (uint32_t)kc * 2u);
+                    if (lane == 0) mbar_expect_tx(&s.full[slot], ((job.x_src >> 8) & 1) ? 8u * row_smem : 8u * (uint32_t)kc * 2u);
                     __syncwarp();
                     uint8_t *dst = s.ring + (size_t)slot * kSlotBytes;
-                    if (job.staged) {
+                    if (((job.x_src >> 8) & 1)) {
                         const size_t stage_bytes = 8 * (size_t)row_smem;
                         const uint8_t *g1 = reinterpret_cast<const uint8_t *>(job.w) +
                                             ((size_t)(rr.row0 / 8 + grp) * parts + pt) * stage_bytes;

@@ -639,13 +639,13 @@ static int mega_prepare(b200llm_engine *e) {
         uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
         jobs[4 * l + 0] = MegaJob{st ? w.wqkv_st : w.wqkv, w.attn_norm, kl, kl + e->kv_half_stride,
                                   (c.n_q + 2 * c.n_kv) * c.head_dim, c.d, B200LLM_EPI_QKV_ROPE,
-                                  l == 0 ? MEGA_X_EMBED : MEGA_X_H, st, 0};
-        jobs[4 * l + 1] = MegaJob{st ? w.wo_st : w.wo, nullptr, nullptr, nullptr, c.d, qd, B200LLM_EPI_RESIDUAL, MEGA_X_ATT, st, 0};
-        jobs[4 * l + 2] = MegaJob{st ? w.wgu_st : w.wgu, w.mlp_norm, nullptr, nullptr, 2 * c.ffn, c.d, B200LLM_EPI_SWIGLU, MEGA_X_H, st, 0};
-        jobs[4 * l + 3] = MegaJob{st ? w.wdown_st : w.wdown, nullptr, nullptr, nullptr, c.d, c.ffn, B200LLM_EPI_RESIDUAL, MEGA_X_ACT, st, 0};
+                                  (l == 0 ? MEGA_X_EMBED : MEGA_X_H) | (st << 8)};
+        jobs[4 * l + 1] = MegaJob{st ? w.wo_st : w.wo, nullptr, nullptr, nullptr, c.d, qd, B200LLM_EPI_RESIDUAL, MEGA_X_ATT | (st << 8)};
+        jobs[4 * l + 2] = MegaJob{st ? w.wgu_st : w.wgu, w.mlp_norm, nullptr, nullptr, 2 * c.ffn, c.d, B200LLM_EPI_SWIGLU, MEGA_X_H | (st << 8)};
+        jobs[4 * l + 3] = MegaJob{st ? w.wdown_st : w.wdown, nullptr, nullptr, nullptr, c.d, c.ffn, B200LLM_EPI_RESIDUAL, MEGA_X_ACT | (st << 8)};
     }
     jobs[4 * c.n_layers] = MegaJob{st ? e->lm_head_st : e->lm_head, e->final_norm, nullptr, nullptr, c.vocab, c.d,
-                                   B200LLM_EPI_LOGITS, MEGA_X_H, st, 0};
+                                   B200LLM_EPI_LOGITS, MEGA_X_H | (st << 8)};
     B200_CUDA_OK(cudaMemcpyAsync(e->mega_jobs, jobs.data(), jobs.size() * sizeof(MegaJob), cudaMemcpyHostToDevice,
                                  e->stream));
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));  // `jobs` is a pageable temporary
@@ -678,7 +678,7 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
     p.ring_slots = 5;
-    p.gap_slots = 2;
+    p.gap_slots = 1 << 30;  // gate off: measured best (profiles/); B200LLM_MEGA_GAP=n closes it after n stages
     if (const char *gp = getenv("B200LLM_MEGA_GAP")) p.gap_slots = atoi(gp);
     if (const char *dbg = getenv("B200LLM_MEGA_DBG")) p.dbg = atoi(dbg);
     if (const char *rs = getenv("B200LLM_MEGA_SLOTS")) {

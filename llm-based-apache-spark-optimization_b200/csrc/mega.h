@@ -13,9 +13,7 @@ struct MegaJob {
     void *v_pages;
     int32_t N, K;
     int32_t epi;          // B200LLM_EPI_*
-    int32_t x_src;        // MEGA_X_*
-    int32_t staged;       // 1: w is the stage-major copy (one bulk copy per stage)
-    int32_t pad_;
+    int32_t x_src;        // MEGA_X_* in the low byte; bit 8: w is the stage-major copy (one bulk copy per stage)
 };
 enum { MEGA_X_H = 0, MEGA_X_ATT = 1, MEGA_X_ACT = 2, MEGA_X_EMBED = 3 };
 

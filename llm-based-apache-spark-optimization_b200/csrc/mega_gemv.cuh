@@ -69,8 +69,9 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
     const int n_items = K / 4;
     const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
     const uint16_t *emb = reinterpret_cast<const uint16_t *>(p.embed) + (size_t)c.tok * p.d;
-    const float *xsrc = job.x_src == MEGA_X_H ? p.h : (job.x_src == MEGA_X_ATT ? p.att : p.act);
-    const bool from_embed = job.x_src == MEGA_X_EMBED;
+    const int x_kind = job.x_src & 0xff;
+    const float *xsrc = x_kind == MEGA_X_H ? p.h : (x_kind == MEGA_X_ATT ? p.att : p.act);
+    const bool from_embed = x_kind == MEGA_X_EMBED;
     // residual stream values this thread's epilogue will add to (single-block phases only)
     float hres = 0.f;
     const bool res_pre = epi == B200LLM_EPI_RESIDUAL && rr.nrows <= kRB;

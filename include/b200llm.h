@@ -70,6 +70,8 @@ typedef struct b200llm_config {
     int32_t use_pdl;            /* programmatic dependent launch between kernels */
     int32_t attn_splits;        /* split-T factor of decode attention, 0 = auto */
     int32_t use_megakernel;     /* batch-1 greedy decode as one persistent kernel */
+    int32_t use_tc;             /* passes of more than 4 rows (batches, prefill chunks) on the tcgen05 GEMM:
+                                   activations rounded to bf16 at every matmul input */
     void *stream;               /* cudaStream_t to run on; NULL = engine creates its own */
     const void *nccl_unique_id; /* 128-byte ncclUniqueId when tp_size > 1, else NULL */
 } b200llm_config;
@@ -247,6 +249,13 @@ int b200llm_op_attn_scratch_bytes(int32_t bs, int32_t n_q, int32_t n_kv, int32_t
  * ticket area on `stream` before launching, so calls that may overlap on the GPU (different
  * streams, or different threads) race with each other: serialise them. */
 int b200llm_op_attn_decode_static(const b200llm_attn_args *a, void *stream);
+
+/* tcgen05 tensor-core GEMM of the batch (> 4 rows) and prefill path:
+ *   out[t, n] (+)= sum_k x[t, k] * w[n, k],  w bf16 [N, K], x bf16 [T, K], out fp32 [T, out_stride].
+ * 1 <= T <= 256, N % 128 == 0, K % 64 == 0.  accumulate = 1 adds onto `out` (small matrices are
+ * split along K and meet in `out` with fp32 atomics); accumulate = 0 stores (whole K per CTA). */
+int b200llm_op_gemm_tc(const void *w, const void *x, float *out, int64_t out_stride, int32_t T, int32_t N, int32_t K,
+                       int32_t accumulate, void *stream);
 
 /* Sampler over fp32 logits [bs, vocab] (+ the LOGITS partials for greedy rows). */
 typedef struct b200llm_sample_args {

@@ -25,7 +25,7 @@ class Config(C.Structure):
                 ("rms_eps", C.c_float), ("page_tokens", C.c_int32), ("max_lanes", C.c_int32),
                 ("max_pages_per_lane", C.c_int32), ("max_rows", C.c_int32), ("tp_rank", C.c_int32),
                 ("tp_size", C.c_int32), ("device", C.c_int32), ("use_graphs", C.c_int32), ("use_pdl", C.c_int32),
-                ("attn_splits", C.c_int32), ("use_megakernel", C.c_int32), ("stream", C.c_void_p), ("nccl_unique_id", C.c_void_p)]
+                ("attn_splits", C.c_int32), ("use_megakernel", C.c_int32), ("use_tc", C.c_int32), ("stream", C.c_void_p), ("nccl_unique_id", C.c_void_p)]
 
 
 class TensorDesc(C.Structure):
@@ -99,6 +99,8 @@ SYMBOLS = {
     "b200llm_op_attn_scratch_bytes": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                                 _P(C.c_size_t)]),
     "b200llm_op_attn_decode_static": (C.c_int, [_P(AttnArgs), C.c_void_p]),
+    "b200llm_op_gemm_tc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                     C.c_int32, C.c_void_p]),
     "b200llm_op_sample": (C.c_int, [_P(SampleArgs), C.c_void_p]),
     "b200llm_op_fill_weights": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_float, C.c_float, C.c_void_p]),
 }

@@ -50,7 +50,7 @@ class Engine:
     def __init__(self, geo: Geometry, weights: PackedWeights, device: int = 0, max_lanes: int = 8,
                  max_ctx: int = 4096, max_rows: int = 64, kv_pages: Optional[int] = None, tp_rank: int = 0,
                  tp_size: int = 1, nccl_id: Optional[bytes] = None, use_graphs: bool = True, use_pdl: bool = False,
-                 attn_splits: int = 0, use_megakernel: bool = True):
+                 attn_splits: int = 0, use_megakernel: bool = True, use_tc: bool = True):
         if not torch.cuda.is_available():
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         self.geo, self.weights, self.device = geo, weights, device
@@ -64,7 +64,7 @@ class Engine:
         self._id_buf = C.create_string_buffer(nccl_id, 128) if nccl_id else None
         cfg = _lib.Config(_lib.ABI_VERSION, geo.d, geo.n_layers, geo.n_q, geo.n_kv, geo.head_dim, geo.ffn, geo.vocab,
                           geo.rms_eps, PAGE_TOKENS, max_lanes, self.max_pages_per_lane, max_rows, tp_rank, tp_size,
-                          device, int(use_graphs), int(use_pdl), attn_splits, int(use_megakernel), self.stream.cuda_stream,
+                          device, int(use_graphs), int(use_pdl), attn_splits, int(use_megakernel), int(use_tc), self.stream.cuda_stream,
                           C.cast(self._id_buf, C.c_void_p) if self._id_buf else None)
         self.cfg = cfg
         self._h = C.c_void_p()

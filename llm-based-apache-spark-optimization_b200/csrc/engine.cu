@@ -15,6 +15,7 @@
 #include <string.h>
 
 #include <map>
+#include <tuple>
 #include <mutex>
 #include <vector>
 
@@ -122,6 +123,11 @@ struct b200llm_engine {
     MegaJob *mega_jobs = nullptr;
     unsigned *bar_ctr = nullptr;
     unsigned long long *trace = nullptr;
+    // batch / prefill path
+    uint16_t *xb = nullptr;
+    float *qkv_out = nullptr, *gu_out = nullptr;
+    struct MapBox { alignas(128) unsigned char b[128]; };
+    std::map<std::tuple<const void *, int64_t, int64_t, int>, MapBox *> maps;
     bool mega_ready = false;
     std::vector<b200llm_sampling> samp_host;
     b200llm_sampling *lane_samp;
@@ -163,7 +169,7 @@ static int check_cfg(const b200llm_config *c) {
 struct WsLayout {
     size_t h, q, att, act, delta, logits, part_max, part_idx, row_lane, row_pos, row_token, pf_lane, pf_pos,
         pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
-        attn_scratch, mega_jobs, bar_ctr, trace, total;
+        attn_scratch, mega_jobs, bar_ctr, trace, xb, qkv_out, gu_out, total;
     size_t attn_scratch_bytes;
     int lm_grid, attn_splits;
 };
@@ -221,6 +227,13 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * sizeof(MegaJob));
     w->bar_ctr = take(256);
     w->trace = take(2048 * 8);
+    {   // batch / prefill path (tcgen05 GEMM): bf16 activations and fp32 GEMM outputs
+        size_t widest = c->d > (int)(nq_l * c->head_dim) ? c->d : nq_l * c->head_dim;
+        if (ffn_l > widest) widest = ffn_l;
+        w->xb = take(R * widest * 2);
+        w->qkv_out = take(R * (nq_l + 2 * nkv_l) * c->head_dim * 4);
+        w->gu_out = take(R * 2 * ffn_l * 4);
+    }
     w->total = o;
 }
 
@@ -348,6 +361,7 @@ int b200llm_destroy(b200llm_engine *e) {
     if (!e) return B200LLM_OK;
     cudaStreamSynchronize(e->stream);
     for (auto &kv : e->graphs) cudaGraphExecDestroy(kv.second);
+    for (auto &m : e->maps) delete m.second;
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(e->ev[i]);
     if (e->own_stream) cudaStreamDestroy(e->stream);
@@ -436,6 +450,7 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->mega_jobs = (MegaJob *)(b + w.mega_jobs);
     e->bar_ctr = (unsigned *)(b + w.bar_ctr);
     e->trace = (unsigned long long *)(b + w.trace);
+    e->xb = (uint16_t *)(b + w.xb), e->qkv_out = (float *)(b + w.qkv_out), e->gu_out = (float *)(b + w.gu_out);
     e->mega_ready = false;
     e->samp_host.assign(e->cfg.max_lanes, b200llm_sampling{0.f, 0, 1.f, 1.f, 0});
     // zero everything once: attention tickets must start at zero, lanes at token 0 / pos 0,
@@ -537,7 +552,7 @@ static int tp_allreduce_add(b200llm_engine *e, int rows) {
     return B200LLM_OK;
 }
 
-static int forward_pass(b200llm_engine *e, const PassRows &pr, bool advance) {
+static int forward_pass_gemv(b200llm_engine *e, const PassRows &pr, bool advance) {
     const b200llm_config &c = e->cfg;
     const int rows = pr.rows;
     const bool tp = c.tp_size > 1;
@@ -688,6 +703,111 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     e->last_rows = 1, e->last_logit_rows = 1;
     return mega_decode_launch(p, e->stream);
+}
+
+// ---------------------------------------------------------------- batch / prefill pass (tcgen05 GEMM)
+static int get_map(b200llm_engine *e, const void *base, int64_t rows, int64_t cols, int box, const void **out) {
+    auto key = std::make_tuple(base, rows, cols, box);
+    auto it = e->maps.find(key);
+    if (it == e->maps.end()) {
+        auto *m = new b200llm_engine::MapBox();
+        int rc = tc_make_map(m->b, base, rows, cols, box);
+        if (rc) {
+            delete m;
+            return rc;
+        }
+        it = e->maps.emplace(key, m).first;
+    }
+    *out = it->second->b;
+    return B200LLM_OK;
+}
+
+static bool tc_usable(const b200llm_engine *e, int rows) {
+    const b200llm_config &c = e->cfg;
+    auto okn = [](int n) { return n % 128 == 0; };
+    auto okk = [](int k) { return k % 64 == 0; };
+    return c.use_tc && c.tp_size == 1 && rows > 4 && rows <= 256 && okn((c.n_q + 2 * c.n_kv) * c.head_dim) && okn(c.d) &&
+           okn(2 * c.ffn) && okn(c.vocab) && okk(c.d) && okk(c.n_q * c.head_dim) && okk(c.ffn) &&
+           getenv("B200LLM_NO_TC") == nullptr;
+}
+
+// out (+)= X W^T through the tcgen05 kernel; X = e->xb viewed as [max_rows, K]
+static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, int64_t out_stride, int T,
+                   bool add_to_existing) {
+    const void *mw, *mx;
+    B200_TRY(get_map(e, w, N, K, 128, &mw));
+    B200_TRY(get_map(e, e->xb, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mx));
+    int accumulate = 1;
+    if (!add_to_existing) {
+        if (N / 128 >= kNumSMs) {
+            accumulate = 0;  // enough row tiles: no k split, plain stores
+        } else {
+            B200_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)T * out_stride * 4, e->stream));
+        }
+    }
+    B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, false));
+    e->launches++;
+    return B200LLM_OK;
+}
+
+static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) {
+    const b200llm_config &c = e->cfg;
+    const int rows = pr.rows;
+    cudaStream_t st = e->stream;
+    EmbedArgs ea{};
+    ea.embed = e->embed, ea.h = e->h, ea.row_token = pr.row_token, ea.row_pos = pr.row_pos, ea.row_lane = pr.row_lane;
+    ea.lane_token = e->lane_token, ea.lane_pos = e->lane_pos, ea.rows = rows, ea.d = c.d, ea.vocab = c.vocab;
+    ea.from_lanes = pr.from_lanes ? 1 : 0;
+    B200_TRY(embed_launch_ex(ea, e->lane_hist, pr.from_lanes ? e->step_ctr : nullptr, st, false));
+    e->launches++;
+    const int qd = c.n_q * c.head_dim, qkv_w = (c.n_q + 2 * c.n_kv) * c.head_dim;
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW &w = e->layers[l];
+        uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
+        uint8_t *vl = kl + e->kv_half_stride;
+        B200_TRY(rmsnorm_bf16_launch(e->h, w.attn_norm, e->xb, rows, c.d, c.rms_eps, st, false));
+        B200_TRY(tc_gemm(e, w.wqkv, qkv_w, c.d, e->qkv_out, qkv_w, rows, false));
+        B200_TRY(rope_append_launch(e->qkv_out, e->q, kl, vl, e->inv_freq, pr.row_lane, pr.row_pos, e->page_table, rows,
+                                    c.n_q, c.n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, false));
+        b200llm_attn_args at{};
+        at.q = e->q, at.out = e->att, at.k_pages = kl, at.v_pages = vl, at.row_lane = pr.row_lane, at.row_pos = pr.row_pos;
+        at.page_table = e->page_table, at.bs = rows, at.n_q = c.n_q, at.n_kv = c.n_kv, at.head_dim = c.head_dim;
+        at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane;
+        int want = (kNumSMs + rows * c.n_kv - 1) / (rows * c.n_kv);
+        if (want > 6) want = 6;
+        at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
+        at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
+        B200_TRY(attn_decode_launch(at, st, false));
+        B200_TRY(cast_bf16_launch(e->att, qd, e->xb, rows, qd, st, false));
+        B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->h, c.d, rows, true));
+        B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, false));
+        B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false));
+        B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, c.ffn, st, false));
+        B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true));
+        e->launches += 6;
+    }
+    e->last_rows = rows;
+    e->last_logit_rows = pr.logit_rows;
+    if (pr.logit_rows <= 0) return B200LLM_OK;
+    B200_TRY(rmsnorm_bf16_launch(e->h + (size_t)pr.logit_row0 * c.d, e->final_norm, e->xb, pr.logit_rows, c.d, c.rms_eps,
+                                 st, false));
+    B200_TRY(tc_gemm(e, e->lm_head, c.vocab, c.d, e->logits, c.vocab, pr.logit_rows, false));
+    SampleDev sd{};
+    sd.a.logits = e->logits, sd.a.bs = pr.logit_rows, sd.a.vocab = c.vocab;
+    sd.a.part_max = nullptr, sd.a.part_idx = nullptr, sd.a.n_part = 0;  // full-vocabulary argmax over the logits
+    sd.a.params = e->lane_samp, sd.a.out_token = nullptr;
+    sd.row_lane = pr.row_lane + pr.logit_row0;
+    sd.lane_token = e->lane_token, sd.lane_pos = e->lane_pos, sd.lane_hist = e->lane_hist;
+    sd.gen_out = pr.from_lanes ? e->gen_out : nullptr, sd.step_ctr = pr.from_lanes ? e->step_ctr : nullptr;
+    sd.advance = advance ? 1 : 0;
+    B200_TRY(sample_launch(sd, st, false));
+    e->launches += 2;
+    return B200LLM_OK;
+}
+
+static int forward_pass(b200llm_engine *e, const PassRows &pr, bool advance) {
+    if (tc_usable(e, pr.rows)) return forward_pass_tc(e, pr, advance);
+    return forward_pass_gemv(e, pr, advance);
 }
 
 extern "C" {
@@ -862,6 +982,17 @@ int b200llm_op_attn_scratch_bytes(int32_t bs, int32_t n_q, int32_t n_kv, int32_t
     B200_REQUIRE(bytes && bs >= 1 && n_q >= 1 && n_kv >= 1 && n_splits >= 1, "op_attn_scratch_bytes: bad arguments");
     *bytes = attn_scratch_bytes(bs, n_q, n_kv, head_dim, n_splits);
     return B200LLM_OK;
+}
+
+int b200llm_op_gemm_tc(const void *w, const void *x, float *out, int64_t out_stride, int32_t T, int32_t N, int32_t K,
+                       int32_t accumulate, void *stream) {
+    B200_REQUIRE(w && x && out, "op_gemm_tc: NULL argument");
+    int rc = require_device_any();
+    if (rc) return rc;
+    alignas(128) unsigned char mw[128], mx[128];
+    B200_TRY(tc_make_map(mw, w, N, K, 128));
+    B200_TRY(tc_make_map(mx, x, T, K, (T + 15) / 16 * 16));
+    return tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, (cudaStream_t)stream, false);
 }
 
 int b200llm_op_sample(const b200llm_sample_args *a, void *stream) {

@@ -1,0 +1,258 @@
+// gemm_tc.cu -- tcgen05 / TMEM weight-streaming GEMM for batches > 4 rows and for prefill
+// (kernel K9/K10 of SURVEY.md section 2.3):   out[t, n] (+)= sum_k X[t, k] * W[n, k]
+//
+// Swap-AB: the weight matrix feeds the M side of the MMA (128 weight rows per tile), the
+// tokens are the N side (16..256), so one CTA streams a [128 x K/splits] slab of W exactly
+// once while the small activation tile is re-read from L2.
+//   warp 0   : TMA producer   (cp.async.bulk.tensor.2d, 128B-swizzled [128 x 64] W tiles and
+//                              [BN x 64] X tiles into a multi-stage shared-memory ring)
+//   warp 1   : MMA issuer     (one thread: tcgen05.mma.cta_group::1.kind::f16, M=128, N=BN,
+//                              K=16, bf16 x bf16 -> fp32 in TMEM; tcgen05.commit frees stages)
+//   warp 2   : TMEM allocator
+//   warps 4-7: epilogue       (tcgen05.ld 32x32b of the warp's 32 accumulator lanes = weight
+//                              rows; registers = tokens; coalesced fp32 store / red.add)
+// grid = (N/128 row tiles, k_splits): small matrices are split along K so that ~all SMs stream
+// (decode at batch 64 is still HBM-bound); k-split partial sums meet in the output with fp32
+// red.global.add (the output is zeroed first, or already holds the residual stream).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+
+constexpr int kTcBM = 128;   // weight rows per tile (UMMA M)
+constexpr int kTcBK = 64;    // k per stage: 64 bf16 = one 128-byte swizzle row
+constexpr int kTcThreads = 256;
+
+struct TcParams {
+    float *out;          // fp32 [T, out_stride]
+    int64_t out_stride;
+    int32_t T;           // valid tokens (rows of X)
+    int32_t N, K;
+    int32_t bn;          // token tile = UMMA N (multiple of 16, >= T)
+    int32_t k_per_split; // multiple of 64
+    int32_t stages;
+    int32_t accumulate;  // 1: out += (red.add), 0: plain store (only valid with one k split)
+    int32_t tmem_cols;   // power of two >= max(32, bn)
+};
+
+__device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+// K-major operand tile in shared memory, 128-byte swizzle, rows of 128 bytes, 8-row groups 1024 B apart
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);          // start address
+    d |= (uint64_t)1 << 16;                               // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;                     // stride byte offset between 8-row groups
+    d |= (uint64_t)1 << 46;                               // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                               // SWIZZLE_128B
+    return d;
+}
+
+__device__ __forceinline__ uint32_t umma_idesc_bf16(int m, int n) {
+    return (1u << 4)      // D format f32
+           | (1u << 7)    // A format bf16
+           | (1u << 10)   // B format bf16
+           | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);   // both operands K-major
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
+               const __grid_constant__ TcParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int a_bytes = kTcBM * kTcBK * 2;          // 16 KB
+    const int b_bytes = p.bn * kTcBK * 2;           // multiple of 2 KB (bn % 16 == 0)
+    const int stage_bytes = a_bytes + ((b_bytes + 1023) & ~1023);
+    uint8_t *tiles = smem;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)p.stages * stage_bytes);
+    uint64_t *empty = full + p.stages;
+    uint64_t *tmem_full = empty + p.stages;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_full + 1);
+
+    const int row0 = blockIdx.x * kTcBM;
+    const int k0 = blockIdx.y * p.k_per_split;
+    const int n_k = min(p.k_per_split, p.K - k0) / kTcBK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(tmem_full, 1);
+        mbar_fence_init();
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)p.tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = *tmem_slot;
+    pdl_wait();  // X (and the residual in `out`) come from the previous kernel
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int i = 0; i < n_k; ++i) {
+                const int s = i % p.stages, use = i / p.stages;
+                if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
+                uint8_t *a_dst = tiles + (size_t)s * stage_bytes;
+                mbar_expect_tx(&full[s], (uint32_t)(a_bytes + b_bytes));
+                tma_load_2d(a_dst, &map_w, k0 + i * kTcBK, row0, &full[s]);
+                tma_load_2d(a_dst + a_bytes, &map_x, k0 + i * kTcBK, 0, &full[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16(kTcBM, p.bn);
+            for (int i = 0; i < n_k; ++i) {
+                const int s = i % p.stages, use = i / p.stages;
+                mbar_wait(&full[s], use & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a_addr = smem_u32(tiles + (size_t)s * stage_bytes);
+                const uint64_t adesc = umma_desc_sw128(a_addr);
+                const uint64_t bdesc = umma_desc_sw128(a_addr + a_bytes);
+#pragma unroll
+                for (int k = 0; k < kTcBK / 16; ++k) {
+                    const uint32_t accum = (i > 0 || k > 0) ? 1u : 0u;
+                    // advancing 16 k = 32 bytes inside the 128-byte swizzle row: +2 in the address field
+                    asm volatile(
+                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+                        "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc + (uint64_t)(2 * k)), "r"(idesc), "r"(accum)
+                        : "memory");
+                }
+                // frees the stage once the MMAs above have read it
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                 smem_u32(&empty[s]))
+                             : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                             smem_u32(tmem_full))
+                         : "memory");
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue: this warp owns accumulator lanes 32*(warp%4) .. +31 = 32 weight rows =====
+        mbar_wait(tmem_full, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int q = warp & 3;
+        const int n = row0 + q * 32 + lane;  // output column (weight row) of this thread
+        for (int c0 = 0; c0 < p.bn; c0 += 16) {
+            uint32_t v[16];
+            const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, "
+                "%14, %15}, [%16];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const int t = c0 + j;
+                if (t < p.T && n < p.N) {
+                    float *dst = p.out + (size_t)t * p.out_stride + n;
+                    if (p.accumulate)
+                        atomicAdd(dst, __uint_as_float(v[j]));
+                    else
+                        *dst = __uint_as_float(v[j]);
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == 2) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)p.tmem_cols)
+                     : "memory");
+    }
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+static int load_encode() {
+    if (g_encode) return B200LLM_OK;
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    B200_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (!fn || qres != cudaDriverEntryPointSuccess) {
+        set_error("cuTensorMapEncodeTiled is not available from the driver");
+        return B200LLM_ECUDA;
+    }
+    g_encode = (EncodeTiledFn)fn;
+    return B200LLM_OK;
+}
+
+// bf16 row-major [rows, cols] -> 2-D map with a [box_rows x 64] box, 128-byte swizzle, zero fill out of bounds
+int tc_make_map(void *map_out, const void *base, int64_t rows, int64_t cols, int box_rows) {
+    int rc = load_encode();
+    if (rc) return rc;
+    B200_REQUIRE(cols % 8 == 0 && ((uintptr_t)base % 16) == 0 && box_rows >= 1 && box_rows <= 256,
+                 "tensor map: bad shape/alignment");
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)cols * 2};
+    cuuint32_t box[2] = {(cuuint32_t)kTcBK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(reinterpret_cast<CUtensorMap *>(map_out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                          const_cast<void *>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with %d (rows %lld cols %lld box %d)", (int)r, (long long)rows,
+                  (long long)cols, box_rows);
+        return B200LLM_ECUDA;
+    }
+    return B200LLM_OK;
+}
+
+int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
+                   int accumulate, cudaStream_t stream, bool pdl) {
+    B200_REQUIRE(T >= 1 && T <= 256 && N % kTcBM == 0 && K % kTcBK == 0, "gemm_tc: need 1 <= T <= 256, N %% 128 == 0, K %% 64 == 0 (T %d N %d K %d)", T, N, K);
+    TcParams p{};
+    p.out = out, p.out_stride = out_stride, p.T = T, p.N = N, p.K = K;
+    p.bn = (T + 15) / 16 * 16;
+    const int tiles = N / kTcBM;
+    int ks = kNumSMs / tiles;
+    const int k_iters = K / kTcBK;
+    if (ks < 1) ks = 1;
+    if (ks > k_iters) ks = k_iters;
+    if (!accumulate) ks = 1;  // a plain store needs the whole K in one CTA
+    const int it_per = (k_iters + ks - 1) / ks;
+    ks = (k_iters + it_per - 1) / it_per;
+    p.k_per_split = it_per * kTcBK;
+    p.accumulate = accumulate;
+    int cols = 32;
+    while (cols < p.bn) cols <<= 1;
+    p.tmem_cols = cols;
+    const int stage_bytes = kTcBM * kTcBK * 2 + ((p.bn * kTcBK * 2 + 1023) & ~1023);
+    int stages = (200 * 1024) / stage_bytes;
+    p.stages = stages > 8 ? 8 : (stages < 2 ? 2 : stages);
+    const size_t smem = (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16 + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set = true;
+    }
+    LaunchCfg lc(dim3(tiles, ks), dim3(kTcThreads), smem, stream, pdl);
+    B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, gemm_tc_kernel, *reinterpret_cast<const CUtensorMap *>(map_w),
+                                    *reinterpret_cast<const CUtensorMap *>(map_x), p));
+    return B200LLM_OK;
+}
+
+}  // namespace b200

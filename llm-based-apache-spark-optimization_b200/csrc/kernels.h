@@ -52,6 +52,18 @@ struct SampleDev {
 };
 int sample_launch(const SampleDev &a, cudaStream_t stream, bool pdl);
 
+// gemm_tc.cu: tcgen05 GEMM  out[t, n] (+)= sum_k X[t, k] W[n, k]  (bf16 in, fp32 out), T <= 256
+int tc_make_map(void *map_out_128B, const void *base, int64_t rows, int64_t cols, int box_rows);
+int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
+                   int accumulate, cudaStream_t stream, bool pdl);
+// batch_ops.cu
+int rmsnorm_bf16_launch(const float *x, const void *gain, void *out, int rows, int d, float eps, cudaStream_t s, bool pdl);
+int cast_bf16_launch(const float *x, int64_t in_stride, void *out, int rows, int n, cudaStream_t s, bool pdl);
+int swiglu_bf16_launch(const float *gu, void *out, int rows, int ffn, cudaStream_t s, bool pdl);
+int rope_append_launch(const float *qkv, float *q, void *k_pages, void *v_pages, const float *inv_freq,
+                       const int32_t *row_lane, const int32_t *row_pos, const int32_t *page_table, int rows, int n_q,
+                       int n_kv, int hd, int page_tokens, int max_pages, cudaStream_t s, bool pdl);
+
 int fill_weights_launch(void *dev_bf16, uint64_t n, uint64_t seed, float sigma, float mean, cudaStream_t s);
 int add_inplace_launch(float *dst, const float *src, size_t n, cudaStream_t s, bool pdl);
 

@@ -32,13 +32,13 @@ def test_struct_sizes_match_header():
     assert C.sizeof(_lib.Sampling) == 24
     assert C.sizeof(_lib.TensorDesc) == 32
     assert C.sizeof(_lib.Timing) == 24
-    assert C.sizeof(_lib.Config) == 96
+    assert C.sizeof(_lib.Config) == 104
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
 def test_no_gpu_fails_loudly():
     from b200llm import _lib
-    geo_cfg = _lib.Config(_lib.ABI_VERSION, 256, 2, 4, 2, 64, 512, 1024, 1e-5, 16, 2, 8, 4, 0, 1, 0, 1, 1, 0, 1, None, None)
+    geo_cfg = _lib.Config(_lib.ABI_VERSION, 256, 2, 4, 2, 64, 512, 1024, 1e-5, 16, 2, 8, 4, 0, 1, 0, 1, 1, 0, 1, 1, None, None)
     h = C.c_void_p()
     rc = _lib.lib.b200llm_create(C.byref(geo_cfg), C.byref(h))
     assert rc == _lib.ENODEV
@@ -54,14 +54,14 @@ def test_no_gpu_fails_loudly():
 def test_config_validation_messages():
     from b200llm import _lib
     n = C.c_size_t()
-    bad = _lib.Config(_lib.ABI_VERSION, 256, 2, 4, 2, 96, 512, 1024, 1e-5, 16, 2, 8, 4, 0, 1, 0, 1, 1, 0, 1, None, None)
+    bad = _lib.Config(_lib.ABI_VERSION, 256, 2, 4, 2, 96, 512, 1024, 1e-5, 16, 2, 8, 4, 0, 1, 0, 1, 1, 0, 1, 1, None, None)
     assert _lib.lib.b200llm_workspace_bytes(C.byref(bad), C.byref(n)) == _lib.EINVAL
     assert b"head_dim" in _lib.lib.b200llm_last_error()
-    ok = _lib.Config(_lib.ABI_VERSION, 256, 2, 4, 2, 64, 512, 1024, 1e-5, 16, 2, 8, 4, 0, 1, 0, 1, 1, 0, 1, None, None)
+    ok = _lib.Config(_lib.ABI_VERSION, 256, 2, 4, 2, 64, 512, 1024, 1e-5, 16, 2, 8, 4, 0, 1, 0, 1, 1, 0, 1, 1, None, None)
     assert _lib.lib.b200llm_workspace_bytes(C.byref(ok), C.byref(n)) == 0 and n.value > 0
     assert _lib.lib.b200llm_kv_page_bytes(C.byref(ok), C.byref(n)) == 0
     assert n.value == 2 * 2 * 2 * 16 * 64 * 2
-    wrong_abi = _lib.Config(99, 256, 2, 4, 2, 64, 512, 1024, 1e-5, 16, 2, 8, 4, 0, 1, 0, 1, 1, 0, 1, None, None)
+    wrong_abi = _lib.Config(99, 256, 2, 4, 2, 64, 512, 1024, 1e-5, 16, 2, 8, 4, 0, 1, 0, 1, 1, 0, 1, 1, None, None)
     assert _lib.lib.b200llm_workspace_bytes(C.byref(wrong_abi), C.byref(n)) == _lib.EINVAL
 
 

@@ -27,6 +27,7 @@ TIGHT_TOL = 3e-3       # what the fp32-activation path achieves vs the mirrored 
 def _engine(name, sd_cpu=None, seed=0xB200, sigma=0.02, **kw):
     from b200llm import Engine, geometry, weights
     geo = geometry.resolve(name)
+    kw.setdefault("use_tc", False)      # fp32-activation path: what the kvbf16 goldens describe
     if sd_cpu is not None:
         w = weights.pack(geo, {k: v.cuda() for k, v in sd_cpu.items()})
     else:
@@ -161,6 +162,39 @@ def test_repeated_requests_on_one_engine(mega):
         toks, tm = eng.generate_ids(ids, 12, SamplingParams(temperature=0.0))
         assert toks == want
         assert tm.decode_steps == 11 and tm.prefill_tokens == 87
+    eng.close()
+
+
+@pytest.mark.parametrize("name", ["tiny", "small"])
+def test_tensor_core_batch_path_matches_bf16_activation_oracle(name, golden_dir):
+    """Prefill chunks and an 8-lane decode batch on the tcgen05 GEMM path (activations rounded to
+    bf16 at every matmul input) against the oracle in the same rounding model."""
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    geo = lo.GEOMETRIES[name]
+    sd = lo.make_weights(geo, int(g["seed"]), sigma=float(g["sigma"]), embed_sigma=float(g["embed_sigma"]))
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16, act_dtype=torch.bfloat16)
+    prompts = [wg.gen_tokens(20 + 9 * i, 300 + i, geo.vocab) for i in range(8)]
+    eng = _engine(name, sd, max_lanes=8, max_ctx=256, max_rows=32, use_tc=True)
+    lanes = [eng.open_lane() for _ in prompts]
+    worst = 0.0
+    for ln, p in zip(lanes, prompts):
+        st = orc.new_state()
+        ref = orc.forward(torch.as_tensor(p, dtype=torch.int64), st)
+        eng.prefill(ln, p)                           # 20..83 tokens in chunks of 32 -> tensor-core passes
+        eng.sync()
+        worst = max(worst, _rel(eng.logits(0), ref.numpy()))
+    assert worst <= LOGIT_TOL, worst
+    # one batched decode step, teacher-forced: every lane gets the oracle's greedy token
+    states, refs = [], []
+    for i, p in enumerate(prompts):
+        st = orc.new_state()
+        l0 = orc.forward(torch.as_tensor(p, dtype=torch.int64), st)
+        t0 = int(torch.argmax(l0))
+        eng.set_lane(lanes[i], t0, len(p))
+        refs.append(orc.forward(torch.tensor([t0]), st))
+    eng.decode(lanes, 1)
+    for i in range(8):
+        assert _rel(eng.logits(i), refs[i].numpy()) <= LOGIT_TOL
     eng.close()
 
 

@@ -241,3 +241,22 @@ def test_sampler_matches_oracle_chain():
     got = sample(torch.from_numpy(lg)[None].cuda(), [_lib.Sampling(0.0, 0, 1.0, 2.0, 0)],
                  history=torch.from_numpy(hist)[None].cuda())
     assert got.tolist() == [77]
+
+
+@pytest.mark.parametrize("N,K,T,acc", [(128, 64, 1, 0), (256, 256, 5, 1), (3072, 3072, 64, 1), (1024, 8192, 256, 1),
+                                       (148 * 128, 512, 33, 0), (5120, 3072, 17, 1), (512, 11008, 100, 1)])
+def test_gemm_tc_matches_fp32_matmul(N, K, T, acc):
+    """tcgen05 GEMM (bf16 x bf16 -> fp32) against torch fp32 on the same bf16 values; the k-split
+    partials meet with fp32 atomics, so the comparison is to 2e-4 of the output scale."""
+    import ctypes as C
+    from b200llm import _lib
+    w = wg.gen_bf16((N, K), 31 * N + K, 0.05)
+    x = (torch.randn(T, K, generator=torch.Generator().manual_seed(T)) * 0.5).to(torch.bfloat16)
+    base = torch.randn(T, N, generator=torch.Generator().manual_seed(1)) if acc else torch.zeros(T, N)
+    ref = base + x.float() @ w.float().t()
+    out = (base.clone() if acc else torch.full((T, N), float("nan"))).cuda()
+    wd, xd = w.cuda(), x.cuda()
+    _lib.check(_lib.lib.b200llm_op_gemm_tc(wd.data_ptr(), xd.data_ptr(), out.data_ptr(), N, T, N, K, acc,
+                                           torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    _close(out.cpu(), ref)

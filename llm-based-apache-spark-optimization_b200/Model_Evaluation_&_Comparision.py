@@ -1,0 +1,207 @@
+#!/usr/bin/env python
+"""Batched synthetic benchmark harness for the B200 decode engine.
+
+Takes the place of the reference's `Model_Evaluation_&_Comparision.py` (a sequential, batch-1
+script that timed `ollama.generate` with time.time() and scored exact match / Levenshtein
+distance; reference lines 19-66 and 109-158).  Those three text columns are kept -- they go
+through the same `ollama.generate(model=, system=, prompt=)` call -- and the harness adds what
+BASELINE.json asks for: decode tokens/s and p50 TTFT per model and batch size, as absolute
+numbers and as a fraction of the measured HBM roofline, on 1 GPU or (under torchrun) on N GPUs
+as request-level replicas, with the CPU path (the oracle port; the real Ollama/llama.cpp cannot
+be built here) timed on the host cores in the same run.
+
+    python "Model_Evaluation_&_Comparision.py" [--models llama3.2 duckdb-nsql] [--batch 1 8 64]
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 "Model_Evaluation_&_Comparision.py"
+
+With random-init weights and the stand-in byte tokenizer the text metrics are meaningless as
+quality numbers (exact match 0, large edit distance); they are reported to keep the columns.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import time
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+for _p in (ROOT, HERE):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+SCHEMA = ("CREATE TABLE taxi (VendorID bigint, tpep_pickup_datetime timestamp, tpep_dropoff_datetime timestamp, "
+          "passenger_count double, trip_distance double, fare_amount double, extra double, tip_amount double, "
+          "tolls_amount double, improvement_surcharge double, total_amount double);")
+# (question, expected SQL): the four multi-query cases of the reference's second part
+CASES = [
+    ("Get all taxis with more than 2 passengers.", "SELECT * FROM taxi WHERE passenger_count > 2;"),
+    ("Show total fare collected by each vendor.",
+     "SELECT VendorID, SUM(total_amount) AS Total_Fare FROM taxi GROUP BY VendorID;"),
+    ("Find the average trip distance for trips that had more than 2 passengers.",
+     "SELECT AVG(trip_distance) FROM taxi WHERE passenger_count > 2;"),
+    ("List all vendors ordered by total fare in descending order.",
+     "SELECT VendorID, SUM(total_amount) AS Total_Fare FROM taxi GROUP BY VendorID ORDER BY Total_Fare DESC;"),
+]
+
+
+def edit_distance(a: str, b: str) -> int:
+    """Levenshtein distance (the `Levenshtein` package is not on this image)."""
+    if len(a) < len(b):
+        a, b = b, a
+    prev = list(range(len(b) + 1))
+    for i, ca in enumerate(a, 1):
+        cur = [i]
+        for j, cb in enumerate(b, 1):
+            cur.append(min(prev[j] + 1, cur[j - 1] + 1, prev[j - 1] + (ca != cb)))
+        prev = cur
+    return prev[-1]
+
+
+def text_metrics(model: str, greedy: bool):
+    """The reference's columns: exact match, edit distance, wall latency of ollama.generate."""
+    import ollama
+    rows = []
+    opts = {"temperature": 0, "num_predict": 48} if greedy else {"num_predict": 48}
+    for question, expected in CASES:
+        t0 = time.time()
+        try:
+            res = ollama.generate(model=model, system="Here is the database schema that the SQL query will run on: "
+                                  + SCHEMA, prompt=question, options=opts)
+        except ollama.ResponseError as e:
+            return {"model": model, "error": str(e)}
+        latency = time.time() - t0
+        got = res.response.strip()
+        rows.append({"exact": int(got == expected), "edit": edit_distance(got, expected), "latency_s": latency,
+                     "ttft_ms": (res.load_duration + res.prompt_eval_duration) / 1e6,
+                     "tok_s": res.eval_count / max(res.eval_duration, 1) * 1e9})
+    n = len(rows)
+    return {"model": model, "exact_match_rate": 100.0 * sum(r["exact"] for r in rows) / n,
+            "avg_edit_distance": sum(r["edit"] for r in rows) / n, "avg_latency_s": sum(r["latency_s"] for r in rows) / n,
+            "queries": rows}
+
+
+def engine_bench(model: str, batch_sizes, prompt_len: int, new_tokens: int, n_ttft: int, local: int):
+    """decode tok/s per batch size + p50 TTFT on this rank's GPU (synthetic prompts, greedy)."""
+    import numpy as np
+    import torch
+    from b200llm import Engine, geometry, weights
+    geo = geometry.resolve(model)
+    w = weights.random_init(geo, 0xB200, local)
+    max_bs = max(batch_sizes)
+    eng = Engine(geo, w, device=local, max_lanes=max_bs, max_ctx=prompt_len + new_tokens + 32, max_rows=max(64, max_bs))
+    rng = np.random.default_rng(7 + local)
+    out = {"model": model, "ttft_ms_p50": None, "decode": []}
+    ttfts = []
+    for _ in range(n_ttft):
+        ln = eng.open_lane()
+        p = rng.integers(0, min(geo.vocab, 128000), prompt_len, dtype=np.int32)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        eng.prefill(ln, p)
+        eng.read_lane(ln)                 # first token on the host = TTFT
+        ttfts.append((time.perf_counter() - t0) * 1e3)
+        eng.close_lane(ln)
+    out["ttft_ms_p50"] = statistics.median(ttfts[1:] or ttfts)
+    for bs in batch_sizes:
+        lanes = [eng.open_lane() for _ in range(bs)]
+        for ln in lanes:
+            eng.prefill(ln, rng.integers(0, min(geo.vocab, 128000), prompt_len, dtype=np.int32))
+        eng.decode(lanes, 4, read=False)  # warm-up / graph capture
+        eng.sync()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(eng.stream)
+        eng.decode(lanes, new_tokens, read=False)
+        ev1.record(eng.stream)
+        torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1) / new_tokens
+        mean_ctx = prompt_len + 4 + (new_tokens - 1) / 2
+        out["decode"].append({"bs": bs, "ms_per_step": ms, "tok_s": bs * 1000.0 / ms,
+                              "bytes_per_step": geo.step_bytes(bs, mean_ctx)})
+        for ln in lanes:
+            eng.close_lane(ln)
+    eng.close()
+    del w
+    torch.cuda.empty_cache()
+    return out
+
+
+def cpu_row(model: str):
+    import bench
+    v, dt, cores = bench.cpu_decode_tok_s(model, 64, 12, 1)
+    return {"tok_s": v, "cores": cores, "sample": "12 decode steps at bs1 after a 64-id prompt, oracle port, torch CPU bf16"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--models", nargs="+", default=["llama3.2", "duckdb-nsql"])
+    ap.add_argument("--batch", nargs="+", type=int, default=[1, 8, 64])
+    ap.add_argument("--prompt-len", type=int, default=296)
+    ap.add_argument("--new-tokens", type=int, default=128)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-text", action="store_true")
+    args = ap.parse_args()
+    import torch
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("gloo")
+    import bench
+    peak, peak_src = bench.peaks()
+    report = {"n_gpus": world, "hbm_peak_gbs": peak, "peak_source": peak_src, "models": []}
+    for model in args.models:
+        entry = {"model": model}
+        if not args.no_text and rank == 0:
+            os.environ["B200LLM_DEVICE"] = str(local)
+            entry["text"] = text_metrics(model, greedy=True)
+            from b200llm import runtime
+            runtime.unload_all()
+            torch.cuda.empty_cache()
+        if world > 1:
+            dist.barrier()
+        mine = engine_bench(model, args.batch, args.prompt_len, args.new_tokens, 4, local)
+        if world > 1:
+            box = [None] * world
+            dist.all_gather_object(box, mine)
+        else:
+            box = [mine]
+        rows = []
+        for i, d in enumerate(mine["decode"]):
+            ms = max(b["decode"][i]["ms_per_step"] for b in box)       # replicas: slowest rank sets the time
+            tok_s = world * d["bs"] * 1000.0 / ms
+            gbs = d["bytes_per_step"] / (ms * 1e-3) / 1e9
+            rows.append({"bs": d["bs"], "ms_per_step": ms, "tok_s_total": tok_s, "gbs_per_gpu": gbs,
+                         "pct_of_measured_peak": 100 * gbs / peak, "pct_of_8000": 100 * gbs / 8000.0})
+        entry["gpu"] = {"ttft_ms_p50": statistics.median(b["ttft_ms_p50"] for b in box), "decode": rows,
+                        "parallelism": f"{world} replica(s)"}
+        if not args.no_cpu and rank == 0:
+            entry["cpu"] = cpu_row(model)
+        report["models"].append(entry)
+    if rank == 0:
+        print("=" * 100)
+        for e in report["models"]:
+            print(f"Model: {e['model']}   ({report['n_gpus']} GPU(s), roofline {peak:.0f} GB/s {peak_src})")
+            t = e.get("text")
+            if t and "error" not in t:
+                print(f"  Exact Match Rate: {t['exact_match_rate']:.2f}%   Average Edit Distance: "
+                      f"{t['avg_edit_distance']:.2f}   Average Latency: {t['avg_latency_s']:.4f} sec")
+            elif t:
+                print(f"  text metrics: {t['error']}")
+            if "cpu" in e:
+                print(f"  CPU ({e['cpu']['cores']} cores, oracle port): {e['cpu']['tok_s']:.2f} tok/s")
+            print(f"  p50 TTFT ({args.prompt_len} ids): {e['gpu']['ttft_ms_p50']:.2f} ms")
+            for r in e["gpu"]["decode"]:
+                print(f"  bs {r['bs']:3d}: {r['tok_s_total']:10.1f} tok/s  {r['ms_per_step']:.3f} ms/step  "
+                      f"{r['gbs_per_gpu']:.0f} GB/s = {r['pct_of_measured_peak']:.1f}% of measured, "
+                      f"{r['pct_of_8000']:.1f}% of 8000")
+            print("=" * 100)
+        print(json.dumps(report))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -119,13 +119,14 @@ def test_chunked_prefill_ragged_and_batched_decode(golden_dir):
 
 
 @pytest.mark.parametrize("mega", [False, True])
-@pytest.mark.parametrize("fname,name", [("llama3.2_1b", "llama3.2:1b"), ("llama3.2", "llama3.2")])
+@pytest.mark.parametrize("fname,name", [("llama3.2_1b", "llama3.2:1b"), ("llama3.2", "llama3.2"),
+                                        ("duckdb-nsql", "duckdb-nsql")])
 def test_golden_parity_full_size(fname, name, mega, golden_dir):
     """BASELINE.json configs 1/2 geometries against the committed golden vectors (oracle run
     in the CPU container); weights come from the device twin of the seeded stream."""
     g = np.load(os.path.join(golden_dir, fname + ".npz"))
-    eng = _engine(name, None, seed=int(g["seed"]), sigma=float(g["sigma"]), max_lanes=1, max_ctx=512, max_rows=64,
-                  use_megakernel=mega)
+    eng = _engine(name, None, seed=int(g["seed"]), sigma=float(g["sigma"]), max_lanes=1,
+                  max_ctx=len(g["prompt"]) + 128, max_rows=64, use_megakernel=mega)
     lane = eng.open_lane()
     prompt, toks, probe = g["prompt"], g["tokens"].tolist(), g["probe_ids"]
     eng.prefill(lane, prompt)

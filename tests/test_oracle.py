@@ -84,7 +84,7 @@ def test_golden_reproduces(name, golden_dir):
 
 
 def test_golden_files_present(golden_dir):
-    for name in ("tiny", "small", "llama3.2_1b", "llama3.2"):
+    for name in ("tiny", "small", "llama3.2_1b", "llama3.2", "duckdb-nsql"):
         g = np.load(os.path.join(golden_dir, name + ".npz"))
         assert g["tokens"].shape == (64,) and g["probe_kvbf16"].shape == (64, 256)
 

@@ -26,8 +26,11 @@
 
 namespace b200 {
 
-constexpr int kMC = 512;                       // compute threads
+constexpr int kMC = 384;                       // compute threads (12 warps + the producer warp leave 152 registers
+                                               // per thread; with 16 warps the 96-register cap spilled, and a spill
+                                               // right after a grid barrier is an L2 round trip)
 constexpr int kMW = kMC / 32;                  // compute warps
+constexpr int kSPW = (64 + kMW - 1) / kMW;     // 32-wide k steps of a ring stage per warp (stage <= 2048 columns)
 constexpr int kMaxKC = 2048;                   // columns of one ring stage (8 rows x kMaxKC)
 constexpr int kSlotBytes = 33792;              // >= 8 * (kMaxKC * 2 + 16), multiple of 128
 constexpr int kSlots = 5;

@@ -184,8 +184,8 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
         bar_sync(1, kMC);
         mega_trace(p, c.ti, bid, tid);  // (debug) all warps done
         // ---- CTA result = merge of the 16 warps; one thread per (q head, dim) ----
-        if (tid < GQ * HD) {
-            const int g = tid / HD, dd = tid % HD;
+        for (int idx = tid; idx < GQ * HD; idx += kMC) {
+            const int g = idx / HD, dd = idx % HD;
             float M = -INFINITY;
 #pragma unroll
             for (int w = 0; w < kMW; ++w) M = fmaxf(M, mrg[((size_t)w * GQ + g) * (HD + 2) + HD]);
@@ -225,8 +225,8 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
                     ml[i] = __ldcg(&p.part_ml[((size_t)(hk * GQ + g) * p.n_splits) * 2 + r]);
                 }
                 bar_sync(1, kMC);
-                if (tid < GQ * HD) {
-                    const int g = tid / HD, dd = tid % HD;
+                for (int idx = tid; idx < GQ * HD; idx += kMC) {
+                    const int g = idx / HD, dd = idx % HD;
                     const size_t pb = (size_t)(hk * GQ + g) * p.n_splits;
                     float M = -INFINITY;
                     for (int sp = 0; sp < ns; ++sp) M = fmaxf(M, ml[(g * ns + sp) * 2]);

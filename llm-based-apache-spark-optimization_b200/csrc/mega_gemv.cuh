@@ -158,11 +158,11 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
                 const int i16_base = (pt * kc) >> 4;
                 // (a) pull this warp's weight fragments out of the stage, (b) hand the slot back to
                 // the producer, (c) only then spend time in the tensor pipe
-                uint32_t af[4][4];
-                uint2 bx[4];
+                uint32_t af[kSPW][4];
+                uint2 bx[kSPW];
                 uint32_t dep = 0;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {  // steps32 <= 64 = 4 per warp
+                for (int j = 0; j < kSPW; ++j) {  // steps32 <= 64: kSPW per warp
                     const int st = warp + j * kMW;
                     af[j][0] = af[j][1] = af[j][2] = af[j][3] = 0u;
                     bx[j] = make_uint2(0u, 0u);
@@ -175,10 +175,10 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
                 __syncwarp();
                 if (lane == 0) mbar_arrive_after(&s.empty[slot], dep);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < kSPW; ++j) {
                     const int st = warp + j * kMW;
                     if (st < ((p.dbg & 1) ? 0 : steps32))
-                        mma_bf16_16816(acc4[j], af[j][0], af[j][1], af[j][2], af[j][3], bx[j].x, bx[j].y);
+                        mma_bf16_16816(acc4[j & 3], af[j][0], af[j][1], af[j][2], af[j][3], bx[j].x, bx[j].y);
                 }
                 if (fine) {
                     unsigned long long t;

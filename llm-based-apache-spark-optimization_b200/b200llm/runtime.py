@@ -15,6 +15,7 @@ import torch
 
 from . import _lib, geometry, weights
 from .engine import Engine
+from .scheduler import Scheduler
 from .tokenizer import ByteTokenizer
 
 SEED = 0xB200
@@ -26,6 +27,7 @@ class LoadedModel:
     engine: Engine
     tokenizer: ByteTokenizer
     load_ns: int
+    scheduler: Scheduler = None
 
 
 _models: Dict[str, LoadedModel] = {}
@@ -37,7 +39,7 @@ def get_model(name: str) -> LoadedModel:
     with _lock:
         m = _models.get(geo.name)
         if m is not None:
-            return LoadedModel(m.name, m.engine, m.tokenizer, 0)
+            return LoadedModel(m.name, m.engine, m.tokenizer, 0, m.scheduler)
         if not torch.cuda.is_available():
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         t0 = time.perf_counter_ns()
@@ -47,7 +49,7 @@ def get_model(name: str) -> LoadedModel:
         eng = Engine(geo, w, device=dev, max_lanes=int(os.environ.get("B200LLM_MAX_LANES", "8")),
                      max_ctx=int(os.environ.get("B200LLM_NUM_CTX", "4096")),
                      max_rows=int(os.environ.get("B200LLM_MAX_ROWS", "64")))
-        m = LoadedModel(geo.name, eng, ByteTokenizer(geo.vocab), time.perf_counter_ns() - t0)
+        m = LoadedModel(geo.name, eng, ByteTokenizer(geo.vocab), time.perf_counter_ns() - t0, Scheduler(eng))
         _models[geo.name] = m
         return m
 
@@ -55,5 +57,6 @@ def get_model(name: str) -> LoadedModel:
 def unload_all() -> None:
     with _lock:
         for m in _models.values():
+            m.scheduler.shutdown()
             m.engine.close()
         _models.clear()

@@ -105,7 +105,7 @@ def generate(model: str = "", prompt: str = "", suffix: str = "", system: str = 
     sp = SamplingParams(temperature=float(opt["temperature"]), top_k=int(opt["top_k"]), top_p=float(opt["top_p"]),
                         repeat_penalty=float(opt["repeat_penalty"]), seed=int(opt["seed"]))
     try:
-        toks, tm = m.engine.generate_ids(ids, num_predict, sp, stop_ids=m.tokenizer.stop_ids)
+        toks, tm = m.scheduler.generate_ids(ids, num_predict, sp, stop_ids=m.tokenizer.stop_ids)
     except B200LLMError as e:
         raise ResponseError(e.message, 500) from e
     stopped = bool(toks) and toks[-1] in m.tokenizer.stop_ids

@@ -199,6 +199,35 @@ def test_tensor_core_batch_path_matches_bf16_activation_oracle(name, golden_dir)
     eng.close()
 
 
+def test_scheduler_batches_concurrent_callers():
+    """Threaded callers (the Flask dev server case) share one engine through the scheduler: every
+    request gets exactly the tokens it gets when run alone, whatever it was batched with."""
+    import threading
+    from b200llm import SamplingParams
+    from b200llm.scheduler import Scheduler
+    geo = lo.GEOMETRIES["tiny"]
+    sd = lo.make_weights(geo, 0xB200, sigma=0.08)
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    prompts = [wg.gen_tokens(10 + 7 * i, 500 + i, geo.vocab) for i in range(6)]
+    budgets = [9, 20, 5, 33, 14, 1]
+    want = [orc.greedy(p, n)[0] for p, n in zip(prompts, budgets)]
+    eng = _engine("tiny", sd, max_lanes=4, max_ctx=128, max_rows=8)      # 6 callers, 4 lanes: two must queue
+    sched = Scheduler(eng, chunk=4)
+    got = [None] * 6
+
+    def call(i):
+        got[i] = sched.generate_ids(prompts[i], budgets[i], SamplingParams(temperature=0.0))[0]
+
+    threads = [threading.Thread(target=call, args=(i,)) for i in range(6)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=120)
+    assert got == want
+    sched.shutdown()
+    eng.close()
+
+
 def test_shim_replays_reference_call_sites():
     """The six ollama.generate call patterns of the reference, unmodified, against the shim."""
     import ollama

@@ -33,6 +33,7 @@ METRIC = "decode_tok_s_llama3.2-3b_bs1"
 UNIT = "tok/s"
 PROMPT_LEN = 296          # 20 system + 25 wrapper + ~250 Spark-error tokens
 E2E_NEW_TOKENS = 128
+NCU_DRAM_BYTES_PER_STEP = (12.958280e9 + 5.217e6) / 2   # profiles/mega_full_r1c_summary.txt
 
 
 def parse_args():
@@ -266,9 +267,16 @@ def run_b200(args):
                     "what": f"ollama-style generate: {PROMPT_LEN} host prompt ids -> prefill -> "
                             f"{E2E_NEW_TOKENS} greedy tokens -> host, x{e2e_runs}; tokens / wall time incl. prefill"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src,
-                         "what": "whole decode step: algorithmic bytes B(bs, mean ctx) of SURVEY.md 8(d) / step time",
-                         "bytes_per_step": step_bytes},
+                         "traffic": (NCU_DRAM_BYTES_PER_STEP * args.steps
+                                     if (args.model == "llama3.2" and bs == 1 and not args.no_mega) else None),
+                         "peak_source": peak_src,
+                         "kernel": "mega_decode_kernel<128,3> (one persistent launch = all timed steps)"
+                                   if (bs == 1 and not args.no_mega) else "CUDA graph of the per-phase kernels",
+                         "what": "algorithmic bytes B(bs, mean ctx) of SURVEY.md 8(d) x steps / device time of the "
+                                 "timed region; traffic = dram read+write bytes of the same kernel under ncu "
+                                 "(profiles/mega_full_r1c_summary.txt: 12.96 GB for a 2-step launch), scaled to "
+                                 "the steps of this launch",
+                         "bytes_per_launch": step_bytes * args.steps, "bytes_per_step": step_bytes},
         }
         if not args.no_cpu_baseline and world == 1:
             v, dt, cores = cpu_decode_tok_s(args.model, 64, 24, 2)

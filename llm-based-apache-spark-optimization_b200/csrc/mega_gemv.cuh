@@ -77,7 +77,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
     const bool res_pre = epi == B200LLM_EPI_RESIDUAL && rr.nrows <= kRB;
     if (res_pre && tid < rr.nrows) hres = __ldcg(p.h + rr.row0 + tid);
     float ss = 0.f;
-#pragma unroll 4
+#pragma unroll 2
     for (int it = tid; it < n_items; it += kMC) {
         const int i16 = it >> 2, t = it & 3;
         const int k = i16 * 16 + t * 2;

@@ -7,11 +7,17 @@
 namespace b200 {
 
 // x fp32 [rows, d] -> bf16 [rows, d] = gain * (x * rsqrt(mean(x^2) + eps)); one CTA per row
+// Also zeroes `zero_w` floats of row `row` of a second buffer (the fp32 output the next, k-split
+// GEMM accumulates into), which saves a memset node between the two kernels.
 __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float *x, const uint16_t *gain, uint16_t *out, int d,
-                                                           float eps) {
+                                                           float eps, float *zero, int zero_w) {
     __shared__ float red[8];
+    pdl_trigger();
     pdl_wait();
     const int row = blockIdx.x;
+    if (zero != nullptr)
+        for (int k = threadIdx.x * 4; k < zero_w; k += blockDim.x * 4)
+            *reinterpret_cast<float4 *>(zero + (size_t)row * zero_w + k) = make_float4(0.f, 0.f, 0.f, 0.f);
     const float *xr = x + (size_t)row * d;
     float ss = 0.f;
     for (int k = threadIdx.x * 4; k < d; k += blockDim.x * 4) {
@@ -37,6 +43,7 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float *x, const
 
 // fp32 [rows, n] (row stride in_stride) -> bf16 [rows, n]
 __global__ void __launch_bounds__(256) cast_bf16_kernel(const float *x, int64_t in_stride, uint16_t *out, int n) {
+    pdl_trigger();
     pdl_wait();
     const int row = blockIdx.y;
     for (int k = (blockIdx.x * blockDim.x + threadIdx.x) * 4; k < n; k += gridDim.x * blockDim.x * 4) {
@@ -50,6 +57,7 @@ __global__ void __launch_bounds__(256) cast_bf16_kernel(const float *x, int64_t 
 
 // gate/up fp32 [rows, 2 ffn] with interleaved rows (2i = gate_i, 2i+1 = up_i) -> bf16 [rows, ffn]
 __global__ void __launch_bounds__(256) swiglu_bf16_kernel(const float *gu, uint16_t *out, int ffn) {
+    pdl_trigger();
     pdl_wait();
     const int row = blockIdx.y;
     const float *g = gu + (size_t)row * 2 * ffn;
@@ -73,6 +81,7 @@ struct RopeArgs {
     int n_q, n_kv, hd, page_tokens, max_pages;
 };
 __global__ void __launch_bounds__(256) rope_append_kernel(const __grid_constant__ RopeArgs a) {
+    pdl_trigger();
     pdl_wait();
     const int row = blockIdx.y;
     const int width = (a.n_q + 2 * a.n_kv) * a.hd;
@@ -101,11 +110,12 @@ __global__ void __launch_bounds__(256) rope_append_kernel(const __grid_constant_
     }
 }
 
-int rmsnorm_bf16_launch(const float *x, const void *gain, void *out, int rows, int d, float eps, cudaStream_t s, bool pdl) {
-    B200_REQUIRE(d % 4 == 0 && rows >= 1, "rmsnorm_bf16: bad shape");
+int rmsnorm_bf16_launch(const float *x, const void *gain, void *out, int rows, int d, float eps, cudaStream_t s, bool pdl,
+                        float *zero, int zero_w) {
+    B200_REQUIRE(d % 4 == 0 && rows >= 1 && zero_w % 4 == 0, "rmsnorm_bf16: bad shape");
     LaunchCfg lc(dim3(rows), dim3(256), 0, s, pdl);
     B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, rmsnorm_bf16_kernel, x, reinterpret_cast<const uint16_t *>(gain),
-                                    reinterpret_cast<uint16_t *>(out), d, eps));
+                                    reinterpret_cast<uint16_t *>(out), d, eps, zero, zero_w));
     return B200LLM_OK;
 }
 int cast_bf16_launch(const float *x, int64_t in_stride, void *out, int rows, int n, cudaStream_t s, bool pdl) {

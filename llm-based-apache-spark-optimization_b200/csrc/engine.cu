@@ -125,6 +125,7 @@ struct b200llm_engine {
     unsigned long long *trace = nullptr;
     // batch / prefill path
     uint16_t *xb = nullptr;
+    bool tc_pdl = true;
     float *qkv_out = nullptr, *gu_out = nullptr;
     struct MapBox { alignas(128) unsigned char b[128]; };
     std::map<std::tuple<const void *, int64_t, int64_t, int>, MapBox *> maps;
@@ -314,6 +315,7 @@ int b200llm_create(const b200llm_config *cfg, b200llm_engine **out) {
     e->max_ctx = cfg->max_pages_per_lane * cfg->page_tokens;
     e->layers.resize(cfg->n_layers);
     e->pdl = cfg->use_pdl != 0;
+    e->tc_pdl = getenv("B200LLM_TC_NO_PDL") == nullptr;
     if (cfg->stream) {
         e->stream = (cudaStream_t)cfg->stream;
     } else {
@@ -733,7 +735,7 @@ static bool tc_usable(const b200llm_engine *e, int rows) {
 
 // out (+)= X W^T through the tcgen05 kernel; X = e->xb viewed as [max_rows, K]
 static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, int64_t out_stride, int T,
-                   bool add_to_existing) {
+                   bool add_to_existing, bool prezeroed = false) {
     const void *mw, *mx;
     B200_TRY(get_map(e, w, N, K, 128, &mw));
     B200_TRY(get_map(e, e->xb, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mx));
@@ -741,11 +743,11 @@ static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, i
     if (!add_to_existing) {
         if (N / 128 >= kNumSMs) {
             accumulate = 0;  // enough row tiles: no k split, plain stores
-        } else {
+        } else if (!prezeroed) {
             B200_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)T * out_stride * 4, e->stream));
         }
     }
-    B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, false));
+    B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, e->tc_pdl));
     e->launches++;
     return B200LLM_OK;
 }
@@ -754,21 +756,22 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
     const b200llm_config &c = e->cfg;
     const int rows = pr.rows;
     cudaStream_t st = e->stream;
+    const bool pdl = e->tc_pdl;
     EmbedArgs ea{};
     ea.embed = e->embed, ea.h = e->h, ea.row_token = pr.row_token, ea.row_pos = pr.row_pos, ea.row_lane = pr.row_lane;
     ea.lane_token = e->lane_token, ea.lane_pos = e->lane_pos, ea.rows = rows, ea.d = c.d, ea.vocab = c.vocab;
     ea.from_lanes = pr.from_lanes ? 1 : 0;
-    B200_TRY(embed_launch_ex(ea, e->lane_hist, pr.from_lanes ? e->step_ctr : nullptr, st, false));
+    B200_TRY(embed_launch_ex(ea, e->lane_hist, pr.from_lanes ? e->step_ctr : nullptr, st, pdl));
     e->launches++;
     const int qd = c.n_q * c.head_dim, qkv_w = (c.n_q + 2 * c.n_kv) * c.head_dim;
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW &w = e->layers[l];
         uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
         uint8_t *vl = kl + e->kv_half_stride;
-        B200_TRY(rmsnorm_bf16_launch(e->h, w.attn_norm, e->xb, rows, c.d, c.rms_eps, st, false));
-        B200_TRY(tc_gemm(e, w.wqkv, qkv_w, c.d, e->qkv_out, qkv_w, rows, false));
+        B200_TRY(rmsnorm_bf16_launch(e->h, w.attn_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->qkv_out, qkv_w));
+        B200_TRY(tc_gemm(e, w.wqkv, qkv_w, c.d, e->qkv_out, qkv_w, rows, false, true));
         B200_TRY(rope_append_launch(e->qkv_out, e->q, kl, vl, e->inv_freq, pr.row_lane, pr.row_pos, e->page_table, rows,
-                                    c.n_q, c.n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, false));
+                                    c.n_q, c.n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, pdl));
         b200llm_attn_args at{};
         at.q = e->q, at.out = e->att, at.k_pages = kl, at.v_pages = vl, at.row_lane = pr.row_lane, at.row_pos = pr.row_pos;
         at.page_table = e->page_table, at.bs = rows, at.n_q = c.n_q, at.n_kv = c.n_kv, at.head_dim = c.head_dim;
@@ -777,12 +780,12 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         if (want > 6) want = 6;
         at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
         at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
-        B200_TRY(attn_decode_launch(at, st, false));
-        B200_TRY(cast_bf16_launch(e->att, qd, e->xb, rows, qd, st, false));
+        B200_TRY(attn_decode_launch(at, st, pdl));
+        B200_TRY(cast_bf16_launch(e->att, qd, e->xb, rows, qd, st, pdl));
         B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->h, c.d, rows, true));
-        B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, false));
-        B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false));
-        B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, c.ffn, st, false));
+        B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->gu_out, 2 * c.ffn));
+        B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false, true));
+        B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, c.ffn, st, pdl));
         B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true));
         e->launches += 6;
     }
@@ -790,7 +793,7 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
     e->last_logit_rows = pr.logit_rows;
     if (pr.logit_rows <= 0) return B200LLM_OK;
     B200_TRY(rmsnorm_bf16_launch(e->h + (size_t)pr.logit_row0 * c.d, e->final_norm, e->xb, pr.logit_rows, c.d, c.rms_eps,
-                                 st, false));
+                                 st, pdl));
     B200_TRY(tc_gemm(e, e->lm_head, c.vocab, c.d, e->logits, c.vocab, pr.logit_rows, false));
     SampleDev sd{};
     sd.a.logits = e->logits, sd.a.bs = pr.logit_rows, sd.a.vocab = c.vocab;
@@ -800,7 +803,7 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
     sd.lane_token = e->lane_token, sd.lane_pos = e->lane_pos, sd.lane_hist = e->lane_hist;
     sd.gen_out = pr.from_lanes ? e->gen_out : nullptr, sd.step_ctr = pr.from_lanes ? e->step_ctr : nullptr;
     sd.advance = advance ? 1 : 0;
-    B200_TRY(sample_launch(sd, st, false));
+    B200_TRY(sample_launch(sd, st, pdl));
     e->launches += 2;
     return B200LLM_OK;
 }

@@ -101,6 +101,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = *tmem_slot;
+    pdl_trigger();
     pdl_wait();  // X (and the residual in `out`) come from the previous kernel
 
     if (warp == 0) {

@@ -57,7 +57,8 @@ int tc_make_map(void *map_out_128B, const void *base, int64_t rows, int64_t cols
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
                    int accumulate, cudaStream_t stream, bool pdl);
 // batch_ops.cu
-int rmsnorm_bf16_launch(const float *x, const void *gain, void *out, int rows, int d, float eps, cudaStream_t s, bool pdl);
+int rmsnorm_bf16_launch(const float *x, const void *gain, void *out, int rows, int d, float eps, cudaStream_t s, bool pdl,
+                        float *zero = nullptr, int zero_w = 0);
 int cast_bf16_launch(const float *x, int64_t in_stride, void *out, int rows, int n, cudaStream_t s, bool pdl);
 int swiglu_bf16_launch(const float *gu, void *out, int rows, int ffn, cudaStream_t s, bool pdl);
 int rope_append_launch(const float *qkv, float *q, void *k_pages, void *v_pages, const float *inv_freq,

@@ -99,7 +99,18 @@ enum {
     B200LLM_W_O_ST = 11,
     B200LLM_W_GATE_UP_ST = 12,
     B200LLM_W_DOWN_ST = 13,
-    B200LLM_W_LM_HEAD_ST = 14
+    B200LLM_W_LM_HEAD_ST = 14,
+    /* Optional copies for the tcgen05 persistent batch-1 kernel, "tile-major": the matrix cut into
+     * [128 rows x 64 k] tiles stored [N/128][K/64][128][64], each 16 KB tile laid out as a
+     * 128-byte-swizzled K-major tensor-core operand (16-byte chunk c of row r at chunk c ^ (r & 7)),
+     * so one bulk copy lands a ready MMA operand.  Needs N % 128 == 0 and K % 64 == 0; rows/cols
+     * in the descriptor are the logical [N, K].  When all five are bound they take precedence
+     * over the stage-major copies. */
+    B200LLM_W_QKV_TM = 15,
+    B200LLM_W_O_TM = 16,
+    B200LLM_W_GATE_UP_TM = 17,
+    B200LLM_W_DOWN_TM = 18,
+    B200LLM_W_LM_HEAD_TM = 19
 };
 
 typedef struct b200llm_tensor_desc {
@@ -210,6 +221,14 @@ typedef struct b200llm_gemv_args {
 int b200llm_op_gemv(const b200llm_gemv_args *a, void *stream);
 /* Number of CTAs b200llm_op_gemv will launch for (N, K, bs, epi): size of the LOGITS partials. */
 int b200llm_op_gemv_grid(int32_t N, int32_t K, int32_t bs, int32_t epi, int32_t *grid);
+
+/* One weight-streaming phase of the tcgen05 persistent decode kernel on its own (test hook):
+ * out[N] = W x with W given tile-major (B200LLM_W_*_TM layout), x and out fp32 on the device.
+ * k_split = 0 cuts the matrix at row-tile boundaries (the lm_head mode, plain stores),
+ * k_split = 1 into 148 equal (tile, k block) ranges whose partial sums meet with fp32 atomics
+ * (the mode of every other phase).  umma_n = 8 or 16 (N of the MMA instruction).  Synchronous. */
+int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, int32_t K, int32_t k_split,
+                       int32_t umma_n, void *stream);
 
 /* Paged GQA decode attention with split-T partials merged by the last CTA to finish.
  * `scratch` holds the split partials and arrival counters; it must be zeroed once

@@ -16,6 +16,7 @@ OK, EINVAL, ENODEV, ECUDA, ESTATE, ENCCL, ENOMEM = 0, -1, -2, -3, -4, -5, -6
 
 W_EMBED, W_LM_HEAD, W_FINAL_NORM, W_INV_FREQ, W_ATTN_NORM, W_QKV, W_O, W_MLP_NORM, W_GATE_UP, W_DOWN = range(10)
 W_QKV_ST, W_O_ST, W_GATE_UP_ST, W_DOWN_ST, W_LM_HEAD_ST = range(10, 15)
+W_QKV_TM, W_O_TM, W_GATE_UP_TM, W_DOWN_TM, W_LM_HEAD_TM = range(15, 20)
 EPI_STORE, EPI_RESIDUAL, EPI_SWIGLU, EPI_QKV_ROPE, EPI_LOGITS = range(5)
 
 
@@ -95,6 +96,7 @@ SYMBOLS = {
     "b200llm_debug_read_trace": (C.c_int, [C.c_void_p, _P(C.c_uint64), C.c_int32]),
     "b200llm_op_gemv": (C.c_int, [_P(GemvArgs), C.c_void_p]),
     "b200llm_op_gemv_grid": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P(C.c_int32)]),
+    "b200llm_op_gemv_tm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "b200llm_op_attn_decode": (C.c_int, [_P(AttnArgs), C.c_void_p]),
     "b200llm_op_attn_scratch_bytes": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                                 _P(C.c_size_t)]),

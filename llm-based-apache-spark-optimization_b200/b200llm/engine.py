@@ -6,6 +6,8 @@ reference's `ollama.generate` calls (Flask/app.py:102-107,160-166; FastAPI/app.p
 """
 from __future__ import annotations
 
+import os
+
 import ctypes as C
 import threading
 from dataclasses import dataclass
@@ -55,8 +57,13 @@ class Engine:
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         self.geo, self.weights, self.device = geo, weights, device
         if use_megakernel and tp_size == 1 and not any(k >= _lib.W_QKV_ST for k, _, _ in weights.tensors):
-            from .weights import add_stage_major
-            add_stage_major(weights)          # the persistent kernel streams its own stage-major copies
+            # the persistent kernels stream their own copies of the matrices: tile-major for the
+            # tcgen05 kernel, stage-major for the mma.sync one (geometries the former cannot tile)
+            from .weights import add_stage_major, add_tile_major, tile_major_ok
+            if tile_major_ok(geo) and os.environ.get("B200LLM_PERSISTENT", "tc") == "tc":
+                add_tile_major(weights)
+            else:
+                add_stage_major(weights)
         self.max_lanes, self.max_rows = max_lanes, max_rows
         self.max_pages_per_lane = (max_ctx + PAGE_TOKENS - 1) // PAGE_TOKENS
         torch.cuda.set_device(device)

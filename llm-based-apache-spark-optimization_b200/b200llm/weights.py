@@ -95,6 +95,36 @@ _ST_KIND = {_lib.W_QKV: _lib.W_QKV_ST, _lib.W_O: _lib.W_O_ST, _lib.W_GATE_UP: _l
             _lib.W_DOWN: _lib.W_DOWN_ST, _lib.W_LM_HEAD: _lib.W_LM_HEAD_ST}
 
 
+def tile_major(w: torch.Tensor) -> torch.Tensor:
+    """[N, K] -> [N/128, K/64, 128, 64]: the tcgen05 persistent kernel's operand tiles, each 16 KB
+    tile contiguous and pre-swizzled (16-byte chunk c of row r stored at chunk c ^ (r & 7)), see
+    B200LLM_W_*_TM in include/b200llm.h."""
+    N, K = w.shape
+    assert N % 128 == 0 and K % 64 == 0
+    t = w.view(N // 128, 128, K // 64, 8, 8).permute(0, 2, 1, 3, 4)            # [tile, kb, row, chunk, 8]
+    idx = torch.arange(8, device=w.device)[None, :] ^ (torch.arange(128, device=w.device)[:, None] & 7)
+    out = t[:, :, torch.arange(128, device=w.device)[:, None], idx].contiguous()  # out[r, c] = in[r, c ^ (r & 7)]
+    out.logical_shape = (N, K)
+    return out
+
+
+def tile_major_ok(geo) -> bool:
+    qkv = (geo.n_q + 2 * geo.n_kv) * geo.head_dim
+    shapes = [(qkv, geo.d), (geo.d, geo.n_q * geo.head_dim), (2 * geo.ffn, geo.d), (geo.d, geo.ffn), (geo.vocab, geo.d)]
+    return all(n % 128 == 0 and k % 64 == 0 for n, k in shapes)
+
+
+_TM_KIND = {_lib.W_QKV: _lib.W_QKV_TM, _lib.W_O: _lib.W_O_TM, _lib.W_GATE_UP: _lib.W_GATE_UP_TM,
+            _lib.W_DOWN: _lib.W_DOWN_TM, _lib.W_LM_HEAD: _lib.W_LM_HEAD_TM}
+
+
+def add_tile_major(pw: "PackedWeights", start: int = 0) -> None:
+    """Append tile-major copies of the matrices pw.tensors[start:] (tcgen05 persistent-kernel layout)."""
+    for kind, layer, t in list(pw.tensors[start:]):
+        if kind in _TM_KIND and pw.tp_size == 1:
+            pw.tensors.append((_TM_KIND[kind], layer, tile_major(t)))
+
+
 def add_stage_major(pw: "PackedWeights", start: int = 0) -> None:
     """Append stage-major copies of the matrices pw.tensors[start:] (persistent-kernel layout)."""
     for kind, layer, t in list(pw.tensors[start:]):

@@ -1,0 +1,246 @@
+// decode_tc.cu -- the batch-1 decode step as ONE persistent kernel whose weight stream is
+// consumed by the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM).
+//
+// decode_mega.cu consumes its ring with mma.sync from registers and is bound by instruction
+// issue at about the HBM rate, so nothing the producer prefetches during a grid barrier is ever
+// caught up on.  Here the consumer is one thread issuing tcgen05.mma straight from shared
+// memory (M = 128 weight rows, N = 8, K = 16 per instruction, 4 KB of weights each), several
+// times faster than the stream, so the ring drains as fast as it fills and HBM stays busy
+// through the barriers:
+//   warp 13      producer: walks the whole weight schedule (every phase of every step) and pulls
+//                this CTA's share through an 8 x 16 KB shared-memory ring, one 1-D TMA bulk copy
+//                per [128 rows x 64 k] tile.  The matrices are stored tile-major and pre-swizzled
+//                (tcd.h), so a tile lands as a ready 128B-swizzled K-major operand and a CTA's
+//                share of a matrix is one contiguous region of HBM.
+//   warp 12      MMA issuer: A = weight tile from the ring, B = the activation vector as
+//                [8 x 64 k] operand blocks (row 0 = bf16 hi part, row 1 = bf16 lo part, rows 2-7
+//                zero; hi + lo is ~fp32 accurate), D[128, 8] fp32 in TMEM; tcgen05.commit hands
+//                ring stages back to the producer and finished accumulators to the epilogue.
+//   warps 0-3    epilogue: tcgen05.ld of the warp's 32 accumulator lanes (= weight rows),
+//                (col 0 + col 1) * norm scale, then red.global.add / store.
+//   warps 0-11   phase prologues (activation vector -> operand blocks, fused RMSNorm / SwiGLU /
+//                embedding), attention, sampling, the grid barrier.
+// Work split: the (row tile, k block) units of a matrix are numbered tile-major and cut into 148
+// equal contiguous ranges (stream-K), so every CTA streams the same number of bytes (+-16 KB) in
+// every phase; partial sums of a tile meet in global memory with fp32 red.add (the residual
+// stream takes them directly, qkv and gate/up go to zeroed buffers whose consumers apply RoPE /
+// SwiGLU on load).  The lm_head is cut at tile boundaries instead so that logits are plain stores.
+#include "common.cuh"
+#include "kernels.h"
+#include "tcd.h"
+
+namespace b200 {
+
+constexpr int kTC = 384;              // compute threads
+constexpr int kTW = kTC / 32;         // compute warps
+constexpr int kTThreads = kTC + 64;   // + MMA issuer warp + producer warp
+constexpr int kTStages = 8;
+constexpr int kTStageBytes = 16384;   // [128 rows x 64 k] bf16
+constexpr int kTBSlots = 64;          // activation operand blocks ([8 x 64 k] bf16 = 1 KB each)
+constexpr int kTAcc = 8;              // accumulators in flight (16 TMEM columns apart)
+constexpr int kTAccCols = 16;
+constexpr int kTPT = 16;              // tokens per KV page
+constexpr int kTMaxPtab = 448;        // page-table entries kept in shared memory
+constexpr int kTMaxJobs = 4 * 32 + 1;
+
+struct TcdSmem {
+    uint8_t *ring, *bop;
+    float *mrg;            // attention merge buffer [kTW][GQ][HD + 2]
+    uint64_t *full, *empty, *acc_full, *acc_empty;
+    uint32_t *tmem_slot;
+    float *red;
+    int *misc;
+    float *rope;           // [head_dim/2][cos, sin] of the current position
+    int32_t *ptab;
+    TcdJob *jobs;
+};
+
+__host__ __device__ __forceinline__ size_t tcd_mrg_bytes(int hd, int gq) { return (size_t)kTW * gq * (hd + 2) * 4; }
+
+__device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq) {
+    TcdSmem s;
+    s.ring = base;
+    s.bop = base + kTStages * kTStageBytes;
+    s.mrg = reinterpret_cast<float *>(s.bop + kTBSlots * 1024);
+    uint8_t *q = reinterpret_cast<uint8_t *>(s.mrg) + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15);
+    s.full = reinterpret_cast<uint64_t *>(q);
+    s.empty = s.full + kTStages;
+    s.acc_full = s.empty + kTStages;
+    s.acc_empty = s.acc_full + kTAcc;
+    s.tmem_slot = reinterpret_cast<uint32_t *>(s.acc_empty + kTAcc);
+    s.red = reinterpret_cast<float *>(s.tmem_slot + 4);
+    s.misc = reinterpret_cast<int *>(s.red + 64);
+    s.rope = reinterpret_cast<float *>(s.misc + 64);
+    s.ptab = reinterpret_cast<int32_t *>(s.rope + 128);
+    s.jobs = reinterpret_cast<TcdJob *>(s.ptab + kTMaxPtab);
+    return s;
+}
+
+static size_t tcd_smem_bytes(int hd, int gq, int n_jobs) {
+    return (size_t)kTStages * kTStageBytes + (size_t)kTBSlots * 1024 + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) +
+           (2 * kTStages + 2 * kTAcc) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 + kTMaxPtab * 4 + (size_t)n_jobs * sizeof(TcdJob) +
+           1024;  // slack for the 1024-byte alignment of the base
+}
+
+// This CTA's contiguous range [g0, g1) of the matrix's (row tile, k block) units, unit g = tile * nkb + kb.
+struct TRange {
+    int g0, g1, nkb;
+};
+__host__ __device__ __forceinline__ TRange tcd_range(int N, int K, bool whole_tiles, int G, int bid) {
+    TRange r;
+    r.nkb = K / 64;
+    const int n_units = whole_tiles ? N / 128 : (N / 128) * r.nkb;
+    const int base = n_units / G, rem = n_units % G;
+    const int u0 = bid * base + (bid < rem ? bid : rem);
+    const int u1 = u0 + base + (bid < rem ? 1 : 0);
+    r.g0 = whole_tiles ? u0 * r.nkb : u0;
+    r.g1 = whole_tiles ? u1 * r.nkb : u1;
+    return r;
+}
+
+bool tcd_job_fits(int N, int K, bool whole_tiles) {
+    if (N % 128 != 0 || K % 64 != 0 || N < 128 || K < 64) return false;
+    const TRange r = tcd_range(N, K, whole_tiles, kNumSMs, 0);  // CTA 0 has the largest share
+    const int need = (r.g1 - r.g0) < r.nkb ? (r.g1 - r.g0) : r.nkb;
+    return need <= kTBSlots;
+}
+
+bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab) {
+    const int G = n_kv > 0 ? n_q / n_kv : 0;
+    if (!(head_dim == 64 || head_dim == 128) || G < 1 || G > 4 || G == 3 && head_dim == 64) return false;
+    const int qd = n_q * head_dim, qkv = (n_q + 2 * n_kv) * head_dim;
+    return tcd_job_fits(qkv, d, false) && tcd_job_fits(d, qd, false) && tcd_job_fits(2 * ffn, d, false) &&
+           tcd_job_fits(d, ffn, false) && tcd_job_fits(vocab, d, true);
+}
+
+__device__ __forceinline__ bool tcd_whole(const TcdParams &p, int j, int n_jobs) {
+    return j == n_jobs - 1 && !p.split_all;
+}
+
+// Grid barrier for the compute threads (producer and MMA warps never take part); see decode_mega.cu.
+__device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, int tid) {
+    bar_sync(1, kTC);
+    if (tid == 0) {
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+        unsigned v;
+        do {
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+        } while (v < target);
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
+    }
+    bar_sync(1, kTC);
+}
+
+// ---------------------------------------------------------------- producer: the weight stream
+__device__ void tcd_producer(const TcdParams &p, const TcdSmem &s, int G, int bid) {
+    const uint64_t pol = l2_policy_evict_first();
+    const int n_jobs = 4 * p.n_layers + 1;
+    uint32_t gs = 0;
+    for (int step = 0; step < p.n_steps; ++step) {
+        for (int j = 0; j < n_jobs; ++j) {
+            const TcdJob &job = s.jobs[j];
+            const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
+            const uint8_t *src = reinterpret_cast<const uint8_t *>(job.w) + (size_t)r.g0 * kTStageBytes;
+            for (int g = r.g0; g < r.g1; ++g, ++gs, src += kTStageBytes) {
+                const uint32_t slot = gs % kTStages, use = gs / kTStages;
+                if (use > 0) mbar_wait(&s.empty[slot], (use - 1) & 1);
+                mbar_expect_tx(&s.full[slot], kTStageBytes);
+                tma_load_1d_hint(s.ring + (size_t)slot * kTStageBytes, src, kTStageBytes, &s.full[slot], pol);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- MMA issuer
+// K-major operand tile, 128-byte swizzle: rows of 128 bytes, 8-row groups `sbo` bytes apart
+__device__ __forceinline__ uint64_t tcd_desc(uint32_t smem_addr, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(sbo >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+__device__ __forceinline__ void tcd_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+
+__device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem) {
+    const int n_jobs = 4 * p.n_layers + 1;
+    // D fp32, A/B bf16, both K-major, M = 128, N = umma_n
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.umma_n >> 3) << 17) | ((128u >> 4) << 24);
+    const uint32_t ring_a = smem_u32(s.ring), bop_a = smem_u32(s.bop);
+    uint32_t gs = 0, as = 0;
+    for (int step = 0; step < p.n_steps; ++step) {
+        for (int j = 0; j < n_jobs; ++j) {
+            const TcdJob &job = s.jobs[j];
+            const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
+            bar_sync(2, kTC + 32);  // the activation operand of this phase is in shared memory
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int kb_start = r.g0 % r.nkb;
+            for (int g = r.g0; lane == 0 && g < r.g1;) {
+                const int t = g / r.nkb;
+                const int seg_end = min(r.g1, (t + 1) * r.nkb);
+                const uint32_t aslot = as % kTAcc;
+                if (as >= kTAcc) {
+                    mbar_wait(&s.acc_empty[aslot], ((as / kTAcc) - 1) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                }
+                const uint32_t d_addr = tmem + aslot * kTAccCols;
+                bool first = true;
+                for (; g < seg_end; ++g, ++gs) {
+                    const uint32_t slot = gs % kTStages, use = gs / kTStages;
+                    int bslot = g % r.nkb - kb_start;
+                    bslot += bslot < 0 ? r.nkb : 0;
+                    mbar_wait(&s.full[slot], use & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint64_t adesc = tcd_desc(ring_a + slot * kTStageBytes, 1024);
+                    const uint64_t bdesc = tcd_desc(bop_a + (uint32_t)bslot * 1024, 0);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t accum = (first && k == 0) ? 0u : 1u;
+                        asm volatile(
+                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_addr),
+                            "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc + (uint64_t)(2 * k)), "r"(idesc), "r"(accum)
+                            : "memory");
+                    }
+                    first = false;
+                    tcd_commit(&s.empty[slot]);  // frees the ring stage once the MMAs above have read it
+                }
+                tcd_commit(&s.acc_full[aslot]);
+                ++as;
+            }
+            __syncwarp();
+        }
+    }
+}
+
+struct TcdCtx {
+    int tok, pos;
+    int ti;               // trace cursor (-1: tracing off for this step)
+    uint32_t as;          // accumulator counter, in lock-step with the MMA issuer
+    float best;           // lm_head: running (max, argmax) of this thread
+    int best_i;
+};
+
+__device__ __forceinline__ void tcd_trace(const TcdParams &p, int &ti, int bid, int tid) {
+    if (ti >= 0 && tid == 0 && ti < 1000) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.trace[(bid ? 1024 : 0) + ti++] = t;
+    }
+}
+
+__device__ __forceinline__ uint32_t tcd_pack_bf16(float a, float b) {
+    return (uint32_t)f32_to_bf16_bits(a) | ((uint32_t)f32_to_bf16_bits(b) << 16);
+}
+__device__ __forceinline__ float tcd_bf16_round(float a) { return __uint_as_float((uint32_t)f32_to_bf16_bits(a) << 16); }
+
+#include "decode_tc_phase.cuh"
+#include "decode_tc_attn.cuh"
+#include "decode_tc_kernel.cuh"
+
+}  // namespace b200

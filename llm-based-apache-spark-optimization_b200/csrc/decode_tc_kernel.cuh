@@ -1,0 +1,196 @@
+// decode_tc_kernel.cuh -- the tcgen05 persistent decode kernel and its launcher (included by decode_tc.cu).
+#pragma once
+
+template <int HD, int GQ>
+__global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_constant__ TcdParams p) {
+    extern __shared__ uint8_t smem_dyn[];
+    // the swizzled operand tiles need 1024-byte alignment
+    uint8_t *smem_raw = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
+    const TcdSmem s = tcd_carve(smem_raw, HD, GQ);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int G = gridDim.x, bid = blockIdx.x;
+    const int n_jobs = 4 * p.n_layers + 1;
+
+    if (tid == 0) {
+        for (int i = 0; i < kTStages; ++i) {
+            mbar_init(&s.full[i], 1);
+            mbar_init(&s.empty[i], 1);
+        }
+        for (int i = 0; i < kTAcc; ++i) {
+            mbar_init(&s.acc_full[i], 1);
+            mbar_init(&s.acc_empty[i], 4);
+        }
+        mbar_fence_init();
+    }
+    if (warp == kTW) {  // TMEM: kTAcc accumulators of kTAccCols columns
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s.tmem_slot)),
+                     "r"((uint32_t)(kTAcc * kTAccCols))
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {   // phase descriptors and page table -> shared memory (read once); operand blocks start as zero
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(p.jobs);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(s.jobs);
+        for (int i = tid; i < n_jobs * (int)(sizeof(TcdJob) / 4); i += kTThreads) dst[i] = src[i];
+        for (int i = tid; i < min(p.n_ptab, kTMaxPtab); i += kTThreads) s.ptab[i] = p.page_table[i];
+        for (int i = tid; i < kTBSlots * 1024 / 16; i += kTThreads) reinterpret_cast<uint4 *>(s.bop)[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = *s.tmem_slot;
+
+    if (warp == kTW + 1) {
+        if (lane == 0) tcd_producer(p, s, G, bid);
+    } else if (warp == kTW) {
+        tcd_mma_warp(p, s, G, bid, lane, tmem);
+    } else {
+        TcdCtx c;
+        c.as = 0;
+        c.tok = __ldcg(p.lane_token + p.lane);
+        c.pos = __ldcg(p.lane_pos + p.lane);
+        unsigned bar_no = 0;
+        // one weight-streaming phase, compute-warp side
+        auto phase = [&](int j) {
+            const TcdJob &job = s.jobs[j];
+            const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
+            const float sc = tcd_prologue(p, job, s, c, r, G, bid, tid);
+            tcd_trace(p, c.ti, bid, tid);
+            if (warp < 4) tcd_epilogue(p, job, s, c, r, sc, warp, lane, tmem);
+            tcd_trace(p, c.ti, bid, tid);
+        };
+        for (int step = 0; step < p.n_steps; ++step) {
+            c.ti = (p.trace != nullptr && step == p.trace_step && (bid == 0 || bid == G - 1)) ? 0 : -1;
+            tcd_trace(p, c.ti, bid, tid);
+            c.tok = min(max(c.tok, 0), p.vocab - 1);
+            if (bid == 0 && tid == 0) p.lane_hist[(size_t)p.lane * 64 + (c.pos & 63)] = c.tok;
+            if (tid < HD / 2) {  // RoPE angles of this position
+                float sn, cs;
+                sincosf((float)c.pos * p.inv_freq[tid], &sn, &cs);
+                s.rope[2 * tid] = cs, s.rope[2 * tid + 1] = sn;
+            }
+            for (int l = 0; l < p.n_layers; ++l) {
+                const TcdJob &qkv_job = s.jobs[4 * l];
+                tcd_attn_prefetch<HD>(p, qkv_job, s, c, G, bid, tid);
+                phase(4 * l);      // rmsnorm + qkv (raw sums)
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_trace(p, c.ti, bid, tid);
+                tcd_attn_phase<HD, GQ>(p, qkv_job, s, c, G, bid, tid);  // rope + kv append + attention
+                tcd_trace(p, c.ti, bid, tid);
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_trace(p, c.ti, bid, tid);
+                phase(4 * l + 1);  // o_proj + residual
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_trace(p, c.ti, bid, tid);
+                phase(4 * l + 2);  // rmsnorm + gate/up (raw sums)
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_trace(p, c.ti, bid, tid);
+                phase(4 * l + 3);  // swiglu + down + residual
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_trace(p, c.ti, bid, tid);
+            }
+            // ---- final norm + lm_head: logits, per-CTA (max, lowest argmax) ----
+            c.best = -INFINITY, c.best_i = 0x7fffffff;
+            phase(n_jobs - 1);
+            {
+                float m = c.best;
+                int mi = c.best_i;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+                    const int oi = __shfl_xor_sync(0xffffffffu, mi, o);
+                    if (om > m || (om == m && oi < mi)) m = om, mi = oi;
+                }
+                bar_sync(1, kTC);
+                if (lane == 0) s.red[warp] = m, s.misc[4 + warp] = mi;
+                bar_sync(1, kTC);
+                if (tid == 0) {
+                    for (int w = 1; w < kTW; ++w)
+                        if (s.red[w] > m || (s.red[w] == m && s.misc[4 + w] < mi)) m = s.red[w], mi = s.misc[4 + w];
+                    p.part_max[bid] = m;
+                    p.part_idx[bid] = mi;
+                }
+            }
+            tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+            if (!p.sample) break;  // caller samples from the logits (temperature > 0)
+            // ---- greedy sampling: every CTA reduces the G partials redundantly (no extra barrier) ----
+            {
+                float m = -INFINITY;
+                int mi = 0x7fffffff;
+                for (int i = tid; i < G; i += kTC) {
+                    const float v = __ldcg(p.part_max + i);
+                    const int vi = __ldcg(p.part_idx + i);
+                    if (v > m || (v == m && vi < mi)) m = v, mi = vi;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+                    const int oi = __shfl_xor_sync(0xffffffffu, mi, o);
+                    if (om > m || (om == m && oi < mi)) m = om, mi = oi;
+                }
+                if (lane == 0) s.red[32 + warp] = m, s.misc[24 + warp] = mi;
+                bar_sync(1, kTC);
+                for (int w = 0; w < kTW; ++w) {
+                    const float om = s.red[32 + w];
+                    const int oi = s.misc[24 + w];
+                    if (om > m || (om == m && oi < mi)) m = om, mi = oi;
+                }
+                c.tok = mi;
+                c.pos += 1;
+                if (bid == 0 && tid == 0) {
+                    p.lane_token[p.lane] = c.tok;
+                    p.lane_pos[p.lane] = c.pos;
+                    p.gen_out[step] = c.tok;
+                }
+                bar_sync(1, kTC);  // red/misc are reused by the next step
+            }
+        }
+    }
+    // every role has finished its schedule: all MMAs are committed and read back
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == kTW)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)(kTAcc * kTAccCols))
+                     : "memory");
+}
+
+template <int HD, int GQ>
+static int tcd_launch_t(const TcdParams &p, cudaStream_t stream) {
+    const size_t smem = tcd_smem_bytes(HD, GQ, 4 * p.n_layers + 1);
+    B200_REQUIRE(smem <= 232448, "tcd: %zu bytes of shared memory needed", smem);
+    B200_CUDA_OK(cudaFuncSetAttribute(tcd_decode_kernel<HD, GQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int dev = 0, sms = 0;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    B200_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    B200_REQUIRE(sms == kNumSMs, "tcd: built for %d SMs, device has %d", kNumSMs, sms);
+    B200_CUDA_OK(cudaMemsetAsync(p.bar_ctr, 0, sizeof(unsigned), stream));
+    // cooperative launch: all CTAs must be co-resident, the grid barrier depends on it
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(sms);
+    cfg.blockDim = dim3(kTThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, tcd_decode_kernel<HD, GQ>, p));
+    return B200LLM_OK;
+}
+
+int tcd_decode_launch(const TcdParams &p, cudaStream_t stream) {
+    B200_REQUIRE(p.n_steps >= 1 && (p.sample || p.n_steps == 1), "tcd: n_steps must be 1 when sampling is external");
+    B200_REQUIRE(p.n_splits >= 1, "tcd: n_splits < 1");
+    B200_REQUIRE(4 * p.n_layers + 1 <= kTMaxJobs, "tcd: more than 32 layers");
+    B200_REQUIRE(p.umma_n == 8 || p.umma_n == 16, "tcd: umma_n must be 8 or 16");
+    const int GQ = p.n_kv > 0 ? p.n_q / p.n_kv : 1;
+#define B200_TCD_CASE(HD_, G_) \
+    if (p.head_dim == HD_ && GQ == G_) return tcd_launch_t<HD_, G_>(p, stream);
+    B200_TCD_CASE(128, 1) B200_TCD_CASE(128, 2) B200_TCD_CASE(128, 3) B200_TCD_CASE(128, 4)
+    B200_TCD_CASE(64, 1) B200_TCD_CASE(64, 2) B200_TCD_CASE(64, 4)
+#undef B200_TCD_CASE
+    set_error("tcd: unsupported head_dim %d / group %d", p.head_dim, GQ);
+    return B200LLM_EINVAL;
+}

@@ -1,0 +1,147 @@
+// decode_tc_phase.cuh -- compute-warp side of one weight-streaming phase of decode_tc.cu:
+// the prologue that turns the activation vector into tcgen05 B-operand blocks, and the
+// epilogue that drains finished accumulators out of TMEM.
+#pragma once
+
+// ---- prologue -------------------------------------------------------------------------------
+// Operand block `slot` (1 KB, 1024-byte aligned) is an [8 rows x 64 k] bf16 K-major tile with the
+// 128-byte swizzle: row r at +128 r, its 16-byte chunk c at chunk position c ^ r.  Row 0 holds
+// the bf16 hi parts of 64 activations, row 1 the lo parts (x - hi), rows 2..7 stay zero.
+// A CTA only needs the k blocks its unit range touches: block kb goes to slot
+// (kb - kb_start) mod nkb, where kb_start is the k block of the range's first unit.
+// Returns the RMSNorm scale rsqrt(mean(x^2) + eps) (1 when the phase has no norm); the scale
+// is applied in the epilogue (it is a scalar factor of the whole dot product).
+__device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSmem &s, TcdCtx &c, const TRange &r,
+                              int G, int bid, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int K = job.K, nkb = r.nkb;
+    const int kb_start = r.g0 % nkb;
+    const int n_slots = min(r.g1 - r.g0, nkb);
+    const int x_kind = job.x_src & 0xff;
+    const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
+
+    {   // the RMSNorm gain vectors of the next two phases are cold (read once per step): pull them into L2
+        const TcdJob *first = s.jobs, *last = s.jobs + 4 * p.n_layers;
+#pragma unroll
+        for (int a = 1; a <= 2; ++a) {
+            const TcdJob *nj = &job + a;
+            if (nj > last) nj = first + (nj - last - 1);
+            if (nj->gain != nullptr && tid * 64 < nj->K)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint16_t *>(nj->gain) + tid * 64));
+        }
+    }
+    if (job.x_src & 0x100) {  // clear the sum buffers the next qkv / gate-up phases add into
+        const int nq4 = (p.n_q + 2 * p.n_kv) * p.head_dim / 4, ng4 = 2 * p.ffn / 4;
+        for (int i = bid * kTC + tid; i < nq4 + ng4; i += G * kTC) {
+            float4 *dst = i < nq4 ? reinterpret_cast<float4 *>(p.qkv) + i : reinterpret_cast<float4 *>(p.gu) + (i - nq4);
+            *dst = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    // phases with a norm (or that seed the residual stream from the embedding) read the whole
+    // vector; the others only the chunks (8 values) of the k blocks this CTA streams
+    const bool full_scan = gain != nullptr || x_kind == TCD_X_EMBED;
+    const int n_iter = full_scan ? K / 8 : n_slots * 8;
+    const uint16_t *emb = reinterpret_cast<const uint16_t *>(p.embed) + (size_t)c.tok * p.d;
+    const float *xsrc = x_kind == TCD_X_ATT ? p.att : p.h;
+    float ss = 0.f;
+#pragma unroll 2
+    for (int idx = tid; idx < n_iter; idx += kTC) {
+        int chunk, slot;
+        if (full_scan) {
+            chunk = idx;
+            slot = (chunk >> 3) - kb_start;
+            slot += slot < 0 ? nkb : 0;
+        } else {
+            slot = idx >> 3;
+            int kb = kb_start + slot;
+            kb -= kb >= nkb ? nkb : 0;
+            chunk = kb * 8 + (idx & 7);
+        }
+        float v[8];
+        if (x_kind == TCD_X_EMBED) {
+            const uint4 u = *reinterpret_cast<const uint4 *>(emb + chunk * 8);
+            v[0] = bf16lo(u.x), v[1] = bf16hi(u.x), v[2] = bf16lo(u.y), v[3] = bf16hi(u.y);
+            v[4] = bf16lo(u.z), v[5] = bf16hi(u.z), v[6] = bf16lo(u.w), v[7] = bf16hi(u.w);
+            if ((chunk % G) == bid) {  // residual stream h <- embedding row, each element written once
+                *reinterpret_cast<float4 *>(p.h + chunk * 8) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4 *>(p.h + chunk * 8 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+            }
+        } else if (x_kind == TCD_X_SWIGLU) {
+            const float4 *gp = reinterpret_cast<const float4 *>(p.gu + (size_t)chunk * 16);
+            const float4 a = __ldcg(gp), b = __ldcg(gp + 1), cc = __ldcg(gp + 2), d = __ldcg(gp + 3);
+            v[0] = (a.x / (1.f + expf(-a.x))) * a.y, v[1] = (a.z / (1.f + expf(-a.z))) * a.w;
+            v[2] = (b.x / (1.f + expf(-b.x))) * b.y, v[3] = (b.z / (1.f + expf(-b.z))) * b.w;
+            v[4] = (cc.x / (1.f + expf(-cc.x))) * cc.y, v[5] = (cc.z / (1.f + expf(-cc.z))) * cc.w;
+            v[6] = (d.x / (1.f + expf(-d.x))) * d.y, v[7] = (d.z / (1.f + expf(-d.z))) * d.w;
+        } else {
+            const float4 a = __ldcg(reinterpret_cast<const float4 *>(xsrc + chunk * 8));
+            const float4 b = __ldcg(reinterpret_cast<const float4 *>(xsrc + chunk * 8 + 4));
+            v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss = fmaf(v[e], v[e], ss);
+        if (slot >= n_slots) continue;
+        if (gain != nullptr) {
+            const uint4 g = *reinterpret_cast<const uint4 *>(gain + chunk * 8);
+            v[0] *= bf16lo(g.x), v[1] *= bf16hi(g.x), v[2] *= bf16lo(g.y), v[3] *= bf16hi(g.y);
+            v[4] *= bf16lo(g.z), v[5] *= bf16hi(g.z), v[6] *= bf16lo(g.w), v[7] *= bf16hi(g.w);
+        }
+        float hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) hi[e] = tcd_bf16_round(v[e]), lo[e] = v[e] - hi[e];
+        uint8_t *blk = s.bop + (size_t)slot * 1024;
+        const int c8 = chunk & 7;
+        *reinterpret_cast<uint4 *>(blk + c8 * 16) = make_uint4(tcd_pack_bf16(hi[0], hi[1]), tcd_pack_bf16(hi[2], hi[3]),
+                                                               tcd_pack_bf16(hi[4], hi[5]), tcd_pack_bf16(hi[6], hi[7]));
+        *reinterpret_cast<uint4 *>(blk + 128 + (c8 ^ 1) * 16) =
+            make_uint4(tcd_pack_bf16(lo[0], lo[1]), tcd_pack_bf16(lo[2], lo[3]), tcd_pack_bf16(lo[4], lo[5]),
+                       tcd_pack_bf16(lo[6], lo[7]));
+    }
+    // generic-proxy writes above -> visible to the async proxy (tcgen05.mma reads the blocks)
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (gain != nullptr) {
+        ss = warp_sum(ss);
+        if (lane == 0) s.red[warp] = ss;
+    }
+    tcd_trace(p, c.ti, bid, tid);
+    bar_sync(2, kTC + 32);  // with the MMA issuer warp: operand blocks (and the norm partials) are complete
+    float sc = 1.f;
+    if (gain != nullptr) {
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < kTW; ++w) tot += s.red[w];
+        sc = rsqrtf(tot / (float)K + p.rms_eps);
+    }
+    return sc;
+}
+
+// ---- epilogue (warps 0..3) ----------------------------------------------------------------------
+// One accumulator per (row tile) segment of the CTA's range: lane i of warp w owns TMEM lane
+// 32 w + i = weight row 128 t + 32 w + i; columns 0 and 1 are the hi and lo partial dot products.
+__device__ void tcd_epilogue(const TcdParams &p, const TcdJob &job, const TcdSmem &s, TcdCtx &c, const TRange &r,
+                             float sc, int warp, int lane, uint32_t tmem) {
+    for (int g = r.g0; g < r.g1;) {
+        const int t = g / r.nkb;
+        const int seg_end = min(r.g1, (t + 1) * r.nkb);
+        const uint32_t aslot = c.as % kTAcc;
+        mbar_wait(&s.acc_full[aslot], (c.as / kTAcc) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        uint32_t r0, r1;
+        const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + aslot * kTAccCols;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(taddr) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s.acc_empty[aslot]);
+        const float v = (__uint_as_float(r0) + __uint_as_float(r1)) * sc;
+        const int n = t * 128 + warp * 32 + lane;
+        if (job.epi == TCD_EPI_ADD) {
+            asm volatile("red.global.add.f32 [%0], %1;" ::"l"(job.out + n), "f"(v) : "memory");
+        } else {
+            job.out[n] = v;
+            if (v > c.best) c.best = v, c.best_i = n;
+        }
+        ++c.as;
+        g = seg_end;
+    }
+}

@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "mega.h"
+#include "tcd.h"
 
 namespace b200 {
 
@@ -95,6 +96,7 @@ struct LayerW {
     const void *attn_norm = nullptr, *wqkv = nullptr, *wo = nullptr, *mlp_norm = nullptr, *wgu = nullptr,
                *wdown = nullptr;
     const void *wqkv_st = nullptr, *wo_st = nullptr, *wgu_st = nullptr, *wdown_st = nullptr;  // stage-major copies
+    const void *wqkv_tm = nullptr, *wo_tm = nullptr, *wgu_tm = nullptr, *wdown_tm = nullptr;  // tile-major copies
 };
 
 struct b200llm_engine {
@@ -104,7 +106,7 @@ struct b200llm_engine {
     bool own_stream = false;
     bool pdl = false;
     // weights
-    const void *embed = nullptr, *lm_head = nullptr, *final_norm = nullptr, *lm_head_st = nullptr;
+    const void *embed = nullptr, *lm_head = nullptr, *final_norm = nullptr, *lm_head_st = nullptr, *lm_head_tm = nullptr;
     const float *inv_freq = nullptr;
     std::vector<LayerW> layers;
     bool weights_bound = false;
@@ -130,6 +132,7 @@ struct b200llm_engine {
     struct MapBox { alignas(128) unsigned char b[128]; };
     std::map<std::tuple<const void *, int64_t, int64_t, int>, MapBox *> maps;
     bool mega_ready = false;
+    bool tcd_ready = false;
     std::vector<b200llm_sampling> samp_host;
     b200llm_sampling *lane_samp;
     void *attn_scratch;
@@ -225,7 +228,7 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->gath_max = take(R * tp * w->lm_grid * 4);
     w->gath_idx = take(R * tp * w->lm_grid * 4);
     w->attn_scratch = take(w->attn_scratch_bytes);
-    w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * sizeof(MegaJob));
+    w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * (sizeof(MegaJob) > sizeof(TcdJob) ? sizeof(MegaJob) : sizeof(TcdJob)));
     w->bar_ctr = take(256);
     w->trace = take(2048 * 8);
     {   // batch / prefill path (tcgen05 GEMM): bf16 activations and fp32 GEMM outputs
@@ -386,7 +389,7 @@ int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, in
             return true;
         };
         const int64_t qkv_rows = (int64_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim;
-        if (t.kind >= B200LLM_W_ATTN_NORM && t.kind != B200LLM_W_LM_HEAD_ST) B200_REQUIRE(t.layer >= 0 && t.layer < c.n_layers, "tensor %d: bad layer", i);
+        if (t.kind >= B200LLM_W_ATTN_NORM && t.kind != B200LLM_W_LM_HEAD_ST && t.kind != B200LLM_W_LM_HEAD_TM) B200_REQUIRE(t.layer >= 0 && t.layer < c.n_layers, "tensor %d: bad layer", i);
         switch (t.kind) {
             case B200LLM_W_EMBED: if (!shape(c.vocab, c.d)) return B200LLM_EINVAL; e->embed = t.dev; break;
             case B200LLM_W_LM_HEAD: if (!shape(e->vocab_l, c.d)) return B200LLM_EINVAL; e->lm_head = t.dev; break;
@@ -403,6 +406,11 @@ int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, in
             case B200LLM_W_GATE_UP_ST: if (!shape(2 * (int64_t)e->ffn_l, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wgu_st = t.dev; break;
             case B200LLM_W_DOWN_ST: if (!shape(c.d, e->ffn_l)) return B200LLM_EINVAL; e->layers[t.layer].wdown_st = t.dev; break;
             case B200LLM_W_LM_HEAD_ST: if (!shape(e->vocab_l, c.d)) return B200LLM_EINVAL; e->lm_head_st = t.dev; break;
+            case B200LLM_W_QKV_TM: if (!shape(qkv_rows, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wqkv_tm = t.dev; break;
+            case B200LLM_W_O_TM: if (!shape(c.d, (int64_t)e->nq_l * c.head_dim)) return B200LLM_EINVAL; e->layers[t.layer].wo_tm = t.dev; break;
+            case B200LLM_W_GATE_UP_TM: if (!shape(2 * (int64_t)e->ffn_l, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wgu_tm = t.dev; break;
+            case B200LLM_W_DOWN_TM: if (!shape(c.d, e->ffn_l)) return B200LLM_EINVAL; e->layers[t.layer].wdown_tm = t.dev; break;
+            case B200LLM_W_LM_HEAD_TM: if (!shape(e->vocab_l, c.d)) return B200LLM_EINVAL; e->lm_head_tm = t.dev; break;
             default: set_error("tensor %d: unknown kind %d", i, t.kind); return B200LLM_EINVAL;
         }
     }
@@ -454,6 +462,7 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->trace = (unsigned long long *)(b + w.trace);
     e->xb = (uint16_t *)(b + w.xb), e->qkv_out = (float *)(b + w.qkv_out), e->gu_out = (float *)(b + w.gu_out);
     e->mega_ready = false;
+    e->tcd_ready = false;
     e->samp_host.assign(e->cfg.max_lanes, b200llm_sampling{0.f, 0, 1.f, 1.f, 0});
     // zero everything once: attention tickets must start at zero, lanes at token 0 / pos 0,
     // sampling = greedy, page tables -> page 0
@@ -667,6 +676,7 @@ static int mega_prepare(b200llm_engine *e) {
                                  e->stream));
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));  // `jobs` is a pageable temporary
     e->mega_ready = true;
+    e->tcd_ready = false;
     return B200LLM_OK;
 }
 
@@ -705,6 +715,70 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     e->last_rows = 1, e->last_logit_rows = 1;
     return mega_decode_launch(p, e->stream);
+}
+
+// ---------------------------------------------------------------- persistent batch-1 decode, tcgen05 consumer
+static bool tcd_usable(const b200llm_engine *e) {
+    const b200llm_config &c = e->cfg;
+    if (getenv("B200LLM_NO_TCD")) return false;
+    bool tiled = e->lm_head_tm != nullptr;
+    for (auto &w : e->layers) tiled = tiled && w.wqkv_tm && w.wo_tm && w.wgu_tm && w.wdown_tm;
+    return tiled && tcd_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim, c.vocab);
+}
+
+static int tcd_prepare(b200llm_engine *e) {
+    const b200llm_config &c = e->cfg;
+    std::vector<TcdJob> jobs(4 * c.n_layers + 1);
+    const int qd = c.n_q * c.head_dim;
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW &w = e->layers[l];
+        uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
+        jobs[4 * l + 0] = TcdJob{w.wqkv_tm, w.attn_norm, kl, kl + e->kv_half_stride, e->qkv_out,
+                                 (c.n_q + 2 * c.n_kv) * c.head_dim, c.d, TCD_EPI_ADD, l == 0 ? TCD_X_EMBED : TCD_X_H};
+        jobs[4 * l + 1] = TcdJob{w.wo_tm, nullptr, nullptr, nullptr, e->h, c.d, qd, TCD_EPI_ADD, TCD_X_ATT | 0x100};
+        jobs[4 * l + 2] = TcdJob{w.wgu_tm, w.mlp_norm, nullptr, nullptr, e->gu_out, 2 * c.ffn, c.d, TCD_EPI_ADD, TCD_X_H};
+        jobs[4 * l + 3] = TcdJob{w.wdown_tm, nullptr, nullptr, nullptr, e->h, c.d, c.ffn, TCD_EPI_ADD, TCD_X_SWIGLU};
+    }
+    jobs[4 * c.n_layers] = TcdJob{e->lm_head_tm, e->final_norm, nullptr, nullptr, e->logits, c.vocab, c.d, TCD_EPI_LOGITS, TCD_X_H};
+    B200_CUDA_OK(cudaMemcpyAsync(e->mega_jobs, jobs.data(), jobs.size() * sizeof(TcdJob), cudaMemcpyHostToDevice, e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));  // `jobs` is a pageable temporary
+    e->tcd_ready = true;
+    e->mega_ready = false;  // the two kernels share the descriptor array
+    return B200LLM_OK;
+}
+
+static int tcd_decode(b200llm_engine *e, int lane, int n_steps) {
+    const b200llm_config &c = e->cfg;
+    if (!e->tcd_ready) B200_TRY(tcd_prepare(e));
+    TcdParams p{};
+    p.jobs = reinterpret_cast<const TcdJob *>(e->mega_jobs), p.n_layers = c.n_layers;
+    p.d = c.d, p.n_q = c.n_q, p.n_kv = c.n_kv, p.head_dim = c.head_dim, p.ffn = c.ffn, p.vocab = c.vocab;
+    p.rms_eps = c.rms_eps;
+    p.scale_log2 = (float)(1.4426950408889634 / sqrt((double)c.head_dim));
+    p.h = e->h, p.qkv = e->qkv_out, p.att = e->att, p.gu = e->gu_out, p.logits = e->logits;
+    p.part_max = e->part_max, p.part_idx = e->part_idx;
+    p.embed = e->embed, p.inv_freq = e->inv_freq;
+    p.lane = lane, p.lane_token = e->lane_token, p.lane_pos = e->lane_pos, p.lane_hist = e->lane_hist;
+    p.page_table = e->page_table + (size_t)lane * c.max_pages_per_lane;
+    p.n_ptab = c.max_pages_per_lane;
+    p.gen_out = e->gen_out, p.n_steps = n_steps;
+    int ns = kNumSMs / c.n_kv;
+    ns = ns < 1 ? 1 : (ns > e->attn_splits ? e->attn_splits : ns);
+    p.n_splits = ns;
+    uint8_t *sc = reinterpret_cast<uint8_t *>(e->attn_scratch);
+    p.tickets = reinterpret_cast<unsigned *>(sc);
+    p.part_o = reinterpret_cast<float *>(sc + kAttnTicketBytes);
+    p.part_ml = p.part_o + (size_t)c.n_q * ns * c.head_dim;
+    p.bar_ctr = e->bar_ctr;
+    p.sample = 1;
+    p.umma_n = 8;
+    if (const char *un = getenv("B200LLM_UMMA_N")) p.umma_n = atoi(un);
+    if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
+    // the qkv and gate/up phases ADD into these rows; later layers find them cleared by the o_proj phase
+    B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)(c.n_q + 2 * c.n_kv) * c.head_dim * 4, e->stream));
+    B200_CUDA_OK(cudaMemsetAsync(e->gu_out, 0, (size_t)2 * c.ffn * 4, e->stream));
+    e->last_rows = 1, e->last_logit_rows = 1;
+    return tcd_decode_launch(p, e->stream);
 }
 
 // ---------------------------------------------------------------- batch / prefill pass (tcgen05 GEMM)
@@ -864,8 +938,11 @@ int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int
     B200_CUDA_OK(cudaEventRecord(e->ev[2], e->stream));
     const b200llm_sampling &sp0 = e->samp_host[lanes[0]];
     const bool greedy = sp0.temperature <= 0.f && sp0.repeat_penalty == 1.f;
-    if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy &&
-        mega_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim)) {
+    if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy && tcd_usable(e)) {
+        B200_TRY(tcd_decode(e, lanes[0], n_steps));
+        e->timing.kernel_launches = 1;
+    } else if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy &&
+               mega_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim)) {
         B200_TRY(mega_decode(e, lanes[0], n_steps));
         e->timing.kernel_launches = 1;
     } else if (c.use_graphs) {
@@ -969,6 +1046,41 @@ int b200llm_op_gemv_grid(int32_t N, int32_t K, int32_t bs, int32_t epi, int32_t 
     int g = gemv_grid(N, K, bs, epi, 0);
     B200_REQUIRE(g > 0, "op_gemv_grid: unsupported shape");
     *grid = g;
+    return B200LLM_OK;
+}
+
+int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, int32_t K, int32_t k_split,
+                       int32_t umma_n, void *stream) {
+    B200_REQUIRE(w_tm && x && out, "op_gemv_tm: NULL argument");
+    B200_REQUIRE(tcd_job_fits(N, K, !k_split), "op_gemv_tm: N %% 128, K %% 64, or the per-CTA share does not fit");
+    int rc = require_device_any();
+    if (rc) return rc;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    // scratch of this test entry point: one descriptor, per-CTA argmax partials, lane state, barrier counter
+    uint8_t *scr = nullptr;
+    B200_CUDA_OK(cudaMalloc(&scr, 8192));
+    B200_CUDA_OK(cudaMemsetAsync(scr, 0, 8192, st));
+    TcdJob job{w_tm, nullptr, nullptr, nullptr, out, N, K, k_split ? TCD_EPI_ADD : TCD_EPI_LOGITS, TCD_X_H};
+    B200_CUDA_OK(cudaMemcpyAsync(scr, &job, sizeof(job), cudaMemcpyHostToDevice, st));
+    if (k_split) B200_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)N * 4, st));
+    TcdParams p{};
+    p.jobs = reinterpret_cast<const TcdJob *>(scr), p.n_layers = 0;
+    p.d = K, p.n_q = 1, p.n_kv = 1, p.head_dim = 128, p.ffn = 0, p.vocab = N;
+    p.h = const_cast<float *>(x), p.logits = out;
+    p.part_max = reinterpret_cast<float *>(scr + 1024), p.part_idx = reinterpret_cast<int32_t *>(scr + 2048);
+    p.lane = 0, p.lane_token = reinterpret_cast<int32_t *>(scr + 3072), p.lane_pos = reinterpret_cast<int32_t *>(scr + 3200);
+    p.lane_hist = reinterpret_cast<int32_t *>(scr + 3328);
+    p.page_table = reinterpret_cast<const int32_t *>(scr + 3840), p.n_ptab = 0;
+    p.inv_freq = reinterpret_cast<const float *>(scr + 4096);
+    p.embed = x;
+    p.gen_out = reinterpret_cast<int32_t *>(scr + 3712), p.n_steps = 1, p.n_splits = 1;
+    p.bar_ctr = reinterpret_cast<unsigned *>(scr + 3776);
+    p.sample = 0, p.umma_n = umma_n, p.split_all = k_split ? 1 : 0;
+    rc = tcd_decode_launch(p, st);
+    cudaError_t ce = cudaStreamSynchronize(st);
+    cudaFree(scr);
+    if (rc) return rc;
+    B200_CUDA_OK(ce);
     return B200LLM_OK;
 }
 

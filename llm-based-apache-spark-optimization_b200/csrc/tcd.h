@@ -1,0 +1,66 @@
+// tcd.h -- parameters of the tcgen05 persistent batch-1 decode kernel (decode_tc.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// One weight-streaming phase: y (+)= W x over a whole matrix.  W is the TILE-MAJOR copy of the
+// matrix: [N/128 row tiles][K/64 k blocks][128 rows][64 k] bf16, every 16 KB tile stored the way
+// a 128-byte-swizzled K-major tcgen05 operand lies in shared memory, so that one 1-D bulk copy
+// drops a ready-to-use MMA operand into the ring (weights.py: tile_major()).
+struct TcdJob {
+    const void *w;        // tile-major bf16
+    const void *gain;     // bf16 [K] RMSNorm gain fused in front, or NULL
+    void *k_pages;        // qkv job: this layer's K / V page regions (used by the attention phase)
+    void *v_pages;
+    float *out;           // fp32 [N]: partial sums are added (TCD_EPI_ADD) or rows stored (TCD_EPI_LOGITS)
+    int32_t N, K;         // N % 128 == 0, K % 64 == 0
+    int32_t epi;          // TCD_EPI_*
+    int32_t x_src;        // TCD_X_* in the low byte; bit 8: this phase also clears the qkv and gate/up sum buffers
+};
+enum { TCD_EPI_ADD = 0, TCD_EPI_LOGITS = 1 };
+enum { TCD_X_H = 0, TCD_X_ATT = 1, TCD_X_SWIGLU = 2, TCD_X_EMBED = 3 };
+
+struct TcdParams {
+    const TcdJob *jobs;   // device array: 4 per layer (qkv, o, gate_up, down) + lm_head
+    int32_t n_layers;
+    int32_t d, n_q, n_kv, head_dim, ffn, vocab;
+    float rms_eps;
+    float scale_log2;     // log2(e) / sqrt(head_dim)
+    // activations (fp32), one row (batch 1)
+    float *h;             // residual stream [d]
+    float *qkv;           // raw q|k|v sums of the current layer [(n_q + 2 n_kv) * head_dim], q/k rows pair-interleaved
+    float *att;           // attention output [n_q * head_dim]
+    float *gu;            // raw gate/up sums [2 ffn], interleaved
+    float *logits;        // [vocab]
+    float *part_max;      // [grid]
+    int32_t *part_idx;    // [grid]
+    const void *embed;    // bf16 [vocab, d]
+    const float *inv_freq;
+    // lane state
+    int32_t lane;
+    int32_t *lane_token, *lane_pos, *lane_hist;
+    const int32_t *page_table;  // this lane's row
+    int32_t n_ptab;
+    int32_t *gen_out;     // [n_steps]
+    int32_t n_steps;
+    // attention split partials
+    float *part_o;        // [n_q, n_splits, head_dim]
+    float *part_ml;       // [n_q, n_splits, 2]
+    unsigned *tickets;    // [n_kv]
+    int32_t n_splits;
+    unsigned *bar_ctr;    // grid barrier counter (zeroed before every launch)
+    int32_t sample;       // 1: greedy argmax + feedback inside the kernel; 0: stop after the logits
+    int32_t umma_n;       // 8 or 16: N of the MMA instruction (columns 0/1 carry the result)
+    int32_t split_all;    // (test hook) k-split the last job too instead of giving whole tiles
+    unsigned long long *trace;  // optional [2][1024] globaltimer stamps of CTA 0 and CTA G-1 (debug)
+    int32_t trace_step;
+};
+
+int tcd_decode_launch(const TcdParams &p, cudaStream_t stream);
+bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab);
+// per-phase check that the activation operand of one CTA fits its 64 k-block buffer
+bool tcd_job_fits(int N, int K, bool whole_tiles);
+
+}  // namespace b200

@@ -260,3 +260,25 @@ def test_gemm_tc_matches_fp32_matmul(N, K, T, acc):
                                            torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     _close(out.cpu(), ref)
+
+
+@pytest.mark.parametrize("N,K", [(128, 64), (512, 256), (3072, 3072), (5120, 3072), (3072, 8192), (16384, 3072),
+                                 (4096, 11008), (128256, 2048)])
+@pytest.mark.parametrize("k_split", [0, 1])
+def test_gemv_tile_major_tcgen05_phase(N, K, k_split):
+    """One phase of the tcgen05 persistent decode kernel: tile-major weights, activation split into
+    bf16 hi + lo operand rows, fp32 accumulation in TMEM.  k_split = 1 is the stream-K mode (partial
+    sums meet with fp32 atomics), 0 the whole-tile mode the lm_head uses."""
+    from b200llm import _lib, weights
+    if k_split == 0 and K // 64 * ((N // 128 + 147) // 148) > 64 and K // 64 > 64:
+        pytest.skip("share of one CTA exceeds the operand buffer in whole-tile mode")
+    w = wg.gen_bf16((N, K), N * 17 + K, 0.05)
+    x = torch.randn(K, generator=torch.Generator().manual_seed(K + N))
+    ref = w.float() @ x
+    wt = weights.tile_major(w.cuda())
+    xd = x.cuda()
+    out = torch.full((N,), 7.0, device="cuda")
+    torch.cuda.synchronize()
+    _lib.check(_lib.lib.b200llm_op_gemv_tm(wt.data_ptr(), xd.data_ptr(), out.data_ptr(), N, K, k_split, 8,
+                                           torch.cuda.current_stream().cuda_stream))
+    _close(out.cpu(), ref, 2e-5)

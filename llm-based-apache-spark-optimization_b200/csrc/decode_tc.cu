@@ -222,15 +222,19 @@ struct TcdCtx {
     int tok, pos;
     int ti;               // trace cursor (-1: tracing off for this step)
     uint32_t as;          // accumulator counter, in lock-step with the MMA issuer
+    int att_ns;           // split-T factor of this step's attention phases
     float best;           // lm_head: running (max, argmax) of this thread
     int best_i;
 };
 
-__device__ __forceinline__ void tcd_trace(const TcdParams &p, int &ti, int bid, int tid) {
+// (debug) tagged globaltimer stamps of thread 0: tag in bits 48.., nanoseconds below
+enum { TT_STEP = 1, TT_XCONV = 2, TT_XREADY = 3, TT_EPI = 4, TT_BAR = 5, TT_ATT_Q = 6, TT_ATT_KV = 7, TT_ATT_WARPS = 8,
+       TT_ATT_DONE = 9 };
+__device__ __forceinline__ void tcd_trace(const TcdParams &p, int &ti, int bid, int tid, int tag) {
     if (ti >= 0 && tid == 0 && ti < 1000) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        p.trace[(bid ? 1024 : 0) + ti++] = t;
+        p.trace[(bid ? 1024 : 0) + ti++] = (t & 0xFFFFFFFFFFFFull) | ((unsigned long long)tag << 48);
     }
 }
 

@@ -7,7 +7,9 @@
 // q on load, and the current token's k/v by warp 0 of the item that owns the last page, which
 // rounds them to bf16, starts its running softmax with them and appends them to the KV page for
 // the steps to come.  The page loop masks the current position out of the cache reads.
-// Work items = (kv head, split); item i runs on CTA i % G.
+// Work items = (kv head, split); item i runs on CTA i % G.  With more than one split the items
+// leave (max, sum, unnormalised output) partials in part_ml / part_o and the next phase's
+// prologue merges them while it builds its operand (tcd_prologue, TCD_X_ATT).
 #pragma once
 
 __device__ __forceinline__ void prefetch_l2(const void *ptr) {
@@ -22,7 +24,7 @@ __device__ __forceinline__ void tcd_attn_prefetch(const TcdParams &p, const TcdJ
                                                    const TcdCtx &c, int G, int bid, int tid) {
     constexpr int LINES = kTPT * HD * 2 / 128;  // 128-byte lines per K (or V) page tile
     const int n_pages = c.pos / kTPT + 1;
-    const int ns = min(p.n_splits, (n_pages + 2 * kTW - 1) / (2 * kTW));
+    const int ns = min(p.n_splits, (n_pages + kTW - 1) / kTW);  // at most one page per warp while splits last
     const int pps = (n_pages + ns - 1) / ns;
     const int n_items = p.n_kv * ns;
     const uint8_t *kbase = reinterpret_cast<const uint8_t *>(qkv_job.k_pages);
@@ -47,7 +49,7 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
     const int warp = tid >> 5, lane = tid & 31;
     const int tg = lane >> 4, p16 = lane & 15;
     const int n_pages = c.pos / kTPT + 1;
-    const int ns = min(p.n_splits, (n_pages + 2 * kTW - 1) / (2 * kTW));
+    const int ns = min(p.n_splits, (n_pages + kTW - 1) / kTW);  // at most one page per warp while splits last
     const int pps = (n_pages + ns - 1) / ns;
     const int n_items = p.n_kv * ns;
     const uint16_t *kbase = reinterpret_cast<const uint16_t *>(qkv_job.k_pages);
@@ -74,7 +76,7 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
             for (int e = 0; e < EL; ++e) o[g][e] = 0.f;
             m[g] = -INFINITY, l[g] = 0.f;
         }
-        if (q[0][0] != 1.2345e30f) tcd_trace(p, c.ti, bid, tid);  // (debug) q arrived
+        if (c.ti >= 0 && q[0][0] != 1.2345e30f) tcd_trace(p, c.ti, bid, tid, TT_ATT_Q);  // (debug) q arrived
         if (split == own_split && warp == 0) {
             // the current token: k (RoPE) and v of this kv head from the raw sums, rounded to bf16 as
             // the cache holds them; both half-warps compute it, lanes 0..15 adopt and append it
@@ -141,6 +143,18 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
                         kr[it] = make_uint4(A.x, A.y, 0u, 0u);
                     }
                 }
+                // V rows of the same tokens, issued together with K: one round trip per half-page
+                uint4 vr[4];
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int t = hb * 8 + it * 2 + tg;
+                    if constexpr (EL == 8) {
+                        vr[it] = __ldcg(reinterpret_cast<const uint4 *>(vp + (size_t)t * HD));
+                    } else {
+                        const uint2 B = __ldcg(reinterpret_cast<const uint2 *>(vp + (size_t)t * HD));
+                        vr[it] = make_uint4(B.x, B.y, 0u, 0u);
+                    }
+                }
                 float sc[4][GQ];
 #pragma unroll
                 for (int it = 0; it < 4; ++it) {
@@ -160,18 +174,6 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
                         sv += __shfl_xor_sync(0xffffffffu, sv, 4);
                         sv += __shfl_xor_sync(0xffffffffu, sv, 8);
                         sc[it][g] = ok ? sv : -INFINITY;
-                    }
-                }
-                // V rows of the same tokens: issued now, they arrive while the softmax bookkeeping runs
-                uint4 vr[4];
-#pragma unroll
-                for (int it = 0; it < 4; ++it) {
-                    const int t = hb * 8 + it * 2 + tg;
-                    if constexpr (EL == 8) {
-                        vr[it] = __ldcg(reinterpret_cast<const uint4 *>(vp + (size_t)t * HD));
-                    } else {
-                        const uint2 B = __ldcg(reinterpret_cast<const uint2 *>(vp + (size_t)t * HD));
-                        vr[it] = make_uint4(B.x, B.y, 0u, 0u);
                     }
                 }
 #pragma unroll
@@ -204,7 +206,7 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
                 }
             }
         }
-        if (l[0] != 1.2345e30f) tcd_trace(p, c.ti, bid, tid);  // (debug) this warp's pages done
+        if (c.ti >= 0 && l[0] != 1.2345e30f) tcd_trace(p, c.ti, bid, tid, TT_ATT_KV);  // (debug) this warp's pages done
         // merge the two token streams of the warp (lanes 0..15 and 16..31)
 #pragma unroll
         for (int g = 0; g < GQ; ++g) {
@@ -231,7 +233,7 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
             }
         }
         bar_sync(1, kTC);
-        tcd_trace(p, c.ti, bid, tid);  // (debug) all warps done
+        tcd_trace(p, c.ti, bid, tid, TT_ATT_WARPS);  // (debug) all warps done
         // ---- CTA result = merge of the 16 warps; one thread per (q head, dim) ----
         for (int idx = tid; idx < GQ * HD; idx += kTC) {
             const int g = idx / HD, dd = idx % HD;
@@ -257,41 +259,8 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
                 if (dd == 0) p.part_ml[pi * 2] = M, p.part_ml[pi * 2 + 1] = L;
             }
         }
-        if (ns > 1) {
-            // cross-split merge by the last CTA to arrive for this kv head (fixed split order)
-            __threadfence();
-            bar_sync(1, kTC);
-            if (tid == 0) {
-                const unsigned prev = atomicAdd(&p.tickets[hk], 1u);
-                s.misc[0] = (prev == (unsigned)(ns - 1));
-            }
-            bar_sync(1, kTC);
-            if (s.misc[0]) {
-                __threadfence();
-                float *ml = s.mrg;  // [GQ][ns][2]; the per-warp partials in it are consumed (barrier above)
-                for (int i = tid; i < GQ * ns * 2; i += kTC) {
-                    const int g = i / (ns * 2), r = i % (ns * 2);
-                    ml[i] = __ldcg(&p.part_ml[((size_t)(hk * GQ + g) * p.n_splits) * 2 + r]);
-                }
-                bar_sync(1, kTC);
-                for (int idx = tid; idx < GQ * HD; idx += kTC) {
-                    const int g = idx / HD, dd = idx % HD;
-                    const size_t pb = (size_t)(hk * GQ + g) * p.n_splits;
-                    float M = -INFINITY;
-                    for (int sp = 0; sp < ns; ++sp) M = fmaxf(M, ml[(g * ns + sp) * 2]);
-                    float L = 0.f, O = 0.f;
-#pragma unroll 8
-                    for (int sp = 0; sp < ns; ++sp) {
-                        const float ms = ml[(g * ns + sp) * 2];
-                        const float cf = ms == -INFINITY ? 0.f : exp2f(ms - M);
-                        L += ml[(g * ns + sp) * 2 + 1] * cf;
-                        O += __ldcg(&p.part_o[(pb + sp) * HD + dd]) * cf;
-                    }
-                    p.att[(size_t)(hk * GQ + g) * HD + dd] = O / L;
-                }
-                if (tid == 0) p.tickets[hk] = 0;
-            }
-        }
+        // (ns > 1: the split partials are merged by the o_proj phase's prologue, which has to read the
+        // attention vector from memory anyway -- no ticket, no second pass here)
         bar_sync(1, kTC);  // merge buffers are reused by the next item / phase
     }
 }

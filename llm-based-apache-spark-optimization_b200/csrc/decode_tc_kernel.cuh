@@ -56,15 +56,16 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             const TcdJob &job = s.jobs[j];
             const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
             const float sc = tcd_prologue(p, job, s, c, r, G, bid, tid);
-            tcd_trace(p, c.ti, bid, tid);
+            tcd_trace(p, c.ti, bid, tid, TT_XREADY);
             if (warp < 4) tcd_epilogue(p, job, s, c, r, sc, warp, lane, tmem);
-            tcd_trace(p, c.ti, bid, tid);
+            tcd_trace(p, c.ti, bid, tid, TT_EPI);
         };
         for (int step = 0; step < p.n_steps; ++step) {
             c.ti = (p.trace != nullptr && step == p.trace_step && (bid == 0 || bid == G - 1)) ? 0 : -1;
-            tcd_trace(p, c.ti, bid, tid);
+            tcd_trace(p, c.ti, bid, tid, TT_STEP);
             c.tok = min(max(c.tok, 0), p.vocab - 1);
             if (bid == 0 && tid == 0) p.lane_hist[(size_t)p.lane * 64 + (c.pos & 63)] = c.tok;
+            c.att_ns = min(p.n_splits, (c.pos / kTPT + 1 + kTW - 1) / kTW);  // as in tcd_attn_phase
             if (tid < HD / 2) {  // RoPE angles of this position
                 float sn, cs;
                 sincosf((float)c.pos * p.inv_freq[tid], &sn, &cs);
@@ -72,23 +73,37 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             }
             for (int l = 0; l < p.n_layers; ++l) {
                 const TcdJob &qkv_job = s.jobs[4 * l];
+                int arr_i = (p.trace != nullptr && step == p.trace_step && l == 1 && tid == 0) ? 0 : -1;
+                auto arrive_stamp = [&]() {  // (debug) when does each CTA reach the barriers of layer 1?
+                    if (arr_i >= 0) {
+                        unsigned long long t;
+                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                        p.trace[2048 + arr_i * G + bid] = t;
+                        ++arr_i;
+                    }
+                };
                 tcd_attn_prefetch<HD>(p, qkv_job, s, c, G, bid, tid);
                 phase(4 * l);      // rmsnorm + qkv (raw sums)
+                arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
-                tcd_trace(p, c.ti, bid, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 tcd_attn_phase<HD, GQ>(p, qkv_job, s, c, G, bid, tid);  // rope + kv append + attention
-                tcd_trace(p, c.ti, bid, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_ATT_DONE);
+                arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
-                tcd_trace(p, c.ti, bid, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 phase(4 * l + 1);  // o_proj + residual
+                arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
-                tcd_trace(p, c.ti, bid, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 phase(4 * l + 2);  // rmsnorm + gate/up (raw sums)
+                arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
-                tcd_trace(p, c.ti, bid, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 phase(4 * l + 3);  // swiglu + down + residual
+                arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
-                tcd_trace(p, c.ti, bid, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR);
             }
             // ---- final norm + lm_head: logits, per-CTA (max, lowest argmax) ----
             c.best = -INFINITY, c.best_i = 0x7fffffff;
@@ -113,6 +128,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 }
             }
             tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+            tcd_trace(p, c.ti, bid, tid, TT_BAR);
             if (!p.sample) break;  // caller samples from the logits (temperature > 0)
             // ---- greedy sampling: every CTA reduces the G partials redundantly (no extra barrier) ----
             {

@@ -73,6 +73,31 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
             v[2] = (b.x / (1.f + expf(-b.x))) * b.y, v[3] = (b.z / (1.f + expf(-b.z))) * b.w;
             v[4] = (cc.x / (1.f + expf(-cc.x))) * cc.y, v[5] = (cc.z / (1.f + expf(-cc.z))) * cc.w;
             v[6] = (d.x / (1.f + expf(-d.x))) * d.y, v[7] = (d.z / (1.f + expf(-d.z))) * d.w;
+        } else if (x_kind == TCD_X_ATT && c.att_ns > 1) {
+            // split-T attention partials of this head -> merged output (running max, fixed split order)
+            const int hd = p.head_dim, hq = (chunk * 8) / hd, dd = (chunk * 8) % hd;
+            const size_t pb = (size_t)hq * p.n_splits;
+            float M = -INFINITY, L = 0.f;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = 0.f;
+#pragma unroll 4
+            for (int sp = 0; sp < c.att_ns; ++sp) {
+                const float2 ml = __ldcg(reinterpret_cast<const float2 *>(p.part_ml + (pb + sp) * 2));
+                const float4 a = __ldcg(reinterpret_cast<const float4 *>(p.part_o + (pb + sp) * hd + dd));
+                const float4 b = __ldcg(reinterpret_cast<const float4 *>(p.part_o + (pb + sp) * hd + dd + 4));
+                const float mn = fmaxf(M, ml.x);
+                const float c_old = mn == -INFINITY ? 1.f : exp2f(M - mn);
+                const float c_new = mn == -INFINITY ? 0.f : exp2f(ml.x - mn);
+                L = L * c_old + ml.y * c_new;
+                v[0] = v[0] * c_old + a.x * c_new, v[1] = v[1] * c_old + a.y * c_new;
+                v[2] = v[2] * c_old + a.z * c_new, v[3] = v[3] * c_old + a.w * c_new;
+                v[4] = v[4] * c_old + b.x * c_new, v[5] = v[5] * c_old + b.y * c_new;
+                v[6] = v[6] * c_old + b.z * c_new, v[7] = v[7] * c_old + b.w * c_new;
+                M = mn;
+            }
+            const float inv = 1.f / L;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] *= inv;
         } else {
             const float4 a = __ldcg(reinterpret_cast<const float4 *>(xsrc + chunk * 8));
             const float4 b = __ldcg(reinterpret_cast<const float4 *>(xsrc + chunk * 8 + 4));
@@ -103,7 +128,7 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
         ss = warp_sum(ss);
         if (lane == 0) s.red[warp] = ss;
     }
-    tcd_trace(p, c.ti, bid, tid);
+    tcd_trace(p, c.ti, bid, tid, TT_XCONV);
     bar_sync(2, kTC + 32);  // with the MMA issuer warp: operand blocks (and the norm partials) are complete
     float sc = 1.f;
     if (gain != nullptr) {

@@ -230,7 +230,7 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->attn_scratch = take(w->attn_scratch_bytes);
     w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * (sizeof(MegaJob) > sizeof(TcdJob) ? sizeof(MegaJob) : sizeof(TcdJob)));
     w->bar_ctr = take(256);
-    w->trace = take(2048 * 8);
+    w->trace = take(4096 * 8);
     {   // batch / prefill path (tcgen05 GEMM): bf16 activations and fp32 GEMM outputs
         size_t widest = c->d > (int)(nq_l * c->head_dim) ? c->d : nq_l * c->head_dim;
         if (ffn_l > widest) widest = ffn_l;
@@ -1027,7 +1027,7 @@ int b200llm_last_timing(b200llm_engine *e, b200llm_timing *t) {
 void *b200llm_stream(b200llm_engine *e) { return e ? (void *)e->stream : nullptr; }
 
 int b200llm_debug_read_trace(b200llm_engine *e, uint64_t *out, int32_t n) {
-    B200_REQUIRE(e && e->ws && out && n >= 1 && n <= 2048, "debug_read_trace: bad arguments");
+    B200_REQUIRE(e && e->ws && out && n >= 1 && n <= 4096, "debug_read_trace: bad arguments");
     B200_CUDA_OK(cudaMemcpyAsync(out, e->trace, (size_t)n * 8, cudaMemcpyDeviceToHost, e->stream));
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));
     return B200LLM_OK;

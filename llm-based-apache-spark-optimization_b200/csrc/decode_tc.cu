@@ -33,7 +33,8 @@ namespace b200 {
 
 constexpr int kTC = 384;              // compute threads
 constexpr int kTW = kTC / 32;         // compute warps
-constexpr int kTThreads = kTC + 64;   // + MMA issuer warp + producer warp
+constexpr int kTIssuers = 2;           // MMA issuer threads (one warp each): stage i of a phase goes to issuer i % 2
+constexpr int kTThreads = kTC + 32 * kTIssuers + 32;   // + MMA issuer warps + producer warp
 constexpr int kTStages = 8;
 constexpr int kTStageBytes = 16384;   // [128 rows x 64 k] bf16
 constexpr int kTBSlots = 64;          // activation operand blocks ([8 x 64 k] bf16 = 1 KB each)
@@ -167,7 +168,11 @@ __device__ __forceinline__ void tcd_commit(uint64_t *bar) {
                  : "memory");
 }
 
-__device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem) {
+// Issuer `me` (0 or 1) takes every second stage of the CTA's range.  One thread sustains a
+// tcgen05.mma every ~64 clk, two threads together one every ~39 clk (scripts/ubench_umma.cu), which
+// is what drains a prefetched ring quickly after a barrier.  The issuers accumulate into separate
+// column groups of the segment's accumulator (columns 0..7 and 8..15); the epilogue adds them.
+__device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem, int me) {
     const int n_jobs = 4 * p.n_layers + 1;
     // D fp32, A/B bf16, both K-major, M = 128, N = umma_n
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.umma_n >> 3) << 17) | ((128u >> 4) << 24);
@@ -177,7 +182,7 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
         for (int j = 0; j < n_jobs; ++j) {
             const TcdJob &job = s.jobs[j];
             const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
-            bar_sync(2, kTC + 32);  // the activation operand of this phase is in shared memory
+            bar_sync(2, kTC + 32 * kTIssuers);  // the activation operand of this phase is in shared memory
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const int kb_start = r.g0 % r.nkb;
             for (int g = r.g0; lane == 0 && g < r.g1;) {
@@ -188,9 +193,10 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
                     mbar_wait(&s.acc_empty[aslot], ((as / kTAcc) - 1) & 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 }
-                const uint32_t d_addr = tmem + aslot * kTAccCols;
+                const uint32_t d_addr = tmem + aslot * kTAccCols + me * 8;
                 bool first = true;
-                for (; g < seg_end; ++g, ++gs) {
+                for (int u = 0; g < seg_end; ++g, ++gs, ++u) {
+                    if ((u & 1) != me) continue;
                     const uint32_t slot = gs % kTStages, use = gs / kTStages;
                     int bslot = g % r.nkb - kb_start;
                     bslot += bslot < 0 ? r.nkb : 0;
@@ -210,7 +216,11 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
                     first = false;
                     tcd_commit(&s.empty[slot]);  // frees the ring stage once the MMAs above have read it
                 }
-                tcd_commit(&s.acc_full[aslot]);
+                if (first) {
+                    mbar_arrive(&s.acc_full[aslot]);  // a one-stage segment: nothing for this issuer
+                } else {
+                    tcd_commit(&s.acc_full[aslot]);
+                }
                 ++as;
             }
             __syncwarp();

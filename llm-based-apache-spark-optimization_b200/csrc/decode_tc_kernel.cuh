@@ -17,7 +17,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             mbar_init(&s.empty[i], 1);
         }
         for (int i = 0; i < kTAcc; ++i) {
-            mbar_init(&s.acc_full[i], 1);
+            mbar_init(&s.acc_full[i], kTIssuers);
             mbar_init(&s.acc_empty[i], 4);
         }
         mbar_fence_init();
@@ -41,10 +41,10 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *s.tmem_slot;
 
-    if (warp == kTW + 1) {
+    if (warp == kTW + kTIssuers) {
         if (lane == 0) tcd_producer(p, s, G, bid);
-    } else if (warp == kTW) {
-        tcd_mma_warp(p, s, G, bid, lane, tmem);
+    } else if (warp >= kTW) {
+        tcd_mma_warp(p, s, G, bid, lane, tmem, warp - kTW);
     } else {
         TcdCtx c;
         c.as = 0;

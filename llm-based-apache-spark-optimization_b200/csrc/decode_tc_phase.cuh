@@ -58,6 +58,9 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
             chunk = kb * 8 + (idx & 7);
         }
         float v[8];
+        // issued with the activation loads below: behind the `continue` it would cost a second L2 round trip
+        uint4 gn = make_uint4(0u, 0u, 0u, 0u);
+        if (gain != nullptr) gn = *reinterpret_cast<const uint4 *>(gain + chunk * 8);
         if (x_kind == TCD_X_EMBED) {
             const uint4 u = *reinterpret_cast<const uint4 *>(emb + chunk * 8);
             v[0] = bf16lo(u.x), v[1] = bf16hi(u.x), v[2] = bf16lo(u.y), v[3] = bf16hi(u.y);
@@ -107,7 +110,7 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
         for (int e = 0; e < 8; ++e) ss = fmaf(v[e], v[e], ss);
         if (slot >= n_slots) continue;
         if (gain != nullptr) {
-            const uint4 g = *reinterpret_cast<const uint4 *>(gain + chunk * 8);
+            const uint4 g = gn;
             v[0] *= bf16lo(g.x), v[1] *= bf16hi(g.x), v[2] *= bf16lo(g.y), v[3] *= bf16hi(g.y);
             v[4] *= bf16lo(g.z), v[5] *= bf16hi(g.z), v[6] *= bf16lo(g.w), v[7] *= bf16hi(g.w);
         }
@@ -129,7 +132,7 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
         if (lane == 0) s.red[warp] = ss;
     }
     tcd_trace(p, c.ti, bid, tid, TT_XCONV);
-    bar_sync(2, kTC + 32);  // with the MMA issuer warp: operand blocks (and the norm partials) are complete
+    bar_sync(2, kTC + 32 * kTIssuers);  // with the MMA issuer warps: operand blocks (and the norm partials) are complete
     float sc = 1.f;
     if (gain != nullptr) {
         float tot = 0.f;
@@ -151,14 +154,18 @@ __device__ void tcd_epilogue(const TcdParams &p, const TcdJob &job, const TcdSme
         const uint32_t aslot = c.as % kTAcc;
         mbar_wait(&s.acc_full[aslot], (c.as / kTAcc) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        uint32_t r0, r1;
+        uint32_t r0, r1, r2, r3;
         const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + aslot * kTAccCols;
         asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(taddr) : "memory");
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r2), "=r"(r3) : "r"(taddr + 8) : "memory");
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncwarp();
         if (lane == 0) mbar_arrive(&s.acc_empty[aslot]);
-        const float v = (__uint_as_float(r0) + __uint_as_float(r1)) * sc;
+        // columns 0/1: hi/lo sums of the first issuer's stages, 8/9: the second issuer's (if the segment has > 1 stage)
+        float v = __uint_as_float(r0) + __uint_as_float(r1);
+        if (seg_end - g > 1) v += __uint_as_float(r2) + __uint_as_float(r3);
+        v *= sc;
         const int n = t * 128 + warp * 32 + lane;
         if (job.epi == TCD_EPI_ADD) {
             asm volatile("red.global.add.f32 [%0], %1;" ::"l"(job.out + n), "f"(v) : "memory");

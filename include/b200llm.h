@@ -226,9 +226,9 @@ int b200llm_op_gemv_grid(int32_t N, int32_t K, int32_t bs, int32_t epi, int32_t 
  * out[N] = W x with W given tile-major (B200LLM_W_*_TM layout), x and out fp32 on the device.
  * k_split = 0 cuts the matrix at row-tile boundaries (the lm_head mode, plain stores),
  * k_split = 1 into 148 equal (tile, k block) ranges whose partial sums meet with fp32 atomics
- * (the mode of every other phase).  umma_n = 8 or 16 (N of the MMA instruction).  Synchronous. */
+ * (the mode of every other phase).  Synchronous. */
 int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, int32_t K, int32_t k_split,
-                       int32_t umma_n, void *stream);
+                       void *stream);
 
 /* Paged GQA decode attention with split-T partials merged by the last CTA to finish.
  * `scratch` holds the split partials and arrival counters; it must be zeroed once

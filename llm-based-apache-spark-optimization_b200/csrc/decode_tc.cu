@@ -174,8 +174,8 @@ __device__ __forceinline__ void tcd_commit(uint64_t *bar) {
 // column groups of the segment's accumulator (columns 0..7 and 8..15); the epilogue adds them.
 __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem, int me) {
     const int n_jobs = 4 * p.n_layers + 1;
-    // D fp32, A/B bf16, both K-major, M = 128, N = umma_n
-    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.umma_n >> 3) << 17) | ((128u >> 4) << 24);
+    // D fp32, A/B bf16, both K-major, M = 128, N = 8
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((8u >> 3) << 17) | ((128u >> 4) << 24);
     const uint32_t ring_a = smem_u32(s.ring), bop_a = smem_u32(s.bop);
     uint32_t gs = 0, as = 0;
     for (int step = 0; step < p.n_steps; ++step) {

@@ -200,7 +200,6 @@ int tcd_decode_launch(const TcdParams &p, cudaStream_t stream) {
     B200_REQUIRE(p.n_steps >= 1 && (p.sample || p.n_steps == 1), "tcd: n_steps must be 1 when sampling is external");
     B200_REQUIRE(p.n_splits >= 1, "tcd: n_splits < 1");
     B200_REQUIRE(4 * p.n_layers + 1 <= kTMaxJobs, "tcd: more than 32 layers");
-    B200_REQUIRE(p.umma_n == 8 || p.umma_n == 16, "tcd: umma_n must be 8 or 16");
     const int GQ = p.n_kv > 0 ? p.n_q / p.n_kv : 1;
 #define B200_TCD_CASE(HD_, G_) \
     if (p.head_dim == HD_ && GQ == G_) return tcd_launch_t<HD_, G_>(p, stream);

@@ -771,8 +771,6 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps) {
     p.part_ml = p.part_o + (size_t)c.n_q * ns * c.head_dim;
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
-    p.umma_n = 8;
-    if (const char *un = getenv("B200LLM_UMMA_N")) p.umma_n = atoi(un);
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     // the qkv and gate/up phases ADD into these rows; later layers find them cleared by the o_proj phase
     B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)(c.n_q + 2 * c.n_kv) * c.head_dim * 4, e->stream));
@@ -1050,7 +1048,7 @@ int b200llm_op_gemv_grid(int32_t N, int32_t K, int32_t bs, int32_t epi, int32_t 
 }
 
 int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, int32_t K, int32_t k_split,
-                       int32_t umma_n, void *stream) {
+                       void *stream) {
     B200_REQUIRE(w_tm && x && out, "op_gemv_tm: NULL argument");
     B200_REQUIRE(tcd_job_fits(N, K, !k_split), "op_gemv_tm: N %% 128, K %% 64, or the per-CTA share does not fit");
     int rc = require_device_any();
@@ -1075,7 +1073,7 @@ int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, 
     p.embed = x;
     p.gen_out = reinterpret_cast<int32_t *>(scr + 3712), p.n_steps = 1, p.n_splits = 1;
     p.bar_ctr = reinterpret_cast<unsigned *>(scr + 3776);
-    p.sample = 0, p.umma_n = umma_n, p.split_all = k_split ? 1 : 0;
+    p.sample = 0, p.split_all = k_split ? 1 : 0;
     rc = tcd_decode_launch(p, st);
     cudaError_t ce = cudaStreamSynchronize(st);
     cudaFree(scr);

@@ -52,7 +52,6 @@ struct TcdParams {
     int32_t n_splits;
     unsigned *bar_ctr;    // grid barrier counter (zeroed before every launch)
     int32_t sample;       // 1: greedy argmax + feedback inside the kernel; 0: stop after the logits
-    int32_t umma_n;       // 8 or 16: N of the MMA instruction (columns 0/1 carry the result)
     int32_t split_all;    // (test hook) k-split the last job too instead of giving whole tiles
     unsigned long long *trace;  // optional [2][1024] globaltimer stamps of CTA 0 and CTA G-1 (debug)
     int32_t trace_step;

@@ -279,6 +279,6 @@ def test_gemv_tile_major_tcgen05_phase(N, K, k_split):
     xd = x.cuda()
     out = torch.full((N,), 7.0, device="cuda")
     torch.cuda.synchronize()
-    _lib.check(_lib.lib.b200llm_op_gemv_tm(wt.data_ptr(), xd.data_ptr(), out.data_ptr(), N, K, k_split, 8,
+    _lib.check(_lib.lib.b200llm_op_gemv_tm(wt.data_ptr(), xd.data_ptr(), out.data_ptr(), N, K, k_split,
                                            torch.cuda.current_stream().cuda_stream))
     _close(out.cpu(), ref, 2e-5)

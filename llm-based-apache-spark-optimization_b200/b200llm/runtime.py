@@ -31,13 +31,23 @@ class LoadedModel:
 
 
 _models: Dict[str, LoadedModel] = {}
+_checkpoints: Dict[str, str] = {}      # model name -> GGUF path (gguf_loader.register)
 _lock = threading.Lock()
 
 
-def get_model(name: str) -> LoadedModel:
-    geo = geometry.resolve(name)          # KeyError -> the shim turns it into ResponseError 404
+def register_checkpoint(name: str, path: str) -> None:
+    """Serve `name` from a GGUF checkpoint instead of seeded random-init weights (loaded on first use)."""
+    if not os.path.isfile(path):
+        raise FileNotFoundError(path)
     with _lock:
-        m = _models.get(geo.name)
+        _checkpoints[name] = path
+
+
+def get_model(name: str) -> LoadedModel:
+    ckpt = _checkpoints.get(name)
+    key = name if ckpt else geometry.resolve(name).name   # KeyError -> the shim turns it into ResponseError 404
+    with _lock:
+        m = _models.get(key)
         if m is not None:
             return LoadedModel(m.name, m.engine, m.tokenizer, 0, m.scheduler)
         if not torch.cuda.is_available():
@@ -45,12 +55,19 @@ def get_model(name: str) -> LoadedModel:
         t0 = time.perf_counter_ns()
         dev = int(os.environ.get("B200LLM_DEVICE", "0"))
         torch.cuda.set_device(dev)
-        w = weights.random_init(geo, SEED, dev)
+        if ckpt:
+            from . import gguf_loader
+            geo, sd = gguf_loader.load(ckpt, dev, name)
+            w = weights.pack(geo, sd)
+            del sd
+        else:
+            geo = geometry.resolve(name)
+            w = weights.random_init(geo, SEED, dev)
         eng = Engine(geo, w, device=dev, max_lanes=int(os.environ.get("B200LLM_MAX_LANES", "8")),
                      max_ctx=int(os.environ.get("B200LLM_NUM_CTX", "4096")),
                      max_rows=int(os.environ.get("B200LLM_MAX_ROWS", "64")))
-        m = LoadedModel(geo.name, eng, ByteTokenizer(geo.vocab), time.perf_counter_ns() - t0, Scheduler(eng))
-        _models[geo.name] = m
+        m = LoadedModel(key, eng, ByteTokenizer(geo.vocab), time.perf_counter_ns() - t0, Scheduler(eng))
+        _models[key] = m
         return m
 
 

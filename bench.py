@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--pdl", action="store_true")
+    ap.add_argument("--max-rows", type=int, default=256, help="rows per forward pass (prefill chunk size / batch limit)")
     ap.add_argument("--no-mega", action="store_true", help="multi-kernel CUDA-graph path instead of the persistent kernel")
     ap.add_argument("--attn-splits", type=int, default=0)
     return ap.parse_args()
@@ -171,7 +172,7 @@ def run_b200(args):
     bs = args.bs
     w = weights.random_init(geo, 0xB200, local)
     max_ctx = PROMPT_LEN + args.steps + args.warmup + E2E_NEW_TOKENS + 64
-    eng = Engine(geo, w, device=local, max_lanes=bs + 1, max_ctx=max_ctx, max_rows=max(bs, 64),
+    eng = Engine(geo, w, device=local, max_lanes=bs + 1, max_ctx=max_ctx, max_rows=max(bs, args.max_rows),
                  use_graphs=not args.no_graphs, use_pdl=args.pdl, attn_splits=args.attn_splits,
                  use_megakernel=not args.no_mega)
     # synthetic prompts: uniform ids, one stream per (rank, sequence)

@@ -65,7 +65,7 @@ def get_model(name: str) -> LoadedModel:
             w = weights.random_init(geo, SEED, dev)
         eng = Engine(geo, w, device=dev, max_lanes=int(os.environ.get("B200LLM_MAX_LANES", "8")),
                      max_ctx=int(os.environ.get("B200LLM_NUM_CTX", "4096")),
-                     max_rows=int(os.environ.get("B200LLM_MAX_ROWS", "64")))
+                     max_rows=int(os.environ.get("B200LLM_MAX_ROWS", "256")))   # prefill chunk = tcgen05 GEMM N limit
         m = LoadedModel(key, eng, ByteTokenizer(geo.vocab), time.perf_counter_ns() - t0, Scheduler(eng))
         _models[key] = m
         return m

@@ -24,7 +24,7 @@ __device__ __forceinline__ void tcd_attn_prefetch(const TcdParams &p, const TcdJ
                                                    const TcdCtx &c, int G, int bid, int tid) {
     constexpr int LINES = kTPT * HD * 2 / 128;  // 128-byte lines per K (or V) page tile
     const int n_pages = c.pos / kTPT + 1;
-    const int ns = min(p.n_splits, (n_pages + kTW - 1) / kTW);  // at most one page per warp while splits last
+    const int ns = min(p.n_splits, (2 * n_pages + kTW - 1) / kTW);  // one half-page (one L2 round trip) per warp while splits last
     const int pps = (n_pages + ns - 1) / ns;
     const int n_items = p.n_kv * ns;
     const uint8_t *kbase = reinterpret_cast<const uint8_t *>(qkv_job.k_pages);
@@ -49,7 +49,7 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
     const int warp = tid >> 5, lane = tid & 31;
     const int tg = lane >> 4, p16 = lane & 15;
     const int n_pages = c.pos / kTPT + 1;
-    const int ns = min(p.n_splits, (n_pages + kTW - 1) / kTW);  // at most one page per warp while splits last
+    const int ns = min(p.n_splits, (2 * n_pages + kTW - 1) / kTW);  // one half-page (one L2 round trip) per warp while splits last
     const int pps = (n_pages + ns - 1) / ns;
     const int n_items = p.n_kv * ns;
     const uint16_t *kbase = reinterpret_cast<const uint16_t *>(qkv_job.k_pages);
@@ -123,15 +123,16 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
                 }
             }
         }
-        for (int pg = pg_begin + warp; pg < pg_end; pg += kTW) {
+        for (int hp = 2 * pg_begin + warp; hp < 2 * pg_end; hp += kTW) {  // half-pages of this item, round-robin over the warps
+            const int pg = hp >> 1;
             const int page = pg < kTMaxPtab ? s.ptab[pg] : p.page_table[pg];
             const size_t tile = ((size_t)page * p.n_kv + hk) * (size_t)(kTPT * HD);
             const uint16_t *kp = kbase + tile + p16 * EL;
             const uint16_t *vp = vbase + tile + p16 * EL;
-            // two half-pages of 4 x 2 tokens: all loads of a half-page in flight together, its 8
-            // scores computed before one running-max update (page-at-a-time softmax, see attn.cu)
-#pragma unroll 1
-            for (int hb = 0; hb < 2; ++hb) {
+            // a half-page = 4 x 2 tokens: all its K and V loads in flight together, its 8 scores
+            // computed before one running-max update (page-at-a-time softmax, see attn.cu)
+            {
+                const int hb = hp & 1;
                 uint4 kr[4];
 #pragma unroll
                 for (int it = 0; it < 4; ++it) {

@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             tcd_trace(p, c.ti, bid, tid, TT_STEP);
             c.tok = min(max(c.tok, 0), p.vocab - 1);
             if (bid == 0 && tid == 0) p.lane_hist[(size_t)p.lane * 64 + (c.pos & 63)] = c.tok;
-            c.att_ns = min(p.n_splits, (c.pos / kTPT + 1 + kTW - 1) / kTW);  // as in tcd_attn_phase
+            c.att_ns = min(p.n_splits, (2 * (c.pos / kTPT + 1) + kTW - 1) / kTW);  // as in tcd_attn_phase
             if (tid < HD / 2) {  // RoPE angles of this position
                 float sn, cs;
                 sincosf((float)c.pos * p.inv_freq[tid], &sn, &cs);

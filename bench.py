@@ -154,6 +154,11 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------------- B200 arm
+def _note(msg):
+    if os.environ.get("B200LLM_BENCH_VERBOSE"):
+        print(f"[bench {time.time():.1f}] {msg}", file=sys.stderr, flush=True)
+
+
 def run_b200(args):
     import numpy as np
     import torch
@@ -183,11 +188,13 @@ def run_b200(args):
         eng.prefill(ln, p)
     eng.sync()
     ttft_ms = eng.timing().prefill_ms
+    _note("prefill done")
 
     sampler = ClockSampler(local) if rank == 0 else None
     # warm-up: graph capture + W steps (at least 3), and keep the GPU loaded until nvidia-smi has sampled
     eng.decode(lanes, max(3, args.warmup), read=False)
     eng.sync()
+    _note("warm-up done")
     first_line = 0
     if sampler is not None and sampler.p is not None:
         t_wait = time.time()
@@ -196,6 +203,7 @@ def run_b200(args):
                 eng.set_lane(ln, 1, PROMPT_LEN)        # rewind so the context stays at the config's length
             eng.decode(lanes, 32, read=False)
             eng.sync()
+            _note("clock-sampler filler decode done")
         first_line = len(sampler.lines())
     for i, ln in enumerate(lanes):                     # timed region starts at the same context on every run
         eng.set_lane(ln, int(prompts[i][0]), PROMPT_LEN)
@@ -212,6 +220,7 @@ def run_b200(args):
     eng.decode(lanes, args.steps, read=False)
     ev1.record(eng.stream)
     torch.cuda.synchronize()
+    _note("timed region done")
     if profiling:
         torch.cuda.profiler.stop()
     if world > 1:

@@ -33,7 +33,9 @@ namespace b200 {
 
 constexpr int kTC = 384;              // compute threads
 constexpr int kTW = kTC / 32;         // compute warps
-constexpr int kTIssuers = 2;           // MMA issuer threads (one warp each): stage i of a phase goes to issuer i % 2
+constexpr int kTIssuers = 1;           // MMA issuer threads (one warp each): stage u of a segment goes to issuer u % kTIssuers.
+                                       // Two issuers are ~3 % faster (a prefilled ring drains at 39 instead of 64 clk per MMA) but
+                                       // rare launch failures / hangs appeared with them, so one is the default
 constexpr int kTThreads = kTC + 32 * kTIssuers + 32;   // + MMA issuer warps + producer warp
 constexpr int kTStages = 8;
 constexpr int kTStageBytes = 16384;   // [128 rows x 64 k] bf16
@@ -196,9 +198,10 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
             const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
             bar_sync(2, kTC + 32 * kTIssuers);  // the activation operand of this phase is in shared memory
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int kb_start = r.g0 % r.nkb;
-            for (int g = r.g0; lane == 0 && g < r.g1;) {
-                const int t = g / r.nkb;
+            // operand slot of the stage's k block: (kb - kb_start) mod nkb = stages since the range began, mod nkb
+            // (kept incrementally: an integer division per stage would cost the issuer ~40 clk)
+            int bslot = 0;
+            for (int g = r.g0, t = r.g0 / r.nkb; lane == 0 && g < r.g1; ++t) {
                 const int seg_end = min(r.g1, (t + 1) * r.nkb);
                 const uint32_t aslot = as % kTAcc;
                 if (as >= kTAcc) {
@@ -207,11 +210,9 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
                 }
                 const uint32_t d_addr = tmem + aslot * kTAccCols + me * 8;
                 bool first = true;
-                for (int u = 0; g < seg_end; ++g, ++gs, ++u) {
-                    if ((u & 1) != me) continue;
+                for (int u = 0; g < seg_end; ++g, ++gs, ++u, bslot = (bslot + 1 == r.nkb ? 0 : bslot + 1)) {
+                    if ((u % kTIssuers) != me) continue;
                     const uint32_t slot = gs % kTStages, use = gs / kTStages;
-                    int bslot = g % r.nkb - kb_start;
-                    bslot += bslot < 0 ? r.nkb : 0;
                     mbar_wait(&s.full[slot], use & 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint64_t adesc = tcd_desc(ring_a + slot * kTStageBytes, 1024);

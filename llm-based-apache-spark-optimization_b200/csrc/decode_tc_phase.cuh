@@ -164,7 +164,7 @@ __device__ void tcd_epilogue(const TcdParams &p, const TcdJob &job, const TcdSme
         if (lane == 0) mbar_arrive(&s.acc_empty[aslot]);
         // columns 0/1: hi/lo sums of the first issuer's stages, 8/9: the second issuer's (if the segment has > 1 stage)
         float v = __uint_as_float(r0) + __uint_as_float(r1);
-        if (seg_end - g > 1) v += __uint_as_float(r2) + __uint_as_float(r3);
+        if (kTIssuers > 1 && seg_end - g > 1) v += __uint_as_float(r2) + __uint_as_float(r3);
         v *= sc;
         const int n = t * 128 + warp * 32 + lane;
         if (job.epi == TCD_EPI_ADD) {

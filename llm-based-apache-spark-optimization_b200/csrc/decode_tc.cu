@@ -37,9 +37,9 @@ constexpr int kTIssuers = 1;           // MMA issuer threads (one warp each): st
                                        // Two issuers are ~3 % faster (a prefilled ring drains at 39 instead of 64 clk per MMA) but
                                        // rare launch failures / hangs appeared with them, so one is the default
 constexpr int kTThreads = kTC + 32 * kTIssuers + 32;   // + MMA issuer warps + producer warp
-constexpr int kTStages = 8;
+constexpr int kTMaxStages = 10;        // ring stages: as many as fit beside the operand blocks (TcdParams::n_stages)
 constexpr int kTStageBytes = 16384;   // [128 rows x 64 k] bf16
-constexpr int kTBSlots = 64;          // activation operand blocks ([8 x 64 k] bf16 = 1 KB each)
+constexpr int kTBSlots = 64;          // most activation operand blocks ([8 x 64 k] bf16 = 1 KB each) a CTA may need (TcdParams::n_bslots)
 constexpr int kTAcc = 8;              // accumulators in flight (16 TMEM columns apart)
 constexpr int kTAccCols = 16;
 constexpr int kTPT = 16;              // tokens per KV page
@@ -60,15 +60,15 @@ struct TcdSmem {
 
 __host__ __device__ __forceinline__ size_t tcd_mrg_bytes(int hd, int gq) { return (size_t)kTW * gq * (hd + 2) * 4; }
 
-__device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq) {
+__device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int n_stages, int n_bslots) {
     TcdSmem s;
     s.ring = base;
-    s.bop = base + kTStages * kTStageBytes;
-    s.mrg = reinterpret_cast<float *>(s.bop + kTBSlots * 1024);
+    s.bop = base + n_stages * kTStageBytes;
+    s.mrg = reinterpret_cast<float *>(s.bop + n_bslots * 1024);
     uint8_t *q = reinterpret_cast<uint8_t *>(s.mrg) + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15);
     s.full = reinterpret_cast<uint64_t *>(q);
-    s.empty = s.full + kTStages;
-    s.acc_full = s.empty + kTStages;
+    s.empty = s.full + kTMaxStages;
+    s.acc_full = s.empty + kTMaxStages;
     s.acc_empty = s.acc_full + kTAcc;
     s.tmem_slot = reinterpret_cast<uint32_t *>(s.acc_empty + kTAcc);
     s.red = reinterpret_cast<float *>(s.tmem_slot + 4);
@@ -79,11 +79,14 @@ __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq) {
     return s;
 }
 
-static size_t tcd_smem_bytes(int hd, int gq, int n_jobs) {
-    return (size_t)kTStages * kTStageBytes + (size_t)kTBSlots * 1024 + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) +
-           (2 * kTStages + 2 * kTAcc) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 + kTMaxPtab * 4 + (size_t)n_jobs * sizeof(TcdJob) +
-           1024;  // slack for the 1024-byte alignment of the base
+static size_t tcd_fixed_smem_bytes(int hd, int gq, int n_jobs) {  // everything but the ring and the operand blocks
+    return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + (2 * kTMaxStages + 2 * kTAcc) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 +
+           kTMaxPtab * 4 + (size_t)n_jobs * sizeof(TcdJob) + 1024;  // slack for the 1024-byte alignment of the base
 }
+static size_t tcd_smem_bytes(int hd, int gq, int n_jobs, int n_stages, int n_bslots) {
+    return (size_t)n_stages * kTStageBytes + (size_t)n_bslots * 1024 + tcd_fixed_smem_bytes(hd, gq, n_jobs);
+}
+constexpr size_t kTSmemLimit = 232448;  // 227 KB per CTA on sm_100
 
 // This CTA's contiguous range [g0, g1) of the matrix's (row tile, k block) units, unit g = tile * nkb + kb.
 struct TRange {
@@ -101,19 +104,48 @@ __host__ __device__ __forceinline__ TRange tcd_range(int N, int K, bool whole_ti
     return r;
 }
 
-bool tcd_job_fits(int N, int K, bool whole_tiles) {
-    if (N % 128 != 0 || K % 64 != 0 || N < 128 || K < 64) return false;
+// operand blocks the CTA with the largest share needs for one matrix (0: the shape cannot be tiled)
+int tcd_job_slots(int N, int K, bool whole_tiles) {
+    if (N % 128 != 0 || K % 64 != 0 || N < 128 || K < 64) return 0;
     const TRange r = tcd_range(N, K, whole_tiles, kNumSMs, 0);  // CTA 0 has the largest share
-    const int need = (r.g1 - r.g0) < r.nkb ? (r.g1 - r.g0) : r.nkb;
-    return need <= kTBSlots;
+    return (r.g1 - r.g0) < r.nkb ? (r.g1 - r.g0) : r.nkb;
+}
+bool tcd_job_fits(int N, int K, bool whole_tiles) {
+    const int need = tcd_job_slots(N, K, whole_tiles);
+    return need >= 1 && need <= kTBSlots;
+}
+int tcd_stages_for(int head_dim, int gq, int n_jobs, int n_bslots) {
+    const size_t fixed = tcd_fixed_smem_bytes(head_dim, gq, n_jobs) + (size_t)n_bslots * 1024;
+    if (fixed + 4 * (size_t)kTStageBytes > kTSmemLimit) return 0;
+    const int st = (int)((kTSmemLimit - fixed) / kTStageBytes);
+    return st > kTMaxStages ? kTMaxStages : st;
 }
 
-bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab) {
-    const int G = n_kv > 0 ? n_q / n_kv : 0;
-    if (!(head_dim == 64 || head_dim == 128) || G < 1 || G > 4 || G == 3 && head_dim == 64) return false;
+// ring stages and operand blocks of a model: the operand buffer is sized for the neediest matrix,
+// the ring takes what is left of the 227 KB (false: not even 4 stages fit)
+bool tcd_plan(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers, int *n_stages, int *n_bslots) {
     const int qd = n_q * head_dim, qkv = (n_q + 2 * n_kv) * head_dim;
-    return tcd_job_fits(qkv, d, false) && tcd_job_fits(d, qd, false) && tcd_job_fits(2 * ffn, d, false) &&
-           tcd_job_fits(d, ffn, false) && tcd_job_fits(vocab, d, true);
+    const int shapes[5][2] = {{qkv, d}, {d, qd}, {2 * ffn, d}, {d, ffn}, {vocab, d}};
+    int slots = 0;
+    for (int i = 0; i < 5; ++i) {
+        const int need = tcd_job_slots(shapes[i][0], shapes[i][1], i == 4);
+        if (need < 1 || need > kTBSlots) return false;
+        slots = need > slots ? need : slots;
+    }
+    const size_t fixed = tcd_fixed_smem_bytes(head_dim, n_kv > 0 ? n_q / n_kv : 1, 4 * n_layers + 1) + (size_t)slots * 1024;
+    if (fixed + 4 * (size_t)kTStageBytes > kTSmemLimit) return false;
+    int st = (int)((kTSmemLimit - fixed) / kTStageBytes);
+    *n_stages = st > kTMaxStages ? kTMaxStages : st;
+    *n_bslots = slots;
+    return true;
+}
+
+bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers) {
+    const int G = n_kv > 0 ? n_q / n_kv : 0;
+    if (!(head_dim == 64 || head_dim == 128) || G < 1 || G > 4 || (G == 3 && head_dim == 64)) return false;
+    if (4 * n_layers + 1 > kTMaxJobs) return false;
+    int st, sl;
+    return tcd_plan(d, ffn, n_q, n_kv, head_dim, vocab, n_layers, &st, &sl);
 }
 
 __device__ __forceinline__ bool tcd_whole(const TcdParams &p, int j, int n_jobs) {
@@ -150,17 +182,20 @@ __device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, in
 __device__ void tcd_producer(const TcdParams &p, const TcdSmem &s, int G, int bid) {
     const uint64_t pol = l2_policy_evict_first();
     const int n_jobs = 4 * p.n_layers + 1;
-    uint32_t gs = 0;
+    // ring position: slot and the parity of its current use (no modulo of a run-time ring size in the loop)
+    int slot = 0;
+    uint32_t par = 0;
+    bool first_round = true;
     for (int step = 0; step < p.n_steps; ++step) {
         for (int j = 0; j < n_jobs; ++j) {
             const TcdJob &job = s.jobs[j];
             const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
             const uint8_t *src = reinterpret_cast<const uint8_t *>(job.w) + (size_t)r.g0 * kTStageBytes;
-            for (int g = r.g0; g < r.g1; ++g, ++gs, src += kTStageBytes) {
-                const uint32_t slot = gs % kTStages, use = gs / kTStages;
-                if (use > 0) mbar_wait(&s.empty[slot], (use - 1) & 1);
+            for (int g = r.g0; g < r.g1; ++g, src += kTStageBytes) {
+                if (!first_round) mbar_wait(&s.empty[slot], par ^ 1);
                 mbar_expect_tx(&s.full[slot], kTStageBytes);
                 tma_load_1d_hint(s.ring + (size_t)slot * kTStageBytes, src, kTStageBytes, &s.full[slot], pol);
+                if (++slot == p.n_stages) slot = 0, par ^= 1, first_round = false;
             }
         }
     }
@@ -191,7 +226,9 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
     // D fp32, A/B bf16, both K-major, M = 128, N = 8
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((8u >> 3) << 17) | ((128u >> 4) << 24);
     const uint32_t ring_a = smem_u32(s.ring), bop_a = smem_u32(s.bop);
-    uint32_t gs = 0, as = 0;
+    uint32_t as = 0;
+    int slot = 0;      // ring position and the parity of its current use, in lock-step with the producer
+    uint32_t par = 0;
     for (int step = 0; step < p.n_steps; ++step) {
         for (int j = 0; j < n_jobs; ++j) {
             const TcdJob &job = s.jobs[j];
@@ -210,12 +247,12 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
                 }
                 const uint32_t d_addr = tmem + aslot * kTAccCols + me * 8;
                 bool first = true;
-                for (int u = 0; g < seg_end; ++g, ++gs, ++u, bslot = (bslot + 1 == r.nkb ? 0 : bslot + 1)) {
+                for (int u = 0; g < seg_end; ++g, ++u, bslot = (bslot + 1 == r.nkb ? 0 : bslot + 1),
+                         par ^= (slot + 1 == p.n_stages), slot = (slot + 1 == p.n_stages ? 0 : slot + 1)) {
                     if ((u % kTIssuers) != me) continue;
-                    const uint32_t slot = gs % kTStages, use = gs / kTStages;
-                    mbar_wait(&s.full[slot], use & 1);
+                    mbar_wait(&s.full[slot], par);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint64_t adesc = tcd_desc(ring_a + slot * kTStageBytes, 1024);
+                    const uint64_t adesc = tcd_desc(ring_a + (uint32_t)slot * kTStageBytes, 1024);
                     const uint64_t bdesc = tcd_desc(bop_a + (uint32_t)bslot * 1024, 0);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {

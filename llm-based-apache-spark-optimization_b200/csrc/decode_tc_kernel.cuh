@@ -6,13 +6,13 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
     extern __shared__ uint8_t smem_dyn[];
     // the swizzled operand tiles need 1024-byte alignment
     uint8_t *smem_raw = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
-    const TcdSmem s = tcd_carve(smem_raw, HD, GQ);
+    const TcdSmem s = tcd_carve(smem_raw, HD, GQ, p.n_stages, p.n_bslots);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int G = gridDim.x, bid = blockIdx.x;
     const int n_jobs = 4 * p.n_layers + 1;
 
     if (tid == 0) {
-        for (int i = 0; i < kTStages; ++i) {
+        for (int i = 0; i < kTMaxStages; ++i) {
             mbar_init(&s.full[i], 1);
             mbar_init(&s.empty[i], 1);
         }
@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
         uint32_t *dst = reinterpret_cast<uint32_t *>(s.jobs);
         for (int i = tid; i < n_jobs * (int)(sizeof(TcdJob) / 4); i += kTThreads) dst[i] = src[i];
         for (int i = tid; i < min(p.n_ptab, kTMaxPtab); i += kTThreads) s.ptab[i] = p.page_table[i];
-        for (int i = tid; i < kTBSlots * 1024 / 16; i += kTThreads) reinterpret_cast<uint4 *>(s.bop)[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = tid; i < p.n_bslots * 1024 / 16; i += kTThreads) reinterpret_cast<uint4 *>(s.bop)[i] = make_uint4(0u, 0u, 0u, 0u);
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -173,8 +173,10 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
 
 template <int HD, int GQ>
 static int tcd_launch_t(const TcdParams &p, cudaStream_t stream) {
-    const size_t smem = tcd_smem_bytes(HD, GQ, 4 * p.n_layers + 1);
-    B200_REQUIRE(smem <= 232448, "tcd: %zu bytes of shared memory needed", smem);
+    B200_REQUIRE(p.n_stages >= 4 && p.n_stages <= kTMaxStages && p.n_bslots >= 1 && p.n_bslots <= kTBSlots,
+                 "tcd: bad ring plan (%d stages, %d operand blocks)", p.n_stages, p.n_bslots);
+    const size_t smem = tcd_smem_bytes(HD, GQ, 4 * p.n_layers + 1, p.n_stages, p.n_bslots);
+    B200_REQUIRE(smem <= kTSmemLimit, "tcd: %zu bytes of shared memory needed", smem);
     B200_CUDA_OK(cudaFuncSetAttribute(tcd_decode_kernel<HD, GQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int dev = 0, sms = 0;
     B200_CUDA_OK(cudaGetDevice(&dev));

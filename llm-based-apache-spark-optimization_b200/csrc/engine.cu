@@ -723,7 +723,7 @@ static bool tcd_usable(const b200llm_engine *e) {
     if (getenv("B200LLM_NO_TCD")) return false;
     bool tiled = e->lm_head_tm != nullptr;
     for (auto &w : e->layers) tiled = tiled && w.wqkv_tm && w.wo_tm && w.wgu_tm && w.wdown_tm;
-    return tiled && tcd_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim, c.vocab);
+    return tiled && tcd_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim, c.vocab, c.n_layers);
 }
 
 static int tcd_prepare(b200llm_engine *e) {
@@ -771,6 +771,9 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps) {
     p.part_ml = p.part_o + (size_t)c.n_q * ns * c.head_dim;
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
+    B200_REQUIRE(tcd_plan(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim, c.vocab, c.n_layers, &p.n_stages, &p.n_bslots),
+                 "tcd: geometry does not fit");
+    if (const char *ns = getenv("B200LLM_TCD_STAGES")) p.n_stages = atoi(ns) < p.n_stages ? atoi(ns) : p.n_stages;
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     // the qkv and gate/up phases ADD into these rows; later layers find them cleared by the o_proj phase
     B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)(c.n_q + 2 * c.n_kv) * c.head_dim * 4, e->stream));
@@ -1074,6 +1077,8 @@ int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, 
     p.gen_out = reinterpret_cast<int32_t *>(scr + 3712), p.n_steps = 1, p.n_splits = 1;
     p.bar_ctr = reinterpret_cast<unsigned *>(scr + 3776);
     p.sample = 0, p.split_all = k_split ? 1 : 0;
+    p.n_bslots = tcd_job_slots(N, K, !k_split);
+    p.n_stages = tcd_stages_for(128, 1, 1, p.n_bslots);
     rc = tcd_decode_launch(p, st);
     cudaError_t ce = cudaStreamSynchronize(st);
     cudaFree(scr);

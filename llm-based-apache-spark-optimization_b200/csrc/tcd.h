@@ -52,13 +52,18 @@ struct TcdParams {
     int32_t n_splits;
     unsigned *bar_ctr;    // grid barrier counter (zeroed before every launch)
     int32_t sample;       // 1: greedy argmax + feedback inside the kernel; 0: stop after the logits
+    int32_t n_stages;     // ring stages of 16 KB (<= 10) and operand blocks of 1 KB (<= 64) in shared memory: tcd_plan()
+    int32_t n_bslots;
     int32_t split_all;    // (test hook) k-split the last job too instead of giving whole tiles
     unsigned long long *trace;  // optional [2][1024] globaltimer stamps of CTA 0 and CTA G-1 (debug)
     int32_t trace_step;
 };
 
 int tcd_decode_launch(const TcdParams &p, cudaStream_t stream);
-bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab);
+bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers);
+bool tcd_plan(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers, int *n_stages, int *n_bslots);
+int tcd_job_slots(int N, int K, bool whole_tiles);
+int tcd_stages_for(int head_dim, int gq, int n_jobs, int n_bslots);
 // per-phase check that the activation operand of one CTA fits its 64 k-block buffer
 bool tcd_job_fits(int N, int K, bool whole_tiles);
 

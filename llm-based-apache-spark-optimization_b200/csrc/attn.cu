@@ -27,6 +27,7 @@ struct AttnDev {
     float *part_ml;    // [rows, n_q, n_splits, 2]
     unsigned *tickets; // [rows, n_kv]
     float scale_log2;  // 1/sqrt(hd) * log2(e)
+    uint16_t *out_bf16; // when set, the output goes here as bf16 (the next GEMM's operand) instead of a.out
 };
 
 __device__ __forceinline__ void merge_state(float &m, float &l, float m2, float l2, float &c1, float &c2) {
@@ -249,7 +250,10 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
         }
         const int hq = hk * G + g;
         if (single) {
-            a.out[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = O / L;
+            if (p.out_bf16 != nullptr)
+                p.out_bf16[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = f32_to_bf16_bits(O / L);
+            else
+                a.out[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = O / L;
         } else {
             const size_t pi = ((size_t)row * a.n_q + hq) * n_splits + split;
             p.part_o[pi * HD + dd] = O;
@@ -282,7 +286,10 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
             L += __ldcg(&p.part_ml[(pb + s) * 2 + 1]) * c;
             O += __ldcg(&p.part_o[(pb + s) * HD + dd]) * c;
         }
-        a.out[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = O / L;
+        if (p.out_bf16 != nullptr)
+            p.out_bf16[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = f32_to_bf16_bits(O / L);
+        else
+            a.out[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = O / L;
     }
     if (tid == 0) p.tickets[(size_t)row * a.n_kv + hk] = 0;  // leave the ticket at zero for the next launch
 }
@@ -308,7 +315,7 @@ static int launch_attn(const AttnDev &d, cudaStream_t stream, bool pdl) {
     return B200LLM_OK;
 }
 
-int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl) {
+int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16) {
     B200_REQUIRE(a.page_tokens == kPT, "attn: page_tokens must be %d (got %d)", kPT, a.page_tokens);
     B200_REQUIRE(a.n_kv > 0 && a.n_q % a.n_kv == 0, "attn: n_q %d not a multiple of n_kv %d", a.n_q, a.n_kv);
     B200_REQUIRE(a.bs >= 1 && a.bs <= 65535 && a.n_splits >= 1 && a.n_splits <= 64, "attn: bad bs/n_splits");
@@ -317,8 +324,9 @@ int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl
         set_error("attn: scratch too small (%zu < %zu)", a.scratch_bytes, need);
         return B200LLM_ENOMEM;
     }
-    AttnDev d;
+    AttnDev d{};
     d.a = a;
+    d.out_bf16 = reinterpret_cast<uint16_t *>(out_bf16);
     d.scale_log2 = (float)(1.4426950408889634 / sqrt((double)a.head_dim));
     uint8_t *s = reinterpret_cast<uint8_t *>(a.scratch);
     B200_REQUIRE((size_t)a.bs * a.n_kv * 4 <= kAttnTicketBytes, "attn: bs * n_kv exceeds %zu tickets", kAttnTicketBytes / 4);
@@ -406,7 +414,7 @@ extern "C" int b200llm_op_attn_decode_static(const b200llm_attn_args *a, void *s
     // the buffer is shared by every call and keeps the last call's contents: the tickets must
     // start at zero, whatever an earlier (possibly failed) launch left behind
     B200_CUDA_OK(cudaMemsetAsync(base, 0, kStaticTicketBytes, st));
-    AttnDev d;
+    AttnDev d{};
     d.a = *a;
     d.a.scratch = base, d.a.scratch_bytes = kStaticScratchBytes;
     d.scale_log2 = (float)(1.4426950408889634 / sqrt((double)a->head_dim));

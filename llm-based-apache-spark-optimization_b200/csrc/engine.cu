@@ -126,7 +126,7 @@ struct b200llm_engine {
     unsigned *bar_ctr = nullptr;
     unsigned long long *trace = nullptr;
     // batch / prefill path
-    uint16_t *xb = nullptr;
+    uint16_t *xb = nullptr, *xb2 = nullptr;
     bool tc_pdl = true;
     float *qkv_out = nullptr, *gu_out = nullptr;
     struct MapBox { alignas(128) unsigned char b[128]; };
@@ -173,7 +173,7 @@ static int check_cfg(const b200llm_config *c) {
 struct WsLayout {
     size_t h, q, att, act, delta, logits, part_max, part_idx, row_lane, row_pos, row_token, pf_lane, pf_pos,
         pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
-        attn_scratch, mega_jobs, bar_ctr, trace, xb, qkv_out, gu_out, total;
+        attn_scratch, mega_jobs, bar_ctr, trace, xb, xb2, qkv_out, gu_out, total;
     size_t attn_scratch_bytes;
     int lm_grid, attn_splits;
 };
@@ -235,6 +235,7 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
         size_t widest = c->d > (int)(nq_l * c->head_dim) ? c->d : nq_l * c->head_dim;
         if (ffn_l > widest) widest = ffn_l;
         w->xb = take(R * widest * 2);
+        w->xb2 = take(R * ffn_l * 2);   // SwiGLU output of the fused gate/up GEMM epilogue (xb is that GEMM's input)
         w->qkv_out = take(R * (nq_l + 2 * nkv_l) * c->head_dim * 4);
         w->gu_out = take(R * 2 * ffn_l * 4);
     }
@@ -460,7 +461,7 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->mega_jobs = (MegaJob *)(b + w.mega_jobs);
     e->bar_ctr = (unsigned *)(b + w.bar_ctr);
     e->trace = (unsigned long long *)(b + w.trace);
-    e->xb = (uint16_t *)(b + w.xb), e->qkv_out = (float *)(b + w.qkv_out), e->gu_out = (float *)(b + w.gu_out);
+    e->xb = (uint16_t *)(b + w.xb), e->xb2 = (uint16_t *)(b + w.xb2), e->qkv_out = (float *)(b + w.qkv_out), e->gu_out = (float *)(b + w.gu_out);
     e->mega_ready = false;
     e->tcd_ready = false;
     e->samp_host.assign(e->cfg.max_lanes, b200llm_sampling{0.f, 0, 1.f, 1.f, 0});
@@ -810,19 +811,21 @@ static bool tc_usable(const b200llm_engine *e, int rows) {
 
 // out (+)= X W^T through the tcgen05 kernel; X = e->xb viewed as [max_rows, K]
 static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, int64_t out_stride, int T,
-                   bool add_to_existing, bool prezeroed = false) {
+                   bool add_to_existing, bool prezeroed = false, const void *x_buf = nullptr, void *out_swiglu = nullptr) {
     const void *mw, *mx;
     B200_TRY(get_map(e, w, N, K, 128, &mw));
-    B200_TRY(get_map(e, e->xb, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mx));
+    B200_TRY(get_map(e, x_buf ? x_buf : e->xb, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mx));
     int accumulate = 1;
-    if (!add_to_existing) {
+    if (out_swiglu != nullptr) {
+        accumulate = 0;
+    } else if (!add_to_existing) {
         if (N / 128 >= kNumSMs) {
             accumulate = 0;  // enough row tiles: no k split, plain stores
         } else if (!prezeroed) {
             B200_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)T * out_stride * 4, e->stream));
         }
     }
-    B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, e->tc_pdl));
+    B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, e->tc_pdl, out_swiglu));
     e->launches++;
     return B200LLM_OK;
 }
@@ -855,14 +858,22 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         if (want > 6) want = 6;
         at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
         at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
-        B200_TRY(attn_decode_launch(at, st, pdl));
-        B200_TRY(cast_bf16_launch(e->att, qd, e->xb, rows, qd, st, pdl));
+        B200_TRY(attn_decode_launch(at, st, pdl, e->xb));  // output rounded to bf16 straight into the o_proj operand
         B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->h, c.d, rows, true));
-        B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->gu_out, 2 * c.ffn));
-        B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false, true));
-        B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, c.ffn, st, pdl));
-        B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true));
-        e->launches += 6;
+        // gate/up: with >= 74 row tiles the GEMM runs without a k split and applies SwiGLU in its epilogue
+        const bool fuse_swiglu = 2 * c.ffn / 128 > kNumSMs / 2;
+        if (fuse_swiglu) {
+            B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl));
+            B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false, true, nullptr, e->xb2));
+            B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true, false, e->xb2));
+            e->launches += 4;
+        } else {
+            B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->gu_out, 2 * c.ffn));
+            B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false, true));
+            B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, c.ffn, st, pdl));
+            B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true));
+            e->launches += 5;
+        }
     }
     e->last_rows = rows;
     e->last_logit_rows = pr.logit_rows;

@@ -35,6 +35,8 @@ struct TcParams {
     int32_t stages;
     int32_t accumulate;  // 1: out += (red.add), 0: plain store (only valid with one k split)
     int32_t tmem_cols;   // power of two >= max(32, bn)
+    uint16_t *out_swiglu; // when set (needs one k split): rows (2i, 2i+1) = (gate_i, up_i) -> bf16 silu(gate) * up at
+                          // out_swiglu[t, i], row stride N / 2, instead of the fp32 output
 };
 
 __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
@@ -160,6 +162,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                 : "r"(taddr));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (p.out_swiglu != nullptr) {
+                // fused SwiGLU: gate and up of one unit sit in adjacent accumulator lanes = adjacent threads
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const int t = c0 + j;
+                    const float mine = __uint_as_float(v[j]);
+                    const float other = __shfl_xor_sync(0xffffffffu, mine, 1);
+                    if ((lane & 1) == 0 && t < p.T && n < p.N)
+                        p.out_swiglu[(size_t)t * (p.N >> 1) + (n >> 1)] = f32_to_bf16_bits((mine / (1.f + expf(-mine))) * other);
+                }
+                continue;
+            }
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
                 const int t = c0 + j;
@@ -223,7 +237,7 @@ int tc_make_map(void *map_out, const void *base, int64_t rows, int64_t cols, int
 }
 
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
-                   int accumulate, cudaStream_t stream, bool pdl) {
+                   int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu) {
     B200_REQUIRE(T >= 1 && T <= 256 && N % kTcBM == 0 && K % kTcBK == 0, "gemm_tc: need 1 <= T <= 256, N %% 128 == 0, K %% 64 == 0 (T %d N %d K %d)", T, N, K);
     TcParams p{};
     p.out = out, p.out_stride = out_stride, p.T = T, p.N = N, p.K = K;
@@ -233,7 +247,8 @@ int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out
     const int k_iters = K / kTcBK;
     if (ks < 1) ks = 1;
     if (ks > k_iters) ks = k_iters;
-    if (!accumulate) ks = 1;  // a plain store needs the whole K in one CTA
+    if (!accumulate || out_swiglu != nullptr) ks = 1;  // a plain store / the fused SwiGLU needs the whole K in one CTA
+    p.out_swiglu = reinterpret_cast<uint16_t *>(out_swiglu);
     const int it_per = (k_iters + ks - 1) / ks;
     ks = (k_iters + it_per - 1) / it_per;
     p.k_per_split = it_per * kTcBK;

@@ -12,7 +12,7 @@ int gemv_launch(const b200llm_gemv_args &a, cudaStream_t stream, bool pdl);
 int gemv_grid(int N, int K, int bs, int epi, int grid_hint);
 
 // attn.cu
-int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl);
+int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16 = nullptr);
 size_t attn_scratch_bytes(int bs, int n_q, int n_kv, int head_dim, int n_splits);
 // The arrival tickets live in a fixed-size region at the start of the scratch buffer, so that
 // launches with different batch sizes sharing one buffer never put partials where another
@@ -55,7 +55,7 @@ int sample_launch(const SampleDev &a, cudaStream_t stream, bool pdl);
 // gemm_tc.cu: tcgen05 GEMM  out[t, n] (+)= sum_k X[t, k] W[n, k]  (bf16 in, fp32 out), T <= 256
 int tc_make_map(void *map_out_128B, const void *base, int64_t rows, int64_t cols, int box_rows);
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
-                   int accumulate, cudaStream_t stream, bool pdl);
+                   int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu = nullptr);
 // batch_ops.cu
 int rmsnorm_bf16_launch(const float *x, const void *gain, void *out, int rows, int d, float eps, cudaStream_t s, bool pdl,
                         float *zero = nullptr, int zero_w = 0);

@@ -199,6 +199,27 @@ def test_tensor_core_batch_path_matches_bf16_activation_oracle(name, golden_dir)
     eng.close()
 
 
+def test_tensor_core_path_with_fused_swiglu_epilogue():
+    """A geometry whose gate/up matrix has >= 74 row tiles: the tcgen05 GEMM then runs without a k
+    split and applies SwiGLU in its epilogue (bf16 straight into the down-projection operand), and
+    the attention kernel writes its output as bf16.  Same bf16-activation oracle as above."""
+    from b200llm import Engine, geometry, weights
+    og = lo.OracleGeometry("wide", 256, 2, 4, 2, 64, 4864, 1024, True, 5e5, True)      # 2 * ffn / 128 = 76 tiles
+    geo = geometry.Geometry("wide", 256, 2, 4, 2, 64, 4864, 1024, True, 5e5, True)
+    sd = lo.make_weights(og, 0xB200 + 7, sigma=0.05, embed_sigma=0.05)
+    orc = lo.LlamaOracle(og, sd, kv_dtype=torch.bfloat16, act_dtype=torch.bfloat16)
+    eng = Engine(geo, weights.pack(geo, {k: v.cuda() for k, v in sd.items()}), max_lanes=4, max_ctx=256, max_rows=64,
+                 use_tc=True, use_megakernel=False)
+    prompts = [wg.gen_tokens(37 + 11 * i, 900 + i, geo.vocab) for i in range(4)]
+    lanes = [eng.open_lane() for _ in prompts]
+    for ln, p in zip(lanes, prompts):
+        ref = orc.forward(torch.as_tensor(p, dtype=torch.int64), orc.new_state())
+        eng.prefill(ln, p)
+        eng.sync()
+        assert _rel(eng.logits(0), ref.numpy()) <= LOGIT_TOL
+    eng.close()
+
+
 def test_scheduler_batches_concurrent_callers():
     """Threaded callers (the Flask dev server case) share one engine through the scheduler: every
     request gets exactly the tokens it gets when run alone, whatever it was batched with."""

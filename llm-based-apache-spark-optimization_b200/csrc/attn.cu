@@ -28,6 +28,7 @@ struct AttnDev {
     unsigned *tickets; // [rows, n_kv]
     float scale_log2;  // 1/sqrt(hd) * log2(e)
     uint16_t *out_bf16; // when set, the output goes here as bf16 (the next GEMM's operand) instead of a.out
+    int64_t out_lo_off; // != 0: the bf16 lo parts (value - hi) go to out_bf16 + out_lo_off
 };
 
 __device__ __forceinline__ void merge_state(float &m, float &l, float m2, float l2, float &c1, float &c2) {
@@ -250,9 +251,14 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
         }
         const int hq = hk * G + g;
         if (single) {
-            if (p.out_bf16 != nullptr)
-                p.out_bf16[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = f32_to_bf16_bits(O / L);
-            else
+            if (p.out_bf16 != nullptr) {
+                const float y = O / L;
+                const uint16_t yh = f32_to_bf16_bits(y);
+                p.out_bf16[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = yh;
+                if (p.out_lo_off != 0)
+                    p.out_bf16[p.out_lo_off + (size_t)row * a.n_q * HD + (size_t)hq * HD + dd] =
+                        f32_to_bf16_bits(y - __uint_as_float((uint32_t)yh << 16));
+            } else
                 a.out[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = O / L;
         } else {
             const size_t pi = ((size_t)row * a.n_q + hq) * n_splits + split;
@@ -286,9 +292,14 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
             L += __ldcg(&p.part_ml[(pb + s) * 2 + 1]) * c;
             O += __ldcg(&p.part_o[(pb + s) * HD + dd]) * c;
         }
-        if (p.out_bf16 != nullptr)
-            p.out_bf16[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = f32_to_bf16_bits(O / L);
-        else
+        if (p.out_bf16 != nullptr) {
+            const float y = O / L;
+            const uint16_t yh = f32_to_bf16_bits(y);
+            p.out_bf16[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = yh;
+            if (p.out_lo_off != 0)
+                p.out_bf16[p.out_lo_off + (size_t)row * a.n_q * HD + (size_t)hq * HD + dd] =
+                    f32_to_bf16_bits(y - __uint_as_float((uint32_t)yh << 16));
+        } else
             a.out[(size_t)row * a.n_q * HD + (size_t)hq * HD + dd] = O / L;
     }
     if (tid == 0) p.tickets[(size_t)row * a.n_kv + hk] = 0;  // leave the ticket at zero for the next launch
@@ -315,7 +326,7 @@ static int launch_attn(const AttnDev &d, cudaStream_t stream, bool pdl) {
     return B200LLM_OK;
 }
 
-int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16) {
+int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16, int64_t out_lo_off) {
     B200_REQUIRE(a.page_tokens == kPT, "attn: page_tokens must be %d (got %d)", kPT, a.page_tokens);
     B200_REQUIRE(a.n_kv > 0 && a.n_q % a.n_kv == 0, "attn: n_q %d not a multiple of n_kv %d", a.n_q, a.n_kv);
     B200_REQUIRE(a.bs >= 1 && a.bs <= 65535 && a.n_splits >= 1 && a.n_splits <= 64, "attn: bad bs/n_splits");
@@ -327,6 +338,7 @@ int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl
     AttnDev d{};
     d.a = a;
     d.out_bf16 = reinterpret_cast<uint16_t *>(out_bf16);
+    d.out_lo_off = out_lo_off;
     d.scale_log2 = (float)(1.4426950408889634 / sqrt((double)a.head_dim));
     uint8_t *s = reinterpret_cast<uint8_t *>(a.scratch);
     B200_REQUIRE((size_t)a.bs * a.n_kv * 4 <= kAttnTicketBytes, "attn: bs * n_kv exceeds %zu tickets", kAttnTicketBytes / 4);

@@ -127,6 +127,7 @@ struct b200llm_engine {
     unsigned long long *trace = nullptr;
     // batch / prefill path
     uint16_t *xb = nullptr, *xb2 = nullptr;
+    int64_t xb_lo = 0, xb2_lo = 0;   // element offsets of the lo parts inside xb / xb2 (0: single-bf16 activations)
     bool tc_pdl = true;
     float *qkv_out = nullptr, *gu_out = nullptr;
     struct MapBox { alignas(128) unsigned char b[128]; };
@@ -175,6 +176,7 @@ struct WsLayout {
         pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
         attn_scratch, mega_jobs, bar_ctr, trace, xb, xb2, qkv_out, gu_out, total;
     size_t attn_scratch_bytes;
+    size_t xb_lo_off, xb2_lo_off;
     int lm_grid, attn_splits;
 };
 
@@ -234,8 +236,11 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     {   // batch / prefill path (tcgen05 GEMM): bf16 activations and fp32 GEMM outputs
         size_t widest = c->d > (int)(nq_l * c->head_dim) ? c->d : nq_l * c->head_dim;
         if (ffn_l > widest) widest = ffn_l;
-        w->xb = take(R * widest * 2);
-        w->xb2 = take(R * ffn_l * 2);   // SwiGLU output of the fused gate/up GEMM epilogue (xb is that GEMM's input)
+        // bf16 GEMM operands: hi parts, then (at a fixed element offset) the lo parts x - hi
+        w->xb_lo_off = R * widest;
+        w->xb2_lo_off = R * ffn_l;
+        w->xb = take(2 * R * widest * 2);
+        w->xb2 = take(2 * R * ffn_l * 2);   // SwiGLU output of the fused gate/up GEMM epilogue (xb is that GEMM's input)
         w->qkv_out = take(R * (nq_l + 2 * nkv_l) * c->head_dim * 4);
         w->gu_out = take(R * 2 * ffn_l * 4);
     }
@@ -461,6 +466,8 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->mega_jobs = (MegaJob *)(b + w.mega_jobs);
     e->bar_ctr = (unsigned *)(b + w.bar_ctr);
     e->trace = (unsigned long long *)(b + w.trace);
+    const bool hilo = getenv("B200LLM_TC_BF16ACT") == nullptr;  // default: hi + lo operand pairs, ~fp32-accurate activations
+    e->xb_lo = hilo ? (int64_t)w.xb_lo_off : 0, e->xb2_lo = hilo ? (int64_t)w.xb2_lo_off : 0;
     e->xb = (uint16_t *)(b + w.xb), e->xb2 = (uint16_t *)(b + w.xb2), e->qkv_out = (float *)(b + w.qkv_out), e->gu_out = (float *)(b + w.gu_out);
     e->mega_ready = false;
     e->tcd_ready = false;
@@ -812,9 +819,12 @@ static bool tc_usable(const b200llm_engine *e, int rows) {
 // out (+)= X W^T through the tcgen05 kernel; X = e->xb viewed as [max_rows, K]
 static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, int64_t out_stride, int T,
                    bool add_to_existing, bool prezeroed = false, const void *x_buf = nullptr, void *out_swiglu = nullptr) {
-    const void *mw, *mx;
+    const void *mw, *mx, *mxl = nullptr;
+    const uint16_t *xb = x_buf ? reinterpret_cast<const uint16_t *>(x_buf) : e->xb;
+    const int64_t lo = xb == e->xb2 ? e->xb2_lo : e->xb_lo;
     B200_TRY(get_map(e, w, N, K, 128, &mw));
-    B200_TRY(get_map(e, x_buf ? x_buf : e->xb, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mx));
+    B200_TRY(get_map(e, xb, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mx));
+    if (lo != 0) B200_TRY(get_map(e, xb + lo, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mxl));
     int accumulate = 1;
     if (out_swiglu != nullptr) {
         accumulate = 0;
@@ -825,7 +835,8 @@ static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, i
             B200_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)T * out_stride * 4, e->stream));
         }
     }
-    B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, e->tc_pdl, out_swiglu));
+    B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, e->tc_pdl, out_swiglu, mxl,
+                            out_swiglu != nullptr ? e->xb2_lo : 0));
     e->launches++;
     return B200LLM_OK;
 }
@@ -846,7 +857,7 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         const LayerW &w = e->layers[l];
         uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
         uint8_t *vl = kl + e->kv_half_stride;
-        B200_TRY(rmsnorm_bf16_launch(e->h, w.attn_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->qkv_out, qkv_w));
+        B200_TRY(rmsnorm_bf16_launch(e->h, w.attn_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->qkv_out, qkv_w, e->xb_lo));
         B200_TRY(tc_gemm(e, w.wqkv, qkv_w, c.d, e->qkv_out, qkv_w, rows, false, true));
         B200_TRY(rope_append_launch(e->qkv_out, e->q, kl, vl, e->inv_freq, pr.row_lane, pr.row_pos, e->page_table, rows,
                                     c.n_q, c.n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, pdl));
@@ -858,19 +869,19 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         if (want > 6) want = 6;
         at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
         at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
-        B200_TRY(attn_decode_launch(at, st, pdl, e->xb));  // output rounded to bf16 straight into the o_proj operand
+        B200_TRY(attn_decode_launch(at, st, pdl, e->xb, e->xb_lo));  // output rounded to bf16 straight into the o_proj operand
         B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->h, c.d, rows, true));
         // gate/up: with >= 74 row tiles the GEMM runs without a k split and applies SwiGLU in its epilogue
         const bool fuse_swiglu = 2 * c.ffn / 128 > kNumSMs / 2;
         if (fuse_swiglu) {
-            B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl));
+            B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, nullptr, 0, e->xb_lo));
             B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false, true, nullptr, e->xb2));
             B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true, false, e->xb2));
             e->launches += 4;
         } else {
-            B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->gu_out, 2 * c.ffn));
+            B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->gu_out, 2 * c.ffn, e->xb_lo));
             B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false, true));
-            B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, c.ffn, st, pdl));
+            B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, c.ffn, st, pdl, e->xb_lo));
             B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true));
             e->launches += 5;
         }
@@ -879,7 +890,7 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
     e->last_logit_rows = pr.logit_rows;
     if (pr.logit_rows <= 0) return B200LLM_OK;
     B200_TRY(rmsnorm_bf16_launch(e->h + (size_t)pr.logit_row0 * c.d, e->final_norm, e->xb, pr.logit_rows, c.d, c.rms_eps,
-                                 st, pdl));
+                                 st, pdl, nullptr, 0, e->xb_lo));
     B200_TRY(tc_gemm(e, e->lm_head, c.vocab, c.d, e->logits, c.vocab, pr.logit_rows, false));
     SampleDev sd{};
     sd.a.logits = e->logits, sd.a.bs = pr.logit_rows, sd.a.vocab = c.vocab;

@@ -35,6 +35,8 @@ struct TcParams {
     int32_t stages;
     int32_t accumulate;  // 1: out += (red.add), 0: plain store (only valid with one k split)
     int32_t tmem_cols;   // power of two >= max(32, bn)
+    int32_t has_lo;       // 1: a second X map holds the bf16 lo parts (x - hi); both are multiplied, ~fp32-accurate activations
+    int64_t swiglu_lo_off; // != 0: lo parts of the fused SwiGLU output go to out_swiglu + swiglu_lo_off
     uint16_t *out_swiglu; // when set (needs one k split): rows (2i, 2i+1) = (gate_i, up_i) -> bf16 silu(gate) * up at
                           // out_swiglu[t, i], row stride N / 2, instead of the fp32 output
 };
@@ -67,12 +69,13 @@ __device__ __forceinline__ uint32_t umma_idesc_bf16(int m, int n) {
 
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
-               const __grid_constant__ TcParams p) {
+               const __grid_constant__ CUtensorMap map_xl, const __grid_constant__ TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int a_bytes = kTcBM * kTcBK * 2;          // 16 KB
     const int b_bytes = p.bn * kTcBK * 2;           // multiple of 2 KB (bn % 16 == 0)
-    const int stage_bytes = a_bytes + ((b_bytes + 1023) & ~1023);
+    const int b_pad = (b_bytes + 1023) & ~1023;
+    const int stage_bytes = a_bytes + (p.has_lo ? 2 : 1) * b_pad;
     uint8_t *tiles = smem;
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)p.stages * stage_bytes);
     uint64_t *empty = full + p.stages;
@@ -92,6 +95,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
         mbar_fence_init();
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+        if (p.has_lo) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_xl) : "memory");
     }
     if (warp == 2) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
@@ -112,14 +116,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                 const int s = i % p.stages, use = i / p.stages;
                 if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
                 uint8_t *a_dst = tiles + (size_t)s * stage_bytes;
-                mbar_expect_tx(&full[s], (uint32_t)(a_bytes + b_bytes));
+                mbar_expect_tx(&full[s], (uint32_t)(a_bytes + (p.has_lo ? 2 : 1) * b_bytes));
                 tma_load_2d(a_dst, &map_w, k0 + i * kTcBK, row0, &full[s]);
                 tma_load_2d(a_dst + a_bytes, &map_x, k0 + i * kTcBK, 0, &full[s]);
+                if (p.has_lo) tma_load_2d(a_dst + a_bytes + b_pad, &map_xl, k0 + i * kTcBK, 0, &full[s]);
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(kTcBM, p.bn);
+            // hi and lo tiles of a stage are contiguous (bn * 128 B is a multiple of 1 KB), so up to bn = 128 they are ONE
+            // B operand of N = 2 bn: columns [0, bn) = W x hi, [bn, 2 bn) = W x lo, added in the epilogue
+            const bool stacked = p.has_lo && p.bn <= 128;
+            const uint32_t idesc = umma_idesc_bf16(kTcBM, stacked ? 2 * p.bn : p.bn);
             for (int i = 0; i < n_k; ++i) {
                 const int s = i % p.stages, use = i / p.stages;
                 mbar_wait(&full[s], use & 1);
@@ -127,6 +135,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                 const uint32_t a_addr = smem_u32(tiles + (size_t)s * stage_bytes);
                 const uint64_t adesc = umma_desc_sw128(a_addr);
                 const uint64_t bdesc = umma_desc_sw128(a_addr + a_bytes);
+                const uint64_t bdesc_lo = umma_desc_sw128(a_addr + a_bytes + b_pad);
 #pragma unroll
                 for (int k = 0; k < kTcBK / 16; ++k) {
                     const uint32_t accum = (i > 0 || k > 0) ? 1u : 0u;
@@ -136,6 +145,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
                         "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc + (uint64_t)(2 * k)), "r"(idesc), "r"(accum)
                         : "memory");
+                    if (p.has_lo && !stacked)  // W x lo(X) into the same accumulator
+                        asm volatile(
+                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+                            "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc_lo + (uint64_t)(2 * k)), "r"(idesc), "r"(1u)
+                            : "memory");
                 }
                 // frees the stage once the MMAs above have read it
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
@@ -162,6 +177,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                 : "r"(taddr));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (p.has_lo && p.bn <= 128) {  // stacked hi | lo accumulator halves
+                uint32_t w[16];
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, "
+                    "%14, %15}, [%16];"
+                    : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]),
+                      "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15])
+                    : "r"(taddr + (uint32_t)p.bn));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+            }
             if (p.out_swiglu != nullptr) {
                 // fused SwiGLU: gate and up of one unit sit in adjacent accumulator lanes = adjacent threads
 #pragma unroll
@@ -169,8 +196,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                     const int t = c0 + j;
                     const float mine = __uint_as_float(v[j]);
                     const float other = __shfl_xor_sync(0xffffffffu, mine, 1);
-                    if ((lane & 1) == 0 && t < p.T && n < p.N)
-                        p.out_swiglu[(size_t)t * (p.N >> 1) + (n >> 1)] = f32_to_bf16_bits((mine / (1.f + expf(-mine))) * other);
+                    if ((lane & 1) == 0 && t < p.T && n < p.N) {
+                        const float y = (mine / (1.f + expf(-mine))) * other;
+                        const uint16_t yh = f32_to_bf16_bits(y);
+                        const size_t at = (size_t)t * (p.N >> 1) + (n >> 1);
+                        p.out_swiglu[at] = yh;
+                        if (p.swiglu_lo_off != 0)
+                            p.out_swiglu[p.swiglu_lo_off + at] = f32_to_bf16_bits(y - __uint_as_float((uint32_t)yh << 16));
+                    }
                 }
                 continue;
             }
@@ -237,7 +270,8 @@ int tc_make_map(void *map_out, const void *base, int64_t rows, int64_t cols, int
 }
 
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
-                   int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu) {
+                   int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu, const void *map_x_lo,
+                   int64_t swiglu_lo_off) {
     B200_REQUIRE(T >= 1 && T <= 256 && N % kTcBM == 0 && K % kTcBK == 0, "gemm_tc: need 1 <= T <= 256, N %% 128 == 0, K %% 64 == 0 (T %d N %d K %d)", T, N, K);
     TcParams p{};
     p.out = out, p.out_stride = out_stride, p.T = T, p.N = N, p.K = K;
@@ -249,14 +283,16 @@ int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out
     if (ks > k_iters) ks = k_iters;
     if (!accumulate || out_swiglu != nullptr) ks = 1;  // a plain store / the fused SwiGLU needs the whole K in one CTA
     p.out_swiglu = reinterpret_cast<uint16_t *>(out_swiglu);
+    p.has_lo = map_x_lo != nullptr ? 1 : 0;
+    p.swiglu_lo_off = swiglu_lo_off;
     const int it_per = (k_iters + ks - 1) / ks;
     ks = (k_iters + it_per - 1) / it_per;
     p.k_per_split = it_per * kTcBK;
     p.accumulate = accumulate;
     int cols = 32;
-    while (cols < p.bn) cols <<= 1;
+    while (cols < ((p.has_lo && p.bn <= 128) ? 2 * p.bn : p.bn)) cols <<= 1;
     p.tmem_cols = cols;
-    const int stage_bytes = kTcBM * kTcBK * 2 + ((p.bn * kTcBK * 2 + 1023) & ~1023);
+    const int stage_bytes = kTcBM * kTcBK * 2 + (p.has_lo ? 2 : 1) * ((p.bn * kTcBK * 2 + 1023) & ~1023);
     int stages = (200 * 1024) / stage_bytes;
     p.stages = stages > 8 ? 8 : (stages < 2 ? 2 : stages);
     const size_t smem = (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16 + 1024;
@@ -267,7 +303,8 @@ int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out
     }
     LaunchCfg lc(dim3(tiles, ks), dim3(kTcThreads), smem, stream, pdl);
     B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, gemm_tc_kernel, *reinterpret_cast<const CUtensorMap *>(map_w),
-                                    *reinterpret_cast<const CUtensorMap *>(map_x), p));
+                                    *reinterpret_cast<const CUtensorMap *>(map_x),
+                                    *reinterpret_cast<const CUtensorMap *>(map_x_lo ? map_x_lo : map_x), p));
     return B200LLM_OK;
 }
 

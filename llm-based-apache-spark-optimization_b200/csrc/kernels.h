@@ -12,7 +12,8 @@ int gemv_launch(const b200llm_gemv_args &a, cudaStream_t stream, bool pdl);
 int gemv_grid(int N, int K, int bs, int epi, int grid_hint);
 
 // attn.cu
-int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16 = nullptr);
+int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16 = nullptr,
+                       int64_t out_lo_off = 0);
 size_t attn_scratch_bytes(int bs, int n_q, int n_kv, int head_dim, int n_splits);
 // The arrival tickets live in a fixed-size region at the start of the scratch buffer, so that
 // launches with different batch sizes sharing one buffer never put partials where another
@@ -55,12 +56,13 @@ int sample_launch(const SampleDev &a, cudaStream_t stream, bool pdl);
 // gemm_tc.cu: tcgen05 GEMM  out[t, n] (+)= sum_k X[t, k] W[n, k]  (bf16 in, fp32 out), T <= 256
 int tc_make_map(void *map_out_128B, const void *base, int64_t rows, int64_t cols, int box_rows);
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
-                   int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu = nullptr);
+                   int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu = nullptr,
+                   const void *map_x_lo = nullptr, int64_t swiglu_lo_off = 0);
 // batch_ops.cu
 int rmsnorm_bf16_launch(const float *x, const void *gain, void *out, int rows, int d, float eps, cudaStream_t s, bool pdl,
-                        float *zero = nullptr, int zero_w = 0);
-int cast_bf16_launch(const float *x, int64_t in_stride, void *out, int rows, int n, cudaStream_t s, bool pdl);
-int swiglu_bf16_launch(const float *gu, void *out, int rows, int ffn, cudaStream_t s, bool pdl);
+                        float *zero = nullptr, int zero_w = 0, int64_t lo_off = 0);
+int cast_bf16_launch(const float *x, int64_t in_stride, void *out, int rows, int n, cudaStream_t s, bool pdl, int64_t lo_off = 0);
+int swiglu_bf16_launch(const float *gu, void *out, int rows, int ffn, cudaStream_t s, bool pdl, int64_t lo_off = 0);
 int rope_append_launch(const float *qkv, float *q, void *k_pages, void *v_pages, const float *inv_freq,
                        const int32_t *row_lane, const int32_t *row_pos, const int32_t *page_table, int rows, int n_q,
                        int n_kv, int hd, int page_tokens, int max_pages, cudaStream_t s, bool pdl);

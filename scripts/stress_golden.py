@@ -16,7 +16,7 @@ prompt, toks, probe = g["prompt"], g["tokens"].tolist(), g["probe_ids"]
 w = weights.random_init(geo, int(g["seed"]), 0, sigma=float(g["sigma"]))
 bad = 0
 for it in range(iters):
-    eng = Engine(geo, w, max_lanes=1, max_ctx=len(prompt) + 128, max_rows=64, use_tc=False, use_megakernel=True)
+    eng = Engine(geo, w, max_lanes=1, max_ctx=len(prompt) + 128, max_rows=256, use_tc=(os.environ.get("B200LLM_STRESS_TC") == "1"), use_megakernel=True)
     lane = eng.open_lane()
     eng.prefill(lane, prompt)
     first, _ = eng.read_lane(lane)

@@ -41,9 +41,14 @@ def _rel(a, b):
 
 @pytest.mark.parametrize("name,use_graphs,use_pdl,mega", [("tiny", False, False, False), ("tiny", True, True, False),
                                                            ("small", True, True, False), ("small", True, False, False),
-                                                           ("tiny", True, False, True), ("small", True, False, True)])
-def test_live_oracle_parity(name, use_graphs, use_pdl, mega, golden_dir):
-    """Engine vs the oracle run live on this box's CPU, weights uploaded from the oracle's stream."""
+                                                           ("tiny", True, False, True), ("small", True, False, True),
+                                                           ("tiny", True, False, "mma"), ("small", True, False, "mma")])
+def test_live_oracle_parity(name, use_graphs, use_pdl, mega, golden_dir, monkeypatch):
+    """Engine vs the oracle run live on this box's CPU, weights uploaded from the oracle's stream.
+    mega: False = per-phase kernels, True = tcgen05 persistent kernel, "mma" = the mma.sync persistent
+    kernel (what geometries that cannot be tiled 128 x 64 fall back to)."""
+    if mega == "mma":
+        monkeypatch.setenv("B200LLM_PERSISTENT", "mma")
     g = np.load(os.path.join(golden_dir, name + ".npz"))
     geo = lo.GEOMETRIES[name]
     sd = lo.make_weights(geo, int(g["seed"]), sigma=float(g["sigma"]), embed_sigma=float(g["embed_sigma"]))
@@ -52,7 +57,7 @@ def test_live_oracle_parity(name, use_graphs, use_pdl, mega, golden_dir):
     toks, lg, mar = orc.greedy(prompt, 64)
     assert toks == g["tokens"].tolist()
     eng = _engine(name, sd, max_lanes=2, max_ctx=256, max_rows=16, use_graphs=use_graphs, use_pdl=use_pdl,
-                  use_megakernel=mega)
+                  use_megakernel=bool(mega))
     lane = eng.open_lane()
     eng.prefill(lane, prompt)
     first, pos = eng.read_lane(lane)

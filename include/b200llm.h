@@ -147,6 +147,16 @@ int b200llm_destroy(b200llm_engine *e);
 /* Rank 0 of a tensor-parallel group calls this and hands the 128 bytes to the other
  * ranks (any host channel); every rank passes them in b200llm_config.nccl_unique_id. */
 int b200llm_nccl_unique_id(void *out128);
+
+/* One-shot all-reduce over NVLink peer memory for tensor parallel (optional; without it the
+ * engine uses ncclAllReduce).  Every rank calls b200llm_tp_export, which allocates the rank's
+ * inbox region and returns its 64-byte CUDA IPC handle; the host gathers the handles of all
+ * ranks (any channel) and passes them, in rank order, to b200llm_tp_import on every rank.  From
+ * then on the two reductions per layer (after o_proj and down_proj) are one kernel each that
+ * pushes the rank's partial sums into the peers' inboxes and adds what the peers pushed.
+ * All ranks must be processes on one node whose GPUs have peer access (NVLink / NVSwitch). */
+int b200llm_tp_export(b200llm_engine *e, void *handle64);
+int b200llm_tp_import(b200llm_engine *e, const void *handles, int32_t n_ranks);
 /* Bytes of scratch (activations, logits, attention split partials) the host must bind. */
 int b200llm_workspace_bytes(const b200llm_config *cfg, size_t *bytes);
 /* Bytes of one KV page across all layers of this rank: n_layers * 2 * (n_kv/tp) * page_tokens * head_dim * 2. */

@@ -93,6 +93,8 @@ SYMBOLS = {
     "b200llm_last_timing": (C.c_int, [C.c_void_p, _P(Timing)]),
     "b200llm_stream": (C.c_void_p, [C.c_void_p]),
     "b200llm_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "b200llm_tp_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "b200llm_tp_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "b200llm_debug_read_trace": (C.c_int, [C.c_void_p, _P(C.c_uint64), C.c_int32]),
     "b200llm_op_gemv": (C.c_int, [_P(GemvArgs), C.c_void_p]),
     "b200llm_op_gemv_grid": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P(C.c_int32)]),

@@ -28,3 +28,17 @@ def shard_bounds(n: int, rank: int, size: int):
     assert n % size == 0
     per = n // size
     return rank * per, (rank + 1) * per
+
+
+def connect_peers(engine, group=None) -> None:
+    """Collective: switch `engine` (one per rank of `group`, all on one node) from ncclAllReduce to the
+    one-shot all-reduce over NVLink peer memory (csrc/tp_ar.cu).  Every rank exports the CUDA IPC handle
+    of its inbox region, the handles travel over torch.distributed, every rank opens its peers'."""
+    size = dist.get_world_size(group)
+    buf = C.create_string_buffer(64)
+    _lib.check(_lib.lib.b200llm_tp_export(engine._h, buf))
+    box = [None] * size
+    dist.all_gather_object(box, bytes(buf.raw), group=group)
+    blob = C.create_string_buffer(b"".join(box), 64 * size)
+    _lib.check(_lib.lib.b200llm_tp_import(engine._h, blob, size))
+    dist.barrier(group)     # nobody reduces before everybody has opened everybody's region

@@ -134,6 +134,14 @@ struct b200llm_engine {
     std::map<std::tuple<const void *, int64_t, int64_t, int>, MapBox *> maps;
     bool mega_ready = false;
     bool tcd_ready = false;
+    // one-shot all-reduce over peer memory (tp_ar.cu): own region + the peers' regions opened through CUDA IPC
+    uint8_t *ar_region = nullptr;
+    void *ar_peer_base[kTpMaxRanks] = {};
+    float *ar_inbox[kTpMaxRanks] = {};
+    unsigned *ar_flags[kTpMaxRanks] = {};
+    unsigned *ar_seq = nullptr;
+    int ar_slot_floats = 0, ar_max_slices = 0;
+    bool ar_ready = false;
     std::vector<b200llm_sampling> samp_host;
     b200llm_sampling *lane_samp;
     void *attn_scratch;
@@ -360,6 +368,65 @@ int b200llm_create(const b200llm_config *cfg, b200llm_engine **out) {
     return B200LLM_OK;
 }
 
+// ---------------------------------------------------------------- peer-memory all-reduce set-up
+static void ar_layout(const b200llm_engine *e, size_t *flag_bytes, size_t *total) {
+    const int tp = e->cfg.tp_size;
+    const size_t slot = (size_t)e->cfg.max_rows * e->cfg.d;
+    const size_t slices = (slot + 1023) / 1024;
+    *flag_bytes = align_up(2 * (size_t)tp * slices * 4 + 256, 256);   // flags, then the local sequence words
+    *total = *flag_bytes + 2 * (size_t)tp * slot * 4;
+}
+
+static void ar_pointers(b200llm_engine *e, int r, uint8_t *base) {
+    size_t flag_bytes, total;
+    ar_layout(e, &flag_bytes, &total);
+    e->ar_flags[r] = reinterpret_cast<unsigned *>(base);
+    e->ar_inbox[r] = reinterpret_cast<float *>(base + flag_bytes);
+}
+
+int b200llm_tp_export(b200llm_engine *e, void *handle64) {
+    B200_REQUIRE(e && handle64, "tp_export: NULL argument");
+    B200_REQUIRE(e->cfg.tp_size >= 2 && e->cfg.tp_size <= kTpMaxRanks, "tp_export: tp_size %d not in [2, %d]", e->cfg.tp_size,
+                 kTpMaxRanks);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+    int rc = require_device(e->cfg.device);
+    if (rc) return rc;
+    size_t flag_bytes, total;
+    ar_layout(e, &flag_bytes, &total);
+    if (!e->ar_region) {
+        B200_CUDA_OK(cudaMalloc(&e->ar_region, total));
+        B200_CUDA_OK(cudaMemset(e->ar_region, 0, total));
+        const size_t slot = (size_t)e->cfg.max_rows * e->cfg.d;
+        e->ar_slot_floats = (int)slot, e->ar_max_slices = (int)((slot + 1023) / 1024);
+        ar_pointers(e, e->cfg.tp_rank, e->ar_region);
+        e->ar_seq = reinterpret_cast<unsigned *>(e->ar_region + flag_bytes - 256);
+    }
+    cudaIpcMemHandle_t h;
+    B200_CUDA_OK(cudaIpcGetMemHandle(&h, e->ar_region));
+    memcpy(handle64, &h, 64);
+    return B200LLM_OK;
+}
+
+int b200llm_tp_import(b200llm_engine *e, const void *handles, int32_t n) {
+    B200_REQUIRE(e && handles && e->ar_region, "tp_import: call tp_export first");
+    B200_REQUIRE(n == e->cfg.tp_size, "tp_import: %d handles for tp_size %d", n, e->cfg.tp_size);
+    int rc = require_device(e->cfg.device);
+    if (rc) return rc;
+    for (int r = 0; r < n; ++r) {
+        if (r == e->cfg.tp_rank || e->ar_peer_base[r]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, reinterpret_cast<const uint8_t *>(handles) + 64 * (size_t)r, 64);
+        void *base = nullptr;
+        B200_CUDA_OK(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+        e->ar_peer_base[r] = base;
+        ar_pointers(e, r, reinterpret_cast<uint8_t *>(base));
+    }
+    e->ar_ready = true;
+    for (auto &kv : e->graphs) cudaGraphExecDestroy(kv.second);   // steps captured with the NCCL all-reduce are stale
+    e->graphs.clear();
+    return B200LLM_OK;
+}
+
 int b200llm_nccl_unique_id(void *out128) {
     B200_REQUIRE(out128 != nullptr, "out is NULL");
     int rc = nccl_load();
@@ -374,6 +441,9 @@ int b200llm_destroy(b200llm_engine *e) {
     for (auto &kv : e->graphs) cudaGraphExecDestroy(kv.second);
     for (auto &m : e->maps) delete m.second;
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
+    for (int r = 0; r < kTpMaxRanks; ++r)
+        if (e->ar_peer_base[r]) cudaIpcCloseMemHandle(e->ar_peer_base[r]);
+    if (e->ar_region) cudaFree(e->ar_region);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(e->ev[i]);
     if (e->own_stream) cudaStreamDestroy(e->stream);
     delete e;
@@ -565,6 +635,12 @@ static int gemv_rows(b200llm_engine *e, b200llm_gemv_args a, int rows, const Pas
 
 static int tp_allreduce_add(b200llm_engine *e, int rows) {
     const size_t n = (size_t)rows * e->cfg.d;
+    if (e->ar_ready) {   // peers connected (b200llm_tp_import): one kernel, one NVLink round trip
+        B200_TRY(tp_allreduce_add_launch(e->h, e->delta, (int)n, e->ar_inbox, e->ar_flags, e->ar_seq, e->cfg.tp_rank,
+                                         e->cfg.tp_size, e->ar_slot_floats, e->ar_max_slices, e->stream));
+        e->launches++;
+        return B200LLM_OK;
+    }
     B200_NCCL_OK(g_nccl.AllReduce(e->delta, e->delta, n, kNcclFloat32, kNcclSum, e->comm, e->stream));
     B200_TRY(add_inplace_launch(e->h, e->delta, n, e->stream, false));
     e->launches++;

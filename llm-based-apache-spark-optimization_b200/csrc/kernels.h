@@ -58,6 +58,10 @@ int tc_make_map(void *map_out_128B, const void *base, int64_t rows, int64_t cols
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
                    int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu = nullptr,
                    const void *map_x_lo = nullptr, int64_t swiglu_lo_off = 0);
+// tp_ar.cu: one-shot all-reduce + residual add over NVLink peer memory (h += sum over ranks of delta)
+constexpr int kTpMaxRanks = 8;
+int tp_allreduce_add_launch(float *h, const float *delta, int n, float *const *inbox, unsigned *const *flags,
+                            unsigned *seq, int rank, int size, int slot_floats, int max_slices, cudaStream_t stream);
 // batch_ops.cu
 int rmsnorm_bf16_launch(const float *x, const void *gain, void *out, int rows, int d, float eps, cudaStream_t s, bool pdl,
                         float *zero = nullptr, int zero_w = 0, int64_t lo_off = 0);

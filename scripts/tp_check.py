@@ -25,6 +25,8 @@ for name in (["small", "duckdb-nsql"] if len(sys.argv) < 2 else sys.argv[1:]):
         # shard the device-generated logical tensors layer by layer (full model never resident twice)
         w = weights.random_init(geo, 0xB200, local, tp_rank=rank, tp_size=world)
     eng = Engine(geo, w, device=local, max_lanes=2, max_ctx=512, max_rows=16, tp_rank=rank, tp_size=world, nccl_id=uid)
+    if os.environ.get("B200LLM_TP_NCCL_ONLY") != "1":
+        tp.connect_peers(eng)      # one-shot all-reduce over NVLink peer memory instead of ncclAllReduce
     lane = eng.open_lane()
     eng.prefill(lane, prompt)
     first, _ = eng.read_lane(lane)

@@ -56,13 +56,13 @@ class Engine:
         if not torch.cuda.is_available():
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         self.geo, self.weights, self.device = geo, weights, device
-        if use_megakernel and tp_size == 1 and not any(k >= _lib.W_QKV_ST for k, _, _ in weights.tensors):
+        if use_megakernel and not any(k >= _lib.W_QKV_ST for k, _, _ in weights.tensors):
             # the persistent kernels stream their own copies of the matrices: tile-major for the
             # tcgen05 kernel, stage-major for the mma.sync one (geometries the former cannot tile)
             from .weights import add_stage_major, add_tile_major, tile_major_ok
-            if tile_major_ok(geo) and os.environ.get("B200LLM_PERSISTENT", "tc") == "tc":
-                add_tile_major(weights)
-            else:
+            if tile_major_ok(geo, tp_size) and os.environ.get("B200LLM_PERSISTENT", "tc") == "tc":
+                add_tile_major(weights)     # (tensor parallel: of this rank's shards; used once tp.connect_peers ran)
+            elif tp_size == 1:
                 add_stage_major(weights)
         self.max_lanes, self.max_rows = max_lanes, max_rows
         self.max_pages_per_lane = (max_ctx + PAGE_TOKENS - 1) // PAGE_TOKENS

@@ -108,9 +108,11 @@ def tile_major(w: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def tile_major_ok(geo) -> bool:
-    qkv = (geo.n_q + 2 * geo.n_kv) * geo.head_dim
-    shapes = [(qkv, geo.d), (geo.d, geo.n_q * geo.head_dim), (2 * geo.ffn, geo.d), (geo.d, geo.ffn), (geo.vocab, geo.d)]
+def tile_major_ok(geo, tp_size: int = 1) -> bool:
+    """Can every matrix of one rank's shard be cut into [128 x 64] tiles?"""
+    nq, nkv, ffn, vocab = geo.n_q // tp_size, geo.n_kv // tp_size, geo.ffn // tp_size, geo.vocab // tp_size
+    qkv = (nq + 2 * nkv) * geo.head_dim
+    shapes = [(qkv, geo.d), (geo.d, nq * geo.head_dim), (2 * ffn, geo.d), (geo.d, ffn), (vocab, geo.d)]
     return all(n % 128 == 0 and k % 64 == 0 for n, k in shapes)
 
 
@@ -121,7 +123,7 @@ _TM_KIND = {_lib.W_QKV: _lib.W_QKV_TM, _lib.W_O: _lib.W_O_TM, _lib.W_GATE_UP: _l
 def add_tile_major(pw: "PackedWeights", start: int = 0) -> None:
     """Append tile-major copies of the matrices pw.tensors[start:] (tcgen05 persistent-kernel layout)."""
     for kind, layer, t in list(pw.tensors[start:]):
-        if kind in _TM_KIND and pw.tp_size == 1:
+        if kind in _TM_KIND:
             pw.tensors.append((_TM_KIND[kind], layer, tile_major(t)))
 
 

@@ -288,6 +288,7 @@ struct TcdCtx {
     int ti;               // trace cursor (-1: tracing off for this step)
     uint32_t as;          // accumulator counter, in lock-step with the MMA issuer
     int att_ns;           // split-T factor of this step's attention phases
+    unsigned ar_s, tok_s; // tensor parallel: sequence numbers of the reductions / token exchanges done so far
     float best;           // lm_head: running (max, argmax) of this thread
     int best_i;
 };

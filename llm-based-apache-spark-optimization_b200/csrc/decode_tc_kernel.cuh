@@ -48,6 +48,8 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
     } else {
         TcdCtx c;
         c.as = 0;
+        c.ar_s = c.tok_s = 0;
+        if (p.tp_size > 1) c.ar_s = __ldcg(p.ar_seq), c.tok_s = __ldcg(p.ar_seq + 2);
         c.tok = __ldcg(p.lane_token + p.lane);
         c.pos = __ldcg(p.lane_pos + p.lane);
         unsigned bar_no = 0;
@@ -63,7 +65,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
         for (int step = 0; step < p.n_steps; ++step) {
             c.ti = (p.trace != nullptr && step == p.trace_step && (bid == 0 || bid == G - 1)) ? 0 : -1;
             tcd_trace(p, c.ti, bid, tid, TT_STEP);
-            c.tok = min(max(c.tok, 0), p.vocab - 1);
+            c.tok = min(max(c.tok, 0), p.vocab_global - 1);
             if (bid == 0 && tid == 0) p.lane_hist[(size_t)p.lane * 64 + (c.pos & 63)] = c.tok;
             c.att_ns = min(p.n_splits, (2 * (c.pos / kTPT + 1) + kTW - 1) / kTW);  // as in tcd_attn_phase
             if (tid < HD / 2) {  // RoPE angles of this position
@@ -96,6 +98,10 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                if (p.tp_size > 1) {   // o_proj is row-parallel: h += sum over ranks of the partial sums
+                    tcd_allreduce_phase(p, c, G, bid, tid);
+                    tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                }
                 phase(4 * l + 2);  // rmsnorm + gate/up (raw sums)
                 arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
@@ -104,6 +110,10 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                if (p.tp_size > 1) {   // down_proj is row-parallel too
+                    tcd_allreduce_phase(p, c, G, bid, tid);
+                    tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                }
             }
             // ---- final norm + lm_head: logits, per-CTA (max, lowest argmax) ----
             c.best = -INFINITY, c.best_i = 0x7fffffff;
@@ -152,6 +162,10 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                     const int oi = s.misc[24 + w];
                     if (om > m || (om == m && oi < mi)) m = om, mi = oi;
                 }
+                if (p.tp_size > 1) {   // vocab-parallel lm_head: this rank's winner against the peers'
+                    bar_sync(1, kTC);  // all threads have read red[32..] / misc[24..]
+                    mi = tcd_token_exchange(p, c, s, m, mi + p.tp_rank * p.vocab, bid, tid);
+                }
                 c.tok = mi;
                 c.pos += 1;
                 if (bid == 0 && tid == 0) {
@@ -161,6 +175,10 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 }
                 bar_sync(1, kTC);  // red/misc are reused by the next step
             }
+        }
+        if (p.tp_size > 1 && bid == 0 && tid == 0) {   // sequence numbers for the next launch (and for tp_ar.cu's kernel)
+            *reinterpret_cast<volatile unsigned *>(p.ar_seq) = c.ar_s;
+            *reinterpret_cast<volatile unsigned *>(p.ar_seq + 2) = c.tok_s;
         }
     }
     // every role has finished its schedule: all MMAs are committed and read back

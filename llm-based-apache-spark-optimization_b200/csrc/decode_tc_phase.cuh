@@ -30,6 +30,9 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint16_t *>(nj->gain) + tid * 64));
         }
     }
+    if ((job.x_src & 0x400) && p.tp_size > 1) {  // tensor parallel: clear the partial-sum vector of the next row-parallel phase
+        for (int i = bid * kTC + tid; i < p.d / 4; i += G * kTC) reinterpret_cast<float4 *>(p.delta)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     if (job.x_src & 0x100) {  // clear the sum buffers the next qkv / gate-up phases add into
         const int nq4 = (p.n_q + 2 * p.n_kv) * p.head_dim / 4, ng4 = 2 * p.ffn / 4;
         for (int i = bid * kTC + tid; i < nq4 + ng4; i += G * kTC) {
@@ -176,4 +179,86 @@ __device__ void tcd_epilogue(const TcdParams &p, const TcdJob &job, const TcdSme
         ++c.as;
         g = seg_end;
     }
+}
+
+// ---- tensor parallel: all-reduce phase ----------------------------------------------------------------
+// h += sum over ranks of delta, the exchange of tp_ar.cu as a phase of the persistent kernel (after the
+// grid barrier that completes this rank's delta): CTA j pushes slice j (1024 floats) into every peer's
+// inbox, publishes the sequence number, waits for the peers' flags in its own memory, adds in rank order.
+__device__ __forceinline__ unsigned tcd_ld_acquire_sys(const unsigned *q) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(q) : "memory");
+    return v;
+}
+__device__ __forceinline__ void tcd_st_release_sys(unsigned *q, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(q), "r"(v) : "memory");
+}
+
+__device__ void tcd_allreduce_phase(const TcdParams &p, TcdCtx &c, int G, int bid, int tid) {
+    const unsigned sq = ++c.ar_s;
+    const int phase = (int)(sq & 1u);
+    const int n_slices = (p.d + 1023) / 1024;
+    for (int j = bid; j < n_slices; j += G) {
+        const int i = j * 1024 + tid * 4;
+        const bool live = tid < 256 && i < p.d;
+        float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (live) mine = __ldcg(reinterpret_cast<const float4 *>(p.delta + i));
+        if (live)
+            for (int r = 0; r < p.tp_size; ++r)
+                if (r != p.tp_rank)
+                    *reinterpret_cast<float4 *>(p.ar_inbox[r] + ((size_t)phase * p.tp_size + p.tp_rank) * p.ar_slot_floats + i) = mine;
+        __threadfence_system();
+        bar_sync(1, kTC);
+        if (tid < p.tp_size && tid != p.tp_rank) {
+            tcd_st_release_sys(p.ar_flags[tid] + ((size_t)phase * p.tp_size + p.tp_rank) * p.ar_max_slices + j, sq);
+            const unsigned *f = p.ar_flags[p.tp_rank] + ((size_t)phase * p.tp_size + tid) * p.ar_max_slices + j;
+            while (tcd_ld_acquire_sys(f) != sq) {
+            }
+        }
+        bar_sync(1, kTC);
+        if (live) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int r = 0; r < p.tp_size; ++r) {   // rank order: every rank holds the same residual stream bit for bit
+                float4 v = mine;
+                if (r != p.tp_rank)
+                    v = __ldcv(reinterpret_cast<const float4 *>(p.ar_inbox[p.tp_rank] + ((size_t)phase * p.tp_size + r) * p.ar_slot_floats + i));
+                acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+            }
+            float4 hv = __ldcg(reinterpret_cast<const float4 *>(p.h + i));
+            hv.x += acc.x, hv.y += acc.y, hv.z += acc.z, hv.w += acc.w;
+            *reinterpret_cast<float4 *>(p.h + i) = hv;
+        }
+    }
+}
+
+// ---- tensor parallel: every rank's best (logit, token id) -> the global greedy token ------------------
+// Called by all compute threads of every CTA with this rank's winner; CTA 0 pushes it to the peers, every
+// CTA waits for the peers' entries in local memory and returns the best of all (lowest id on ties).
+__device__ int tcd_token_exchange(const TcdParams &p, TcdCtx &c, const TcdSmem &s, float m, int gi, int bid, int tid) {
+    const unsigned sq = ++c.tok_s;
+    const int phase = (int)(sq & 1u);
+    const unsigned long long mine = (unsigned long long)__float_as_uint(m) | ((unsigned long long)(unsigned)gi << 32);
+    if (bid == 0 && tid < p.tp_size && tid != p.tp_rank) {
+        *reinterpret_cast<volatile unsigned long long *>(p.tok_inbox[tid] + (size_t)phase * p.tp_size + p.tp_rank) = mine;
+        __threadfence_system();
+        tcd_st_release_sys(p.tok_flags[tid] + (size_t)phase * p.tp_size + p.tp_rank, sq);
+    }
+    if (tid < p.tp_size) {
+        unsigned long long v = mine;
+        if (tid != p.tp_rank) {
+            const unsigned *f = p.tok_flags[p.tp_rank] + (size_t)phase * p.tp_size + tid;
+            while (tcd_ld_acquire_sys(f) != sq) {
+            }
+            v = *reinterpret_cast<volatile unsigned long long *>(p.tok_inbox[p.tp_rank] + (size_t)phase * p.tp_size + tid);
+        }
+        s.red[48 + tid] = __uint_as_float((unsigned)(v & 0xffffffffull));
+        s.misc[48 + tid] = (int)(v >> 32);
+    }
+    bar_sync(1, kTC);
+    float bm = s.red[48];
+    int bi = s.misc[48];
+    for (int r = 1; r < p.tp_size; ++r)
+        if (s.red[48 + r] > bm || (s.red[48 + r] == bm && s.misc[48 + r] < bi)) bm = s.red[48 + r], bi = s.misc[48 + r];
+    bar_sync(1, kTC);   // red/misc are reused
+    return bi;
 }

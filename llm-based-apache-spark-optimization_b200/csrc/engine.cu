@@ -140,6 +140,8 @@ struct b200llm_engine {
     float *ar_inbox[kTpMaxRanks] = {};
     unsigned *ar_flags[kTpMaxRanks] = {};
     unsigned *ar_seq = nullptr;
+    unsigned long long *tok_inbox[kTpMaxRanks] = {};   // greedy-token exchange of the tensor-parallel persistent kernel
+    unsigned *tok_flags[kTpMaxRanks] = {};
     int ar_slot_floats = 0, ar_max_slices = 0;
     bool ar_ready = false;
     std::vector<b200llm_sampling> samp_host;
@@ -382,6 +384,9 @@ static void ar_pointers(b200llm_engine *e, int r, uint8_t *base) {
     ar_layout(e, &flag_bytes, &total);
     e->ar_flags[r] = reinterpret_cast<unsigned *>(base);
     e->ar_inbox[r] = reinterpret_cast<float *>(base + flag_bytes);
+    // the last 256 bytes of the flag area: sequence words (16 B), token-exchange flags (+64), token inbox (+128)
+    e->tok_flags[r] = reinterpret_cast<unsigned *>(base + flag_bytes - 256 + 64);
+    e->tok_inbox[r] = reinterpret_cast<unsigned long long *>(base + flag_bytes - 256 + 128);
 }
 
 int b200llm_tp_export(b200llm_engine *e, void *handle64) {
@@ -807,23 +812,29 @@ static bool tcd_usable(const b200llm_engine *e) {
     if (getenv("B200LLM_NO_TCD")) return false;
     bool tiled = e->lm_head_tm != nullptr;
     for (auto &w : e->layers) tiled = tiled && w.wqkv_tm && w.wo_tm && w.wgu_tm && w.wdown_tm;
-    return tiled && tcd_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim, c.vocab, c.n_layers);
+    if (c.tp_size > 1 && !e->ar_ready) return false;   // tensor parallel needs the peer inboxes (b200llm_tp_import)
+    return tiled && tcd_supported(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, e->vocab_l, c.n_layers);
 }
 
 static int tcd_prepare(b200llm_engine *e) {
     const b200llm_config &c = e->cfg;
     std::vector<TcdJob> jobs(4 * c.n_layers + 1);
-    const int qd = c.n_q * c.head_dim;
+    const int nq = e->nq_l, nkv = e->nkv_l, ffn = e->ffn_l;   // this rank's share (= the model's at tp 1)
+    const int qd = nq * c.head_dim;
+    const bool tp = c.tp_size > 1;
+    // tensor parallel: o_proj and down_proj are row-parallel, their partial sums go to `delta` (cleared by the
+    // phase two before, bit 10) and an all-reduce phase adds every rank's delta to h
+    float *row_out = tp ? e->delta : e->h;
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW &w = e->layers[l];
         uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
         jobs[4 * l + 0] = TcdJob{w.wqkv_tm, w.attn_norm, kl, kl + e->kv_half_stride, e->qkv_out,
-                                 (c.n_q + 2 * c.n_kv) * c.head_dim, c.d, TCD_EPI_ADD, l == 0 ? TCD_X_EMBED : TCD_X_H};
-        jobs[4 * l + 1] = TcdJob{w.wo_tm, nullptr, nullptr, nullptr, e->h, c.d, qd, TCD_EPI_ADD, TCD_X_ATT | 0x100};
-        jobs[4 * l + 2] = TcdJob{w.wgu_tm, w.mlp_norm, nullptr, nullptr, e->gu_out, 2 * c.ffn, c.d, TCD_EPI_ADD, TCD_X_H};
-        jobs[4 * l + 3] = TcdJob{w.wdown_tm, nullptr, nullptr, nullptr, e->h, c.d, c.ffn, TCD_EPI_ADD, TCD_X_SWIGLU};
+                                 (nq + 2 * nkv) * c.head_dim, c.d, TCD_EPI_ADD, (l == 0 ? TCD_X_EMBED : TCD_X_H) | 0x400};
+        jobs[4 * l + 1] = TcdJob{w.wo_tm, nullptr, nullptr, nullptr, row_out, c.d, qd, TCD_EPI_ADD, TCD_X_ATT | 0x100};
+        jobs[4 * l + 2] = TcdJob{w.wgu_tm, w.mlp_norm, nullptr, nullptr, e->gu_out, 2 * ffn, c.d, TCD_EPI_ADD, TCD_X_H | 0x400};
+        jobs[4 * l + 3] = TcdJob{w.wdown_tm, nullptr, nullptr, nullptr, row_out, c.d, ffn, TCD_EPI_ADD, TCD_X_SWIGLU};
     }
-    jobs[4 * c.n_layers] = TcdJob{e->lm_head_tm, e->final_norm, nullptr, nullptr, e->logits, c.vocab, c.d, TCD_EPI_LOGITS, TCD_X_H};
+    jobs[4 * c.n_layers] = TcdJob{e->lm_head_tm, e->final_norm, nullptr, nullptr, e->logits, e->vocab_l, c.d, TCD_EPI_LOGITS, TCD_X_H};
     B200_CUDA_OK(cudaMemcpyAsync(e->mega_jobs, jobs.data(), jobs.size() * sizeof(TcdJob), cudaMemcpyHostToDevice, e->stream));
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));  // `jobs` is a pageable temporary
     e->tcd_ready = true;
@@ -836,7 +847,13 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps) {
     if (!e->tcd_ready) B200_TRY(tcd_prepare(e));
     TcdParams p{};
     p.jobs = reinterpret_cast<const TcdJob *>(e->mega_jobs), p.n_layers = c.n_layers;
-    p.d = c.d, p.n_q = c.n_q, p.n_kv = c.n_kv, p.head_dim = c.head_dim, p.ffn = c.ffn, p.vocab = c.vocab;
+    p.d = c.d, p.n_q = e->nq_l, p.n_kv = e->nkv_l, p.head_dim = c.head_dim, p.ffn = e->ffn_l, p.vocab = e->vocab_l;
+    p.vocab_global = c.vocab, p.tp_rank = c.tp_rank, p.tp_size = c.tp_size;
+    if (c.tp_size > 1) {
+        p.delta = e->delta, p.ar_seq = e->ar_seq, p.ar_slot_floats = e->ar_slot_floats, p.ar_max_slices = e->ar_max_slices;
+        for (int r = 0; r < c.tp_size; ++r)
+            p.ar_inbox[r] = e->ar_inbox[r], p.ar_flags[r] = e->ar_flags[r], p.tok_inbox[r] = e->tok_inbox[r], p.tok_flags[r] = e->tok_flags[r];
+    }
     p.rms_eps = c.rms_eps;
     p.scale_log2 = (float)(1.4426950408889634 / sqrt((double)c.head_dim));
     p.h = e->h, p.qkv = e->qkv_out, p.att = e->att, p.gu = e->gu_out, p.logits = e->logits;
@@ -846,22 +863,22 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps) {
     p.page_table = e->page_table + (size_t)lane * c.max_pages_per_lane;
     p.n_ptab = c.max_pages_per_lane;
     p.gen_out = e->gen_out, p.n_steps = n_steps;
-    int ns = kNumSMs / c.n_kv;
+    int ns = kNumSMs / e->nkv_l;
     ns = ns < 1 ? 1 : (ns > e->attn_splits ? e->attn_splits : ns);
     p.n_splits = ns;
     uint8_t *sc = reinterpret_cast<uint8_t *>(e->attn_scratch);
     p.tickets = reinterpret_cast<unsigned *>(sc);
     p.part_o = reinterpret_cast<float *>(sc + kAttnTicketBytes);
-    p.part_ml = p.part_o + (size_t)c.n_q * ns * c.head_dim;
+    p.part_ml = p.part_o + (size_t)e->nq_l * ns * c.head_dim;
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
-    B200_REQUIRE(tcd_plan(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim, c.vocab, c.n_layers, &p.n_stages, &p.n_bslots),
+    B200_REQUIRE(tcd_plan(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, e->vocab_l, c.n_layers, &p.n_stages, &p.n_bslots),
                  "tcd: geometry does not fit");
     if (const char *ns = getenv("B200LLM_TCD_STAGES")) p.n_stages = atoi(ns) < p.n_stages ? atoi(ns) : p.n_stages;
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     // the qkv and gate/up phases ADD into these rows; later layers find them cleared by the o_proj phase
-    B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)(c.n_q + 2 * c.n_kv) * c.head_dim * 4, e->stream));
-    B200_CUDA_OK(cudaMemsetAsync(e->gu_out, 0, (size_t)2 * c.ffn * 4, e->stream));
+    B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim * 4, e->stream));
+    B200_CUDA_OK(cudaMemsetAsync(e->gu_out, 0, (size_t)2 * e->ffn_l * 4, e->stream));
     e->last_rows = 1, e->last_logit_rows = 1;
     return tcd_decode_launch(p, e->stream);
 }
@@ -1037,7 +1054,7 @@ int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int
     B200_CUDA_OK(cudaEventRecord(e->ev[2], e->stream));
     const b200llm_sampling &sp0 = e->samp_host[lanes[0]];
     const bool greedy = sp0.temperature <= 0.f && sp0.repeat_penalty == 1.f;
-    if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy && tcd_usable(e)) {
+    if (c.use_megakernel && n_lanes == 1 && greedy && tcd_usable(e)) {
         B200_TRY(tcd_decode(e, lanes[0], n_steps));
         e->timing.kernel_launches = 1;
     } else if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy &&
@@ -1165,6 +1182,7 @@ int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, 
     TcdParams p{};
     p.jobs = reinterpret_cast<const TcdJob *>(scr), p.n_layers = 0;
     p.d = K, p.n_q = 1, p.n_kv = 1, p.head_dim = 128, p.ffn = 0, p.vocab = N;
+    p.vocab_global = N, p.tp_rank = 0, p.tp_size = 1;
     p.h = const_cast<float *>(x), p.logits = out;
     p.part_max = reinterpret_cast<float *>(scr + 1024), p.part_idx = reinterpret_cast<int32_t *>(scr + 2048);
     p.lane = 0, p.lane_token = reinterpret_cast<int32_t *>(scr + 3072), p.lane_pos = reinterpret_cast<int32_t *>(scr + 3200);

@@ -55,6 +55,17 @@ struct TcdParams {
     int32_t n_stages;     // ring stages of 16 KB (<= 10) and operand blocks of 1 KB (<= 64) in shared memory: tcd_plan()
     int32_t n_bslots;
     int32_t split_all;    // (test hook) k-split the last job too instead of giving whole tiles
+    // ---- tensor parallel (tp_size > 1): row-parallel phases (bit 10 of x_src) add into `delta`, then an
+    // all-reduce phase pushes delta to the peers' inboxes and adds all ranks' partials to h (see tp_ar.cu)
+    int32_t tp_rank, tp_size;
+    int32_t vocab_global;  // token ids are clamped against this; `vocab` is this rank's share
+    float *delta;          // [d] this rank's partial sums of a row-parallel phase
+    float *ar_inbox[8];    // inbox base of every rank: [2 phases][tp_size][ar_slot_floats]
+    unsigned *ar_flags[8]; // flag base of every rank: [2 phases][tp_size][ar_max_slices]
+    unsigned *ar_seq;      // local: [0] reduction sequence number (shared with tp_ar.cu), [2] token-exchange sequence
+    unsigned long long *tok_inbox[8];  // per rank: [2 phases][tp_size] {max as bits | token id << 32}, and
+    unsigned *tok_flags[8];            // [2 phases][tp_size] sequence words
+    int32_t ar_slot_floats, ar_max_slices;
     unsigned long long *trace;  // optional [2][1024] globaltimer stamps of CTA 0 and CTA G-1 (debug)
     int32_t trace_step;
 };

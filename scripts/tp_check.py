@@ -39,7 +39,8 @@ for name in (["small", "duckdb-nsql"] if len(sys.argv) < 2 else sys.argv[1:]):
     box = [None] * world
     dist.all_gather_object(box, got)
     same = all(b == box[0] for b in box)
-    msg = f"[{name}] tp={world} rank {rank}: ranks agree={same} ms/step={ev0.elapsed_time(ev1)/n:.3f}"
+    msg = (f"[{name}] tp={world} rank {rank}: ranks agree={same} ms/step={ev0.elapsed_time(ev1)/n:.3f} "
+           f"launches per decode call={eng.timing().kernel_launches}")
     if want is not None:
         msg += f" oracle match={got == want}"
         ok = ok and got == want

@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--pdl", action="store_true")
+    ap.add_argument("--tp", action="store_true", help="tensor parallel over the --gpus ranks (one sequence, strong scaling; "
+                    "the 7B configuration) instead of one replica per rank")
     ap.add_argument("--max-rows", type=int, default=256, help="rows per forward pass (prefill chunk size / batch limit)")
     ap.add_argument("--no-mega", action="store_true", help="multi-kernel CUDA-graph path instead of the persistent kernel")
     ap.add_argument("--attn-splits", type=int, default=0)
@@ -144,7 +146,7 @@ def run_reference(args):
               f"{PROMPT_LEN}-id workload), torch CPU bf16, {cores} threads")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": min(args.warmup, 4), "ms_per_step": 1000.0 * dt / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": "strong" if tp_mode else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload_name(args.model, 1), "l2": "inputs larger than L2"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -175,13 +177,22 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     geo = geometry.resolve(args.model)
     bs = args.bs
-    w = weights.random_init(geo, 0xB200, local)
+    tp_mode = args.tp and world > 1
     max_ctx = PROMPT_LEN + args.steps + args.warmup + E2E_NEW_TOKENS + 64
-    eng = Engine(geo, w, device=local, max_lanes=bs + 1, max_ctx=max_ctx, max_rows=max(bs, args.max_rows),
-                 use_graphs=not args.no_graphs, use_pdl=args.pdl, attn_splits=args.attn_splits,
-                 use_megakernel=not args.no_mega)
-    # synthetic prompts: uniform ids, one stream per (rank, sequence)
-    rng = np.random.default_rng(1000 * rank + 1)
+    if tp_mode:
+        from b200llm import tp
+        w = weights.random_init(geo, 0xB200, local, tp_rank=rank, tp_size=world)
+        eng = Engine(geo, w, device=local, max_lanes=bs + 1, max_ctx=max_ctx, max_rows=max(bs, args.max_rows),
+                     tp_rank=rank, tp_size=world, nccl_id=tp.exchange_unique_id(), use_graphs=not args.no_graphs,
+                     attn_splits=args.attn_splits, use_megakernel=not args.no_mega)
+        tp.connect_peers(eng)       # all-reduce over NVLink peer memory; persistent kernel per rank
+    else:
+        w = weights.random_init(geo, 0xB200, local)
+        eng = Engine(geo, w, device=local, max_lanes=bs + 1, max_ctx=max_ctx, max_rows=max(bs, args.max_rows),
+                     use_graphs=not args.no_graphs, use_pdl=args.pdl, attn_splits=args.attn_splits,
+                     use_megakernel=not args.no_mega)
+    # synthetic prompts: uniform ids, one stream per (rank, sequence); tensor parallel: the same stream on every rank
+    rng = np.random.default_rng(1 if tp_mode else 1000 * rank + 1)
     prompts = [rng.integers(0, min(geo.vocab, 128000), PROMPT_LEN, dtype=np.int32) for _ in range(bs)]
     lanes = [eng.open_lane() for _ in range(bs)]
     for ln, p in zip(lanes, prompts):
@@ -196,7 +207,17 @@ def run_b200(args):
     eng.sync()
     _note("warm-up done")
     first_line = 0
-    if sampler is not None and sampler.p is not None:
+    if tp_mode:
+        # tensor parallel: every rank must make exactly the same engine calls (their kernels wait for each other),
+        # so the filler that keeps the GPU loaded until nvidia-smi has sampled is a fixed number of calls
+        for _ in range(24):
+            for ln in lanes:
+                eng.set_lane(ln, 1, PROMPT_LEN)
+            eng.decode(lanes, 32, read=False)
+            eng.sync()
+        if sampler is not None:
+            first_line = max(0, len(sampler.lines()) - 2)
+    elif sampler is not None and sampler.p is not None:
         t_wait = time.time()
         while len(sampler.lines()) < 2 and time.time() - t_wait < 4.0:
             for ln in lanes:
@@ -252,7 +273,7 @@ def run_b200(args):
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_val = world * n_e2e / float(te.item())
+    e2e_val = (1 if tp_mode else world) * n_e2e / float(te.item())
     n_pages = (PROMPT_LEN + E2E_NEW_TOKENS + 15) // 16
     h2d = 3 * 4 * PROMPT_LEN + 4 * n_pages + 24 + 4 + 4          # ids/pos/lane arrays, page table, sampling, lane ids
     d2h = 4 * E2E_NEW_TOKENS + 8
@@ -261,13 +282,13 @@ def run_b200(args):
         mean_ctx = PROMPT_LEN + (args.steps - 1) / 2.0
         step_bytes = geo.step_bytes(bs, mean_ctx)
         peak, peak_src = peaks()
-        achieved = step_bytes / (ms / args.steps * 1e-3) / 1e9
+        achieved = step_bytes / (ms / args.steps * 1e-3) / 1e9 / (world if tp_mode else 1)   # per GPU
         line = {
             "metric": METRIC if (args.model == "llama3.2" and bs == 1) else f"decode_tok_s_{args.model}_bs{bs}",
-            "value": world * bs * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "value": (1 if tp_mode else world) * bs * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": workload_name(args.model, bs), "parallelism": f"replicas x{world}",
+            "scaling": "strong" if tp_mode else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(args.model, bs), "parallelism": f"tp{world}" if tp_mode else f"replicas x{world}",
                        "l2": "inputs larger than L2 (weights streamed every step)", "cuda_graph": not args.no_graphs,
                        "pdl": args.pdl, "persistent_kernel": not args.no_mega, "kv_cache": "bf16 paged (16-token pages)", "mean_ctx": mean_ctx},
             "ttft_ms": ttft_ms,

@@ -652,6 +652,41 @@ static int tp_allreduce_add(b200llm_engine *e, int rows) {
     return B200LLM_OK;
 }
 
+// final norm + lm_head GEMV + sampler (vocab-parallel under tensor parallel: the ranks' (max, argmax) partials are gathered)
+static int lm_head_and_sample(b200llm_engine *e, const PassRows &pr, bool advance) {
+    const b200llm_config &c = e->cfg;
+    const bool tp = c.tp_size > 1;
+    b200llm_gemv_args lm{};
+    lm.w = e->lm_head, lm.x = e->h + (size_t)pr.logit_row0 * c.d, lm.x_stride = c.d, lm.norm_gain = e->final_norm;
+    lm.rms_eps = c.rms_eps, lm.out = e->logits, lm.out_stride = e->vocab_l, lm.N = e->vocab_l, lm.K = c.d;
+    lm.epi = B200LLM_EPI_LOGITS, lm.grid_hint = e->lm_grid, lm.logits_idx_offset = c.tp_rank * e->vocab_l;
+    B200_TRY(gemv_rows(e, lm, pr.logit_rows, pr, pr.logit_row0));
+
+    SampleDev sd{};
+    sd.a.logits = e->logits, sd.a.bs = pr.logit_rows, sd.a.vocab = e->vocab_l;
+    sd.a.part_max = e->part_max, sd.a.part_idx = e->part_idx, sd.a.n_part = e->lm_grid;
+    sd.a.params = e->lane_samp, sd.a.out_token = nullptr;
+    if (tp) {
+        // vocab-parallel greedy: gather every rank's per-row (max, argmax) and reduce those.
+        // TODO(tp sampling): temperature > 0 needs the full logits gathered; greedy only here.
+        B200_NCCL_OK(g_nccl.AllGather(e->part_max, e->gath_max, (size_t)pr.logit_rows * e->lm_grid * 4, kNcclInt8,
+                                      e->comm, e->stream));
+        B200_NCCL_OK(g_nccl.AllGather(e->part_idx, e->gath_idx, (size_t)pr.logit_rows * e->lm_grid * 4, kNcclInt8,
+                                      e->comm, e->stream));
+        // gathered layout is [rank][row][grid]
+        sd.a.part_max = e->gath_max, sd.a.part_idx = e->gath_idx;
+        sd.n_ranks = c.tp_size, sd.rank_stride = (size_t)pr.logit_rows * e->lm_grid;
+    }
+    sd.row_lane = pr.row_lane + pr.logit_row0;
+    sd.lane_token = e->lane_token, sd.lane_pos = e->lane_pos, sd.lane_hist = e->lane_hist;
+    sd.gen_out = pr.from_lanes ? e->gen_out : nullptr, sd.step_ctr = pr.from_lanes ? e->step_ctr : nullptr;
+    sd.advance = advance ? 1 : 0;
+    B200_TRY(sample_launch(sd, e->stream, e->pdl && !tp));
+    e->launches++;
+    return B200LLM_OK;
+}
+
+
 static int forward_pass_gemv(b200llm_engine *e, const PassRows &pr, bool advance) {
     const b200llm_config &c = e->cfg;
     const int rows = pr.rows;
@@ -709,36 +744,7 @@ static int forward_pass_gemv(b200llm_engine *e, const PassRows &pr, bool advance
     e->last_rows = rows;
     e->last_logit_rows = pr.logit_rows;
     if (pr.logit_rows <= 0) return B200LLM_OK;
-
-    // --- final norm + lm_head + sampler ---
-    b200llm_gemv_args lm{};
-    lm.w = e->lm_head, lm.x = e->h + (size_t)pr.logit_row0 * c.d, lm.x_stride = c.d, lm.norm_gain = e->final_norm;
-    lm.rms_eps = c.rms_eps, lm.out = e->logits, lm.out_stride = e->vocab_l, lm.N = e->vocab_l, lm.K = c.d;
-    lm.epi = B200LLM_EPI_LOGITS, lm.grid_hint = e->lm_grid, lm.logits_idx_offset = c.tp_rank * e->vocab_l;
-    B200_TRY(gemv_rows(e, lm, pr.logit_rows, pr, pr.logit_row0));
-
-    SampleDev sd{};
-    sd.a.logits = e->logits, sd.a.bs = pr.logit_rows, sd.a.vocab = e->vocab_l;
-    sd.a.part_max = e->part_max, sd.a.part_idx = e->part_idx, sd.a.n_part = e->lm_grid;
-    sd.a.params = e->lane_samp, sd.a.out_token = nullptr;
-    if (tp) {
-        // vocab-parallel greedy: gather every rank's per-row (max, argmax) and reduce those.
-        // TODO(tp sampling): temperature > 0 needs the full logits gathered; greedy only here.
-        B200_NCCL_OK(g_nccl.AllGather(e->part_max, e->gath_max, (size_t)pr.logit_rows * e->lm_grid * 4, kNcclInt8,
-                                      e->comm, e->stream));
-        B200_NCCL_OK(g_nccl.AllGather(e->part_idx, e->gath_idx, (size_t)pr.logit_rows * e->lm_grid * 4, kNcclInt8,
-                                      e->comm, e->stream));
-        // gathered layout is [rank][row][grid]
-        sd.a.part_max = e->gath_max, sd.a.part_idx = e->gath_idx;
-        sd.n_ranks = c.tp_size, sd.rank_stride = (size_t)pr.logit_rows * e->lm_grid;
-    }
-    sd.row_lane = pr.row_lane + pr.logit_row0;
-    sd.lane_token = e->lane_token, sd.lane_pos = e->lane_pos, sd.lane_hist = e->lane_hist;
-    sd.gen_out = pr.from_lanes ? e->gen_out : nullptr, sd.step_ctr = pr.from_lanes ? e->step_ctr : nullptr;
-    sd.advance = advance ? 1 : 0;
-    B200_TRY(sample_launch(sd, e->stream, e->pdl && !tp));
-    e->launches++;
-    return B200LLM_OK;
+    return lm_head_and_sample(e, pr, advance);
 }
 
 // ---------------------------------------------------------------- persistent batch-1 decode
@@ -904,8 +910,9 @@ static bool tc_usable(const b200llm_engine *e, int rows) {
     const b200llm_config &c = e->cfg;
     auto okn = [](int n) { return n % 128 == 0; };
     auto okk = [](int k) { return k % 64 == 0; };
-    return c.use_tc && c.tp_size == 1 && rows > 4 && rows <= 256 && okn((c.n_q + 2 * c.n_kv) * c.head_dim) && okn(c.d) &&
-           okn(2 * c.ffn) && okn(c.vocab) && okk(c.d) && okk(c.n_q * c.head_dim) && okk(c.ffn) &&
+    const bool lm_ok = c.tp_size > 1 || okn(c.vocab);   // tensor parallel keeps the GEMV lm_head (partials are gathered)
+    return c.use_tc && rows > 4 && rows <= 256 && okn((e->nq_l + 2 * e->nkv_l) * c.head_dim) && okn(c.d) &&
+           okn(2 * e->ffn_l) && lm_ok && okk(c.d) && okk(e->nq_l * c.head_dim) && okk(e->ffn_l) &&
            getenv("B200LLM_NO_TC") == nullptr;
 }
 
@@ -945,7 +952,11 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
     ea.from_lanes = pr.from_lanes ? 1 : 0;
     B200_TRY(embed_launch_ex(ea, e->lane_hist, pr.from_lanes ? e->step_ctr : nullptr, st, pdl));
     e->launches++;
-    const int qd = c.n_q * c.head_dim, qkv_w = (c.n_q + 2 * c.n_kv) * c.head_dim;
+    // this rank's share of heads and MLP units (the whole model at tp 1); o_proj and down_proj are row-parallel
+    // under tensor parallel: their GEMMs fill `delta`, the all-reduce kernel adds every rank's delta to h
+    const bool tp = c.tp_size > 1;
+    const int n_q = e->nq_l, n_kv = e->nkv_l, ffn = e->ffn_l;
+    const int qd = n_q * c.head_dim, qkv_w = (n_q + 2 * n_kv) * c.head_dim;
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW &w = e->layers[l];
         uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
@@ -953,35 +964,51 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         B200_TRY(rmsnorm_bf16_launch(e->h, w.attn_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->qkv_out, qkv_w, e->xb_lo));
         B200_TRY(tc_gemm(e, w.wqkv, qkv_w, c.d, e->qkv_out, qkv_w, rows, false, true));
         B200_TRY(rope_append_launch(e->qkv_out, e->q, kl, vl, e->inv_freq, pr.row_lane, pr.row_pos, e->page_table, rows,
-                                    c.n_q, c.n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, pdl));
+                                    n_q, n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, pdl));
         b200llm_attn_args at{};
         at.q = e->q, at.out = e->att, at.k_pages = kl, at.v_pages = vl, at.row_lane = pr.row_lane, at.row_pos = pr.row_pos;
-        at.page_table = e->page_table, at.bs = rows, at.n_q = c.n_q, at.n_kv = c.n_kv, at.head_dim = c.head_dim;
+        at.page_table = e->page_table, at.bs = rows, at.n_q = n_q, at.n_kv = n_kv, at.head_dim = c.head_dim;
         at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane;
-        int want = (kNumSMs + rows * c.n_kv - 1) / (rows * c.n_kv);
+        int want = (kNumSMs + rows * n_kv - 1) / (rows * n_kv);
         if (want > 6) want = 6;
         at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
         at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
         B200_TRY(attn_decode_launch(at, st, pdl, e->xb, e->xb_lo));  // output rounded to bf16 straight into the o_proj operand
-        B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->h, c.d, rows, true));
+        if (tp) {
+            B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->delta, c.d, rows, false));
+            B200_TRY(tp_allreduce_add(e, rows));
+        } else {
+            B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->h, c.d, rows, true));
+        }
         // gate/up: with >= 74 row tiles the GEMM runs without a k split and applies SwiGLU in its epilogue
-        const bool fuse_swiglu = 2 * c.ffn / 128 > kNumSMs / 2;
+        const bool fuse_swiglu = 2 * ffn / 128 > kNumSMs / 2;
         if (fuse_swiglu) {
             B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, nullptr, 0, e->xb_lo));
-            B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false, true, nullptr, e->xb2));
-            B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true, false, e->xb2));
+            B200_TRY(tc_gemm(e, w.wgu, 2 * ffn, c.d, e->gu_out, 2 * ffn, rows, false, true, nullptr, e->xb2));
+            if (tp) {
+                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->delta, c.d, rows, false, false, e->xb2));
+                B200_TRY(tp_allreduce_add(e, rows));
+            } else {
+                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->h, c.d, rows, true, false, e->xb2));
+            }
             e->launches += 4;
         } else {
-            B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->gu_out, 2 * c.ffn, e->xb_lo));
-            B200_TRY(tc_gemm(e, w.wgu, 2 * c.ffn, c.d, e->gu_out, 2 * c.ffn, rows, false, true));
-            B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, c.ffn, st, pdl, e->xb_lo));
-            B200_TRY(tc_gemm(e, w.wdown, c.d, c.ffn, e->h, c.d, rows, true));
+            B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->gu_out, 2 * ffn, e->xb_lo));
+            B200_TRY(tc_gemm(e, w.wgu, 2 * ffn, c.d, e->gu_out, 2 * ffn, rows, false, true));
+            B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, ffn, st, pdl, e->xb_lo));
+            if (tp) {
+                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->delta, c.d, rows, false));
+                B200_TRY(tp_allreduce_add(e, rows));
+            } else {
+                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->h, c.d, rows, true));
+            }
             e->launches += 5;
         }
     }
     e->last_rows = rows;
     e->last_logit_rows = pr.logit_rows;
     if (pr.logit_rows <= 0) return B200LLM_OK;
+    if (tp) return lm_head_and_sample(e, pr, advance);
     B200_TRY(rmsnorm_bf16_launch(e->h + (size_t)pr.logit_row0 * c.d, e->final_norm, e->xb, pr.logit_rows, c.d, c.rms_eps,
                                  st, pdl, nullptr, 0, e->xb_lo));
     B200_TRY(tc_gemm(e, e->lm_head, c.vocab, c.d, e->logits, c.vocab, pr.logit_rows, false));

@@ -17,7 +17,7 @@ for name in (["small", "duckdb-nsql"] if len(sys.argv) < 2 else sys.argv[1:]):
         ogeo = lo.GEOMETRIES[name]
         sd = lo.make_weights(ogeo, 0xB200, sigma=0.06)
         prompt = wg.gen_tokens(45, 9, geo.vocab)
-        want, lg, _ = lo.LlamaOracle(ogeo, sd, kv_dtype=torch.bfloat16).greedy(prompt, 16)
+        want, lg, margins = lo.LlamaOracle(ogeo, sd, kv_dtype=torch.bfloat16).greedy(prompt, 16)
         w = weights.pack(geo, {k: v.cuda() for k, v in sd.items()}, rank, world)
     else:
         prompt = wg.gen_tokens(64, 9, geo.vocab)
@@ -42,8 +42,14 @@ for name in (["small", "duckdb-nsql"] if len(sys.argv) < 2 else sys.argv[1:]):
     msg = (f"[{name}] tp={world} rank {rank}: ranks agree={same} ms/step={ev0.elapsed_time(ev1)/n:.3f} "
            f"launches per decode call={eng.timing().kernel_launches}")
     if want is not None:
-        msg += f" oracle match={got == want}"
-        ok = ok and got == want
+        bad = [i for i in range(len(want)) if got[i] != want[i]]
+        # a first mismatch is tolerated only where the oracle itself is at a near-tie (top-1 minus top-2 logit below
+        # 5e-3: inside the engine's 3e-3 relative logit tolerance), as in tests/test_gpu_engine.py
+        near_tie = bool(bad) and margins[bad[0]] < 5e-3
+        msg += f" oracle match={got == want or near_tie}"
+        if bad:
+            msg += f" (first difference at step {bad[0]}: got {got[bad[0]]} want {want[bad[0]]}, oracle margin {margins[bad[0]]:.3e})"
+        ok = ok and (got == want or near_tie)
     ok = ok and same
     if rank == 0:
         print(msg, got[:8], flush=True)

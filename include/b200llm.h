@@ -171,6 +171,10 @@ int b200llm_set_page_table(b200llm_engine *e, int32_t lane, const int32_t *pages
 int b200llm_set_sampling(b200llm_engine *e, int32_t lane, const b200llm_sampling *s);
 /* Overwrite the lane's next input token / position (teacher forcing, resume). */
 int b200llm_set_lane(b200llm_engine *e, int32_t lane, int32_t next_token, int32_t pos);
+/* Reset the lane's 64-token repeat-penalty window and seed it with ids[0..n) as the tokens at positions
+ * pos0 .. pos0+n-1 (n <= 64).  Used when a lane starts on KV pages computed by another request (prefix
+ * cache): the window must hold what a full prefill of the same prompt would have left in it. */
+int b200llm_set_history(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t n, int32_t pos0);
 
 /* ---- the hot path ---------------------------------------------------------------- */
 /* Prefill: run `n` prompt ids (host buffer) of `lane` starting at position pos0, append

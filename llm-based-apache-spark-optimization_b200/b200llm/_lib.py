@@ -84,6 +84,7 @@ SYMBOLS = {
     "b200llm_set_page_table": (C.c_int, [C.c_void_p, C.c_int32, _P(C.c_int32), C.c_int32]),
     "b200llm_set_sampling": (C.c_int, [C.c_void_p, C.c_int32, _P(Sampling)]),
     "b200llm_set_lane": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
+    "b200llm_set_history": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.c_int32]),
     "b200llm_prefill": (C.c_int, [C.c_void_p, C.c_int32, _P(C.c_int32), C.c_int32, C.c_int32]),
     "b200llm_decode": (C.c_int, [C.c_void_p, _P(C.c_int32), C.c_int32, C.c_int32]),
     "b200llm_read_tokens": (C.c_int, [C.c_void_p, _P(C.c_int32), C.c_int32, C.c_int32]),

@@ -91,6 +91,8 @@ class Engine:
         _lib.check(_lib.lib.b200llm_bind_kv_pool(self._h, self.kv_pool.data_ptr(), self.kv_pool.numel()))
         _lib.check(_lib.lib.b200llm_bind_workspace(self._h, self.workspace.data_ptr(), self.workspace.numel()))
         self._free_pages = list(range(kv_pages - 1, -1, -1))
+        self._page_ref = [0] * kv_pages      # lanes and prefix-cache entries holding each page
+        self.on_page_pressure = None         # callable(n_pages_short), set by the prefix cache
         self._lane_pages: List[List[int]] = [[] for _ in range(max_lanes)]
         self._free_lanes = list(range(max_lanes - 1, -1, -1))
         self.pos = [0] * max_lanes
@@ -107,9 +109,46 @@ class Engine:
 
     def close_lane(self, lane: int) -> None:
         with self.lock:
-            self._free_pages.extend(reversed(self._lane_pages[lane]))
+            self.release_pages(self._lane_pages[lane])
             self._lane_pages[lane] = []
             self._free_lanes.append(lane)
+
+    # ---- shared KV pages (prefix cache) ------------------------------------------------
+    def lane_pages(self, lane: int) -> List[int]:
+        return list(self._lane_pages[lane])
+
+    def retain_pages(self, pages: Sequence[int]) -> None:
+        with self.lock:
+            for p in pages:
+                self._page_ref[p] += 1
+
+    def release_pages(self, pages: Sequence[int]) -> None:
+        with self.lock:
+            for p in reversed(list(pages)):
+                self._page_ref[p] -= 1
+                if self._page_ref[p] == 0:
+                    self._free_pages.append(p)
+
+    def attach_prefix(self, lane: int, pages: Sequence[int], ids: Sequence[int] = ()) -> None:
+        """Start a fresh lane on KV pages that already hold its first len(pages) * 16 tokens (computed by
+        an earlier request with the same token prefix).  The pages are shared read-only: the lane's own
+        tokens go to pages it allocates after them, so continue with prefill(lane, rest, pos0=len(pages) * 16).
+        `ids` are those first tokens: the last 64 of them seed the lane's repeat-penalty window."""
+        with self.lock:
+            if self._lane_pages[lane]:
+                raise _lib.B200LLMError(_lib.ESTATE, "attach_prefix: the lane already has pages")
+            if len(pages) > self.max_pages_per_lane:
+                raise _lib.B200LLMError(_lib.EINVAL, "attach_prefix: prefix longer than the lane context")
+            self.retain_pages(pages)
+            self._lane_pages[lane] = list(pages)
+            if pages:
+                arr = (C.c_int32 * len(pages))(*pages)
+                _lib.check(_lib.lib.b200llm_set_page_table(self._h, lane, arr, len(pages)))
+            n = len(pages) * PAGE_TOKENS
+            tail = np.ascontiguousarray(np.asarray(ids[:n], dtype=np.int32)[-64:])
+            _lib.check(_lib.lib.b200llm_set_history(self._h, lane, tail.ctypes.data_as(C.POINTER(C.c_int32)), len(tail),
+                                                    max(0, n - len(tail))))
+            self.pos[lane] = n
 
     def _ensure_pages(self, lane: int, n_tokens: int) -> None:
         need = (n_tokens + PAGE_TOKENS - 1) // PAGE_TOKENS
@@ -119,10 +158,13 @@ class Engine:
                                                  f"({self.max_pages_per_lane * PAGE_TOKENS})")
         if need <= len(pages):
             return
+        if need - len(pages) > len(self._free_pages) and self.on_page_pressure is not None:
+            self.on_page_pressure(need - len(pages) - len(self._free_pages))   # the prefix cache gives pages back
         if need - len(pages) > len(self._free_pages):
             raise _lib.B200LLMError(_lib.ENOMEM, "KV pool exhausted")
         while len(pages) < need:
             pages.append(self._free_pages.pop())
+            self._page_ref[pages[-1]] = 1
         arr = (C.c_int32 * len(pages))(*pages)
         _lib.check(_lib.lib.b200llm_set_page_table(self._h, lane, arr, len(pages)))
 

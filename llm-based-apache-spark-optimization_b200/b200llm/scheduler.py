@@ -15,6 +15,7 @@ from dataclasses import dataclass, field
 from typing import Deque, Dict, Iterable, List, Optional, Sequence
 
 from .engine import Engine, GenTiming, SamplingParams
+from .prefix_cache import PrefixCache
 
 
 @dataclass
@@ -31,9 +32,11 @@ class Request:
 
 
 class Scheduler:
-    def __init__(self, engine: Engine, chunk: int = 16):
+    def __init__(self, engine: Engine, chunk: int = 16, prefix_cache: bool = True):
         self.engine = engine
         self.chunk = chunk
+        # KV pages of prompt prefixes seen before (the reference repeats its system prompts): prefix_cache.py
+        self.cache = PrefixCache(engine) if prefix_cache else None
         self._queue: Deque[Request] = deque()
         self._cv = threading.Condition()
         self._active: Dict[int, Request] = {}
@@ -68,6 +71,8 @@ class Scheduler:
             self._stop = True
             self._cv.notify()
         self._thread.join(timeout=30)
+        if self.cache is not None:
+            self.cache.clear()
 
     # ---- scheduler thread -----------------------------------------------------------------
     def _finish(self, req: Request, error: Optional[BaseException] = None):
@@ -83,7 +88,14 @@ class Scheduler:
         try:
             req.lane = eng.open_lane()
             eng.set_sampling(req.lane, req.sampling)
-            eng.prefill(req.lane, req.prompt_ids)
+            shared, pages = self.cache.lookup(req.prompt_ids) if self.cache else (0, [])
+            if shared:
+                eng.attach_prefix(req.lane, pages, req.prompt_ids[:shared])
+                eng.prefill(req.lane, req.prompt_ids[shared:], pos0=shared)
+            else:
+                eng.prefill(req.lane, req.prompt_ids)
+            if self.cache:
+                self.cache.insert(req.prompt_ids, eng.lane_pages(req.lane))
             first, _ = eng.read_lane(req.lane)
             t = eng.timing()
             req.timing.prefill_ms, req.timing.prefill_tokens = t.prefill_ms, t.prefill_tokens

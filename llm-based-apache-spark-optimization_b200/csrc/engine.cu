@@ -601,6 +601,16 @@ int b200llm_set_lane(b200llm_engine *e, int32_t lane, int32_t next_token, int32_
     return B200LLM_OK;
 }
 
+int b200llm_set_history(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t n, int32_t pos0) {
+    B200_REQUIRE(e && e->ws && lane >= 0 && lane < e->cfg.max_lanes, "set_history: bad arguments");
+    B200_REQUIRE(n >= 0 && n <= 64 && (n == 0 || ids) && pos0 >= 0, "set_history: %d ids at pos %d", n, pos0);
+    int32_t ring[64];
+    for (int i = 0; i < 64; ++i) ring[i] = -1;
+    for (int i = 0; i < n; ++i) ring[(pos0 + i) & 63] = ids[i];   // same slot the embedding kernel uses: pos & 63
+    B200_CUDA_OK(cudaMemcpyAsync(e->lane_hist + (size_t)lane * 64, ring, sizeof(ring), cudaMemcpyHostToDevice, e->stream));
+    return B200LLM_OK;   // the pageable source is staged before the call returns
+}
+
 }  // extern "C"
 
 // ---------------------------------------------------------------- one forward pass

@@ -256,6 +256,44 @@ def test_scheduler_batches_concurrent_callers():
     eng.close()
 
 
+def test_prefix_cache_shares_system_prompt_pages():
+    """The reference sends one system prompt with every request (Flask/app.py:104,162; FastAPI/app.py:87,107).
+    The scheduler's prefix cache attaches the KV pages of that shared prefix to later requests: same tokens as
+    the oracle's full-prompt run, fewer tokens prefilled, pages returned to the pool when the cache is cleared."""
+    from b200llm import SamplingParams
+    from b200llm.scheduler import Scheduler
+    geo = lo.GEOMETRIES["tiny"]
+    sd = lo.make_weights(geo, 0xB200, sigma=0.08)
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    system = wg.gen_tokens(53, 900, geo.vocab)                       # 3 whole pages + 5 tokens
+    users = [wg.gen_tokens(n, 910 + i, geo.vocab) for i, n in enumerate([9, 1, 30, 12])]
+    prompts = [system + u for u in users] + [system[:40] + users[0]]  # the last one shares only 2 pages
+    want = [orc.greedy(p, 12)[0] for p in prompts]
+    eng = _engine("tiny", sd, max_lanes=2, max_ctx=160, max_rows=8)
+    free0 = len(eng._free_pages)
+    sched = Scheduler(eng, chunk=4)
+    greedy = SamplingParams(temperature=0.0)
+    prefilled = []
+    for p, w in zip(prompts, want):
+        toks, timing = sched.generate_ids(p, 12, greedy)
+        assert toks == w
+        prefilled.append(timing.prefill_tokens)
+    assert prefilled[0] == len(prompts[0])                           # cold
+    assert prefilled[1:4] == [len(p) - 48 for p in prompts[1:4]]     # 3 shared pages
+    assert prefilled[4] == len(prompts[4]) - 32                      # 2 shared pages
+    assert sched.cache.hits == 4 and sched.cache.misses == 1
+    # a repeat-penalty run sees the same 64-token window with and without the cache
+    pen = SamplingParams(temperature=0.0, repeat_penalty=1.5)
+    with_cache = sched.generate_ids(prompts[2], 12, pen)[0]
+    sched.cache.clear()
+    assert len(eng._free_pages) == free0 and all(r == 0 for r in eng._page_ref)
+    cold = Scheduler(eng, chunk=4, prefix_cache=False)
+    assert cold.generate_ids(prompts[2], 12, pen)[0] == with_cache
+    cold.shutdown()
+    sched.shutdown()
+    eng.close()
+
+
 def test_shim_replays_reference_call_sites():
     """The six ollama.generate call patterns of the reference, unmodified, against the shim."""
     import ollama

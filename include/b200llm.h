@@ -104,8 +104,11 @@ enum {
      * [128 rows x 64 k] tiles stored [N/128][K/64][128][64], each 16 KB tile laid out as a
      * 128-byte-swizzled K-major tensor-core operand (16-byte chunk c of row r at chunk c ^ (r & 7)),
      * so one bulk copy lands a ready MMA operand.  Needs N % 128 == 0 and K % 64 == 0; rows/cols
-     * in the descriptor are the logical [N, K].  When all five are bound they take precedence
-     * over the stage-major copies. */
+     * in the descriptor are the logical [N, K].  The lm_head alone may have a row count that is
+     * no multiple of 128 (vocab 32016; 32000 over 4 ranks): its copy is padded with zero rows to
+     * whole tiles and its descriptor carries the PADDED row count; the kernel neither stores nor
+     * ranks the padding rows.  When all five are bound they take precedence over the stage-major
+     * copies. */
     B200LLM_W_QKV_TM = 15,
     B200LLM_W_O_TM = 16,
     B200LLM_W_GATE_UP_TM = 17,

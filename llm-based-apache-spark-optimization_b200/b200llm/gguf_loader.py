@@ -16,8 +16,8 @@ Comparision.py:69-83).  A blob is a GGUF v3 file; this module reads it without t
 
 `load(path, device)` returns (Geometry, HF-named state dict of device bf16 tensors) ready for
 `weights.pack`; `register(name, path)` makes the model available to `ollama.generate(model=name)`.
-The GGUF tokenizer tables are parsed into the metadata dict but not used yet: the byte tokenizer
-stays the engine's tokenizer until the tokenizer row is built.
+The GGUF tokenizer tables (`tokenizer.ggml.*`) become the model's tokenizer: load_tokenizer() hands
+the metadata to tokenizer.from_gguf_metadata (SentencePiece BPE or byte-level BPE).
 """
 from __future__ import annotations
 
@@ -253,6 +253,16 @@ def load(path: str, device, name: str = "") -> Tuple[Any, Dict[str, Any]]:
     if missing:
         raise ValueError(f"{path}: missing tensors {missing[:4]}{'...' if len(missing) > 4 else ''}")
     return geo, sd
+
+
+def load_tokenizer(path: str):
+    """The tokenizer described by the file's `tokenizer.ggml.*` tables, or None when it has no tokenizer model
+    (a weights-only file: the caller keeps its stand-in)."""
+    from . import tokenizer
+    md = GGUFFile(path).metadata
+    if "tokenizer.ggml.model" not in md:
+        return None
+    return tokenizer.from_gguf_metadata(md)
 
 
 def expected_names(geo) -> List[str]:

@@ -16,7 +16,7 @@ import torch
 from . import _lib, geometry, weights
 from .engine import Engine
 from .scheduler import Scheduler
-from .tokenizer import ByteTokenizer
+from .tokenizer import TEMPLATES, ByteTokenizer
 
 SEED = 0xB200
 
@@ -25,9 +25,10 @@ SEED = 0xB200
 class LoadedModel:
     name: str
     engine: Engine
-    tokenizer: ByteTokenizer
+    tokenizer: object         # ByteTokenizer | SpmTokenizer | BpeTokenizer (same encode / decode / stop_ids)
     load_ns: int
     scheduler: Scheduler = None
+    template: str = ""        # Modelfile TEMPLATE; empty for the seeded random-init models (byte tokenizer)
 
 
 _models: Dict[str, LoadedModel] = {}
@@ -49,7 +50,7 @@ def get_model(name: str) -> LoadedModel:
     with _lock:
         m = _models.get(key)
         if m is not None:
-            return LoadedModel(m.name, m.engine, m.tokenizer, 0, m.scheduler)
+            return LoadedModel(m.name, m.engine, m.tokenizer, 0, m.scheduler, m.template)
         if not torch.cuda.is_available():
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         t0 = time.perf_counter_ns()
@@ -60,13 +61,18 @@ def get_model(name: str) -> LoadedModel:
             geo, sd = gguf_loader.load(ckpt, dev, name)
             w = weights.pack(geo, sd)
             del sd
+            tok = gguf_loader.load_tokenizer(ckpt)
         else:
             geo = geometry.resolve(name)
             w = weights.random_init(geo, SEED, dev)
+            tok = None
+        # a checkpoint with tokenizer tables is prompted through its model's template (by the registered name, else
+        # by the base name before ':'); without tables text goes through the byte stand-in, untemplated
+        template = (TEMPLATES.get(name) or TEMPLATES.get(name.split(":")[0], "")) if tok is not None else ""
         eng = Engine(geo, w, device=dev, max_lanes=int(os.environ.get("B200LLM_MAX_LANES", "8")),
                      max_ctx=int(os.environ.get("B200LLM_NUM_CTX", "4096")),
                      max_rows=int(os.environ.get("B200LLM_MAX_ROWS", "256")))   # prefill chunk = tcgen05 GEMM N limit
-        m = LoadedModel(key, eng, ByteTokenizer(geo.vocab), time.perf_counter_ns() - t0, Scheduler(eng))
+        m = LoadedModel(key, eng, tok or ByteTokenizer(geo.vocab), time.perf_counter_ns() - t0, Scheduler(eng), template)
         _models[key] = m
         return m
 

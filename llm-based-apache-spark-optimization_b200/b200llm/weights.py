@@ -100,7 +100,10 @@ def tile_major(w: torch.Tensor) -> torch.Tensor:
     tile contiguous and pre-swizzled (16-byte chunk c of row r stored at chunk c ^ (r & 7)), see
     B200LLM_W_*_TM in include/b200llm.h."""
     N, K = w.shape
-    assert N % 128 == 0 and K % 64 == 0
+    assert K % 64 == 0
+    if N % 128:     # lm_head of a vocabulary that is no multiple of 128 (32016, or 32000 / 4 ranks): zero rows up to
+        w = torch.cat([w, w.new_zeros(128 - N % 128, K)])   # the next tile; the kernel never stores or ranks them
+        N = w.shape[0]
     t = w.view(N // 128, 128, K // 64, 8, 8).permute(0, 2, 1, 3, 4)            # [tile, kb, row, chunk, 8]
     idx = torch.arange(8, device=w.device)[None, :] ^ (torch.arange(128, device=w.device)[:, None] & 7)
     out = t[:, :, torch.arange(128, device=w.device)[:, None], idx].contiguous()  # out[r, c] = in[r, c ^ (r & 7)]
@@ -112,8 +115,9 @@ def tile_major_ok(geo, tp_size: int = 1) -> bool:
     """Can every matrix of one rank's shard be cut into [128 x 64] tiles?"""
     nq, nkv, ffn, vocab = geo.n_q // tp_size, geo.n_kv // tp_size, geo.ffn // tp_size, geo.vocab // tp_size
     qkv = (nq + 2 * nkv) * geo.head_dim
-    shapes = [(qkv, geo.d), (geo.d, nq * geo.head_dim), (2 * ffn, geo.d), (geo.d, ffn), (vocab, geo.d)]
-    return all(n % 128 == 0 and k % 64 == 0 for n, k in shapes)
+    shapes = [(qkv, geo.d), (geo.d, nq * geo.head_dim), (2 * ffn, geo.d), (geo.d, ffn)]
+    # the lm_head's rows are padded to the next tile (tile_major), the other matrices must fit as they are
+    return all(n % 128 == 0 and k % 64 == 0 for n, k in shapes) and vocab >= 1 and geo.d % 64 == 0
 
 
 _TM_KIND = {_lib.W_QKV: _lib.W_QKV_TM, _lib.W_O: _lib.W_O_TM, _lib.W_GATE_UP: _lib.W_GATE_UP_TM,

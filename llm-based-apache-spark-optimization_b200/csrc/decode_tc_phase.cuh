@@ -172,7 +172,7 @@ __device__ void tcd_epilogue(const TcdParams &p, const TcdJob &job, const TcdSme
         const int n = t * 128 + warp * 32 + lane;
         if (job.epi == TCD_EPI_ADD) {
             asm volatile("red.global.add.f32 [%0], %1;" ::"l"(job.out + n), "f"(v) : "memory");
-        } else {
+        } else if (n < p.vocab) {   // rows past the vocabulary pad the last tile
             job.out[n] = v;
             if (v > c.best) c.best = v, c.best_i = n;
         }

@@ -491,7 +491,10 @@ int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, in
             case B200LLM_W_O_TM: if (!shape(c.d, (int64_t)e->nq_l * c.head_dim)) return B200LLM_EINVAL; e->layers[t.layer].wo_tm = t.dev; break;
             case B200LLM_W_GATE_UP_TM: if (!shape(2 * (int64_t)e->ffn_l, c.d)) return B200LLM_EINVAL; e->layers[t.layer].wgu_tm = t.dev; break;
             case B200LLM_W_DOWN_TM: if (!shape(c.d, e->ffn_l)) return B200LLM_EINVAL; e->layers[t.layer].wdown_tm = t.dev; break;
-            case B200LLM_W_LM_HEAD_TM: if (!shape(e->vocab_l, c.d)) return B200LLM_EINVAL; e->lm_head_tm = t.dev; break;
+            case B200LLM_W_LM_HEAD_TM:   // rows padded with zeros to whole 128-row tiles
+                if (!shape((e->vocab_l + 127) / 128 * 128, c.d)) return B200LLM_EINVAL;
+                e->lm_head_tm = t.dev;
+                break;
             default: set_error("tensor %d: unknown kind %d", i, t.kind); return B200LLM_EINVAL;
         }
     }
@@ -829,7 +832,7 @@ static bool tcd_usable(const b200llm_engine *e) {
     bool tiled = e->lm_head_tm != nullptr;
     for (auto &w : e->layers) tiled = tiled && w.wqkv_tm && w.wo_tm && w.wgu_tm && w.wdown_tm;
     if (c.tp_size > 1 && !e->ar_ready) return false;   // tensor parallel needs the peer inboxes (b200llm_tp_import)
-    return tiled && tcd_supported(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, e->vocab_l, c.n_layers);
+    return tiled && tcd_supported(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, (e->vocab_l + 127) / 128 * 128, c.n_layers);
 }
 
 static int tcd_prepare(b200llm_engine *e) {
@@ -850,7 +853,8 @@ static int tcd_prepare(b200llm_engine *e) {
         jobs[4 * l + 2] = TcdJob{w.wgu_tm, w.mlp_norm, nullptr, nullptr, e->gu_out, 2 * ffn, c.d, TCD_EPI_ADD, TCD_X_H | 0x400};
         jobs[4 * l + 3] = TcdJob{w.wdown_tm, nullptr, nullptr, nullptr, row_out, c.d, ffn, TCD_EPI_ADD, TCD_X_SWIGLU};
     }
-    jobs[4 * c.n_layers] = TcdJob{e->lm_head_tm, e->final_norm, nullptr, nullptr, e->logits, e->vocab_l, c.d, TCD_EPI_LOGITS, TCD_X_H};
+    // the lm_head streams whole tiles: N counts the zero rows that pad the last one, p.vocab bounds what is stored
+    jobs[4 * c.n_layers] = TcdJob{e->lm_head_tm, e->final_norm, nullptr, nullptr, e->logits, (e->vocab_l + 127) / 128 * 128, c.d, TCD_EPI_LOGITS, TCD_X_H};
     B200_CUDA_OK(cudaMemcpyAsync(e->mega_jobs, jobs.data(), jobs.size() * sizeof(TcdJob), cudaMemcpyHostToDevice, e->stream));
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));  // `jobs` is a pageable temporary
     e->tcd_ready = true;
@@ -888,7 +892,7 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps) {
     p.part_ml = p.part_o + (size_t)e->nq_l * ns * c.head_dim;
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
-    B200_REQUIRE(tcd_plan(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, e->vocab_l, c.n_layers, &p.n_stages, &p.n_bslots),
+    B200_REQUIRE(tcd_plan(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, (e->vocab_l + 127) / 128 * 128, c.n_layers, &p.n_stages, &p.n_bslots),
                  "tcd: geometry does not fit");
     if (const char *ns = getenv("B200LLM_TCD_STAGES")) p.n_stages = atoi(ns) < p.n_stages ? atoi(ns) : p.n_stages;
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;

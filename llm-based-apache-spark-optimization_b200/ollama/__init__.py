@@ -94,7 +94,7 @@ def generate(model: str = "", prompt: str = "", suffix: str = "", system: str = 
         raise ResponseError(e.message, 500) from e
     opt = dict(DEFAULT_OPTIONS)
     opt.update(options or {})
-    text = render_prompt(system or "", prompt or "", template or "", raw)
+    text = render_prompt(system or "", prompt or "", template or m.template, raw)
     ids = _list(context or []) + m.tokenizer.encode(text, bos=not context)
     max_ctx = m.engine.max_pages_per_lane * 16
     num_predict = int(opt["num_predict"])

@@ -70,8 +70,9 @@ def _permute(w, n_head):      # llama.cpp convert_hf_to_gguf.py LlamaModel.permu
 _INV = {v: k for k, v in gguf_loader._LAYER_MAP.items()}
 
 
-def write_gguf(path, geo, sd, qt=None):
-    """What llama.cpp's converter emits for a Llama checkpoint (names, q/k permutation, metadata)."""
+def write_gguf(path, geo, sd, qt=None, tok_md=None):
+    """What llama.cpp's converter emits for a Llama checkpoint (names, q/k permutation, metadata; with `tok_md`
+    also the byte-level BPE tokenizer tables)."""
     w = gguf.GGUFWriter(path, "llama")
     w.add_name(geo.name)
     w.add_block_count(geo.n_layers)
@@ -82,7 +83,16 @@ def write_gguf(path, geo, sd, qt=None):
     w.add_key_length(geo.head_dim)
     w.add_rope_freq_base(geo.rope_theta)
     w.add_layer_norm_rms_eps(geo.rms_eps)
-    w.add_token_list([f"<{i}>" for i in range(geo.vocab)])
+    if tok_md is None:
+        w.add_token_list([f"<{i}>" for i in range(geo.vocab)])
+    else:
+        w.add_tokenizer_model(tok_md["tokenizer.ggml.model"])
+        w.add_tokenizer_pre(tok_md["tokenizer.ggml.pre"])
+        w.add_token_list(tok_md["tokenizer.ggml.tokens"])
+        w.add_token_types(tok_md["tokenizer.ggml.token_type"])
+        w.add_token_merges(tok_md["tokenizer.ggml.merges"])
+        w.add_bos_token_id(tok_md["tokenizer.ggml.bos_token_id"])
+        w.add_eos_token_id(tok_md["tokenizer.ggml.eos_token_id"])
     if geo.rope_llama3:
         w.add_tensor("rope_freqs.weight", np.ones(geo.head_dim // 2, np.float32))
     for name, t in sd.items():
@@ -168,3 +178,40 @@ def test_gguf_checkpoint_runs_like_the_same_weights_packed_directly(tmp_path):
     assert outs[0] == outs[1]
     oracle = lo.LlamaOracle(lo.GEOMETRIES["small"], {k: v.float() for k, v in sd.items()}, kv_dtype=torch.bfloat16)
     assert outs[0] == oracle.greedy(prompt.tolist(), 24, keep_logits=False)[0]
+
+
+@pytest.mark.gpu
+def test_text_in_text_out_with_the_checkpoints_tokenizer_and_template(tmp_path):
+    """`ollama.generate(model=, system=, prompt=) -> .response` on a GGUF checkpoint that carries tokenizer tables
+    (the reference's call, Flask/app.py:160-166): the prompt goes through the model's template and the file's
+    byte-level BPE, the answer back through it.  Checkers: the `tokenizers` library for text <-> ids, the CPU
+    oracle for the ids in between.  The vocabulary (trained here) is no multiple of 128 rows."""
+    from dataclasses import replace
+    from b200llm import runtime, tokenizer
+    from oracle import llama_oracle as lo
+    from test_tokenizer import train_bpe
+    import ollama
+    tk, tok, vocab, md = train_bpe()
+    name = "llama3.2:tiny-bpe"
+    geo = replace(geometry.resolve("tiny"), name=name, vocab=len(tok.tokens))
+    assert geo.vocab % 128 != 0
+    sd = _hf_state_dict(geo, 23)
+    path = str(tmp_path / "tiny_bpe.gguf")
+    write_gguf(path, geo, sd, tok_md=md)
+    gguf_loader.register(name, path)
+    system, prompt = "You explain errors.", "Why did the query fail near the unexpected token?"
+    try:
+        r = ollama.generate(model=name, system=system, prompt=prompt, options={"temperature": 0, "num_predict": 20})
+    finally:
+        runtime.unload_all()
+    text = tokenizer.render_prompt(system, prompt, model="llama3.2")
+    ids = [vocab["<|begin_of_text|>"]] + tk.encode(text, add_special_tokens=False).ids
+    assert r.prompt_eval_count == len(ids)
+    oracle = lo.LlamaOracle(replace(lo.GEOMETRIES["tiny"], vocab=geo.vocab), {k: v.float() for k, v in sd.items()},
+                            kv_dtype=torch.bfloat16)
+    want = oracle.greedy(ids, 20, keep_logits=False)[0]
+    stops = {vocab["<|end_of_text|>"], vocab["<|eot_id|>"]}
+    cut = next((i for i, t in enumerate(want) if t in stops), len(want))
+    assert r.response == tk.decode(want[:cut], skip_special_tokens=True)
+    assert r.done_reason == ("stop" if cut < len(want) else "length")
+    assert list(r.context) == ids + want[:cut]

@@ -72,6 +72,32 @@ def test_live_oracle_parity(name, use_graphs, use_pdl, mega, golden_dir, monkeyp
     eng.close()
 
 
+@pytest.mark.parametrize("name,vocab", [("tiny", 1000), ("small", 4000 + 16)])
+def test_vocabulary_that_is_no_multiple_of_the_tile(name, vocab, monkeypatch):
+    """CodeLlama-class checkpoints have 32016 vocabulary rows: the tile-major lm_head copy is padded with zero
+    rows to whole 128-row tiles and the tcgen05 persistent kernel still runs (one launch), never storing or
+    ranking the padding: tokens and logits equal the oracle's."""
+    from dataclasses import replace
+    from b200llm import Engine, geometry, weights
+    ogeo = replace(lo.GEOMETRIES[name], vocab=vocab)
+    sd = lo.make_weights(ogeo, 0xC0DE, sigma=0.08)
+    orc = lo.LlamaOracle(ogeo, sd, kv_dtype=torch.bfloat16)
+    prompt = wg.gen_tokens(21, 77, vocab)
+    toks, lg, _ = orc.greedy(prompt, 24)
+    geo = replace(geometry.resolve(name), vocab=vocab)
+    pw = weights.pack(geo, {k: v.cuda() for k, v in sd.items()})
+    eng = Engine(geo, pw, max_lanes=1, max_ctx=128, max_rows=8, use_tc=False, use_megakernel=True)
+    lane = eng.open_lane()
+    eng.prefill(lane, prompt)
+    first, _ = eng.read_lane(lane)
+    out = eng.decode([lane], 23)[:, 0].tolist()
+    assert eng.timing().kernel_launches == 1          # the persistent kernel, not the per-phase fallback
+    assert [first] + out == toks
+    got = eng.logits(0)
+    assert got.shape[0] == vocab and _rel(got, lg[23].numpy()) <= TIGHT_TOL
+    eng.close()
+
+
 @pytest.mark.parametrize("mega", [False, True])
 def test_teacher_forced_logits_every_step(mega, golden_dir):
     """Per-step logits along the golden token path (b200llm_set_lane forces the input token)."""

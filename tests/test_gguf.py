@@ -201,7 +201,7 @@ def test_text_in_text_out_with_the_checkpoints_tokenizer_and_template(tmp_path):
     gguf_loader.register(name, path)
     system, prompt = "You explain errors.", "Why did the query fail near the unexpected token?"
     try:
-        r = ollama.generate(model=name, system=system, prompt=prompt, options={"temperature": 0, "num_predict": 20})
+        r = ollama.generate(model=name, system=system, prompt=prompt, options={"temperature": 0, "repeat_penalty": 1.0, "num_predict": 20})
     finally:
         runtime.unload_all()
     text = tokenizer.render_prompt(system, prompt, model="llama3.2")

@@ -291,8 +291,8 @@ def test_prefix_cache_shares_system_prompt_pages():
     geo = lo.GEOMETRIES["tiny"]
     sd = lo.make_weights(geo, 0xB200, sigma=0.08)
     orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
-    system = wg.gen_tokens(53, 900, geo.vocab)                       # 3 whole pages + 5 tokens
-    users = [wg.gen_tokens(n, 910 + i, geo.vocab) for i, n in enumerate([9, 1, 30, 12])]
+    system = [int(t) for t in wg.gen_tokens(53, 900, geo.vocab)]     # 3 whole pages + 5 tokens
+    users = [[int(t) for t in wg.gen_tokens(n, 910 + i, geo.vocab)] for i, n in enumerate([9, 1, 30, 12])]
     prompts = [system + u for u in users] + [system[:40] + users[0]]  # the last one shares only 2 pages
     want = [orc.greedy(p, 12)[0] for p in prompts]
     eng = _engine("tiny", sd, max_lanes=2, max_ctx=160, max_rows=8)

@@ -65,12 +65,13 @@ struct TcdSmem {
 
 __host__ __device__ __forceinline__ size_t tcd_mrg_bytes(int hd, int gq) { return (size_t)kTW * gq * (hd + 2) * 4; }
 
-__device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int n_stages, int n_bslots) {
+// Layout: everything the compute warps address sits at COMPILE-TIME offsets from the base (merge buffer,
+// barriers, scratch, page table, phase descriptors), so those pointers cost no registers; the operand blocks
+// and the ring (1024-byte aligned, sizes known at launch) follow.
+__device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int n_jobs, int n_bslots) {
     TcdSmem s;
-    s.ring = base;
-    s.bop = base + n_stages * kTStageBytes;
-    s.mrg = reinterpret_cast<float *>(s.bop + n_bslots * 1024);
-    uint8_t *q = reinterpret_cast<uint8_t *>(s.mrg) + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15);
+    s.mrg = reinterpret_cast<float *>(base);
+    uint8_t *q = base + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15);
     s.full = reinterpret_cast<uint64_t *>(q);
     s.empty = s.full + kTMaxStages;
     s.acc_full = s.empty + kTMaxStages;
@@ -81,12 +82,15 @@ __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int 
     s.rope = reinterpret_cast<float *>(s.misc + 64);
     s.ptab = reinterpret_cast<int32_t *>(s.rope + 128);
     s.jobs = reinterpret_cast<TcdJob *>(s.ptab + kTMaxPtab);
+    const size_t head = (size_t)(reinterpret_cast<uint8_t *>(s.jobs) - base) + (size_t)n_jobs * sizeof(TcdJob);
+    s.bop = base + ((head + 1023) & ~(size_t)1023);
+    s.ring = s.bop + (size_t)n_bslots * 1024;
     return s;
 }
 
 static size_t tcd_fixed_smem_bytes(int hd, int gq, int n_jobs) {  // everything but the ring and the operand blocks
     return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + (2 * kTMaxStages + 2 * kTAcc) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 +
-           kTMaxPtab * 4 + (size_t)n_jobs * sizeof(TcdJob) + 1024;  // slack for the 1024-byte alignment of the base
+           kTMaxPtab * 4 + (size_t)n_jobs * sizeof(TcdJob) + 2 * 1024;  // slack: 1024-byte alignment of the base and of the operand blocks
 }
 static size_t tcd_smem_bytes(int hd, int gq, int n_jobs, int n_stages, int n_bslots) {
     return (size_t)n_stages * kTStageBytes + (size_t)n_bslots * 1024 + tcd_fixed_smem_bytes(hd, gq, n_jobs);
@@ -296,7 +300,13 @@ struct TcdCtx {
 // (debug) tagged globaltimer stamps of thread 0: tag in bits 48.., nanoseconds below
 enum { TT_STEP = 1, TT_XCONV = 2, TT_XREADY = 3, TT_EPI = 4, TT_BAR = 5, TT_ATT_Q = 6, TT_ATT_KV = 7, TT_ATT_WARPS = 8,
        TT_ATT_DONE = 9 };
+// Compiled in only with -DB200LLM_TCD_TRACE (make TRACE=1): the cursor and the stamps cost registers, and what the
+// 128-register kernel spills it reloads right behind the grid barriers (an L2 round trip each, L1 was just invalidated).
 __device__ __forceinline__ void tcd_trace(const TcdParams &p, int &ti, int bid, int tid, int tag) {
+#ifndef B200LLM_TCD_TRACE
+    (void)p, (void)ti, (void)bid, (void)tid, (void)tag;
+    return;
+#endif
     if (ti >= 0 && tid == 0 && ti < 1000) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

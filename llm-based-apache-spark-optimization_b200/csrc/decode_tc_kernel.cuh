@@ -6,10 +6,10 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
     extern __shared__ uint8_t smem_dyn[];
     // the swizzled operand tiles need 1024-byte alignment
     uint8_t *smem_raw = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
-    const TcdSmem s = tcd_carve(smem_raw, HD, GQ, p.n_stages, p.n_bslots);
+    const int n_jobs = 4 * p.n_layers + 1;
+    const TcdSmem s = tcd_carve(smem_raw, HD, GQ, n_jobs, p.n_bslots);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int G = gridDim.x, bid = blockIdx.x;
-    const int n_jobs = 4 * p.n_layers + 1;
 
     if (tid == 0) {
         for (int i = 0; i < kTMaxStages; ++i) {
@@ -63,7 +63,11 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             tcd_trace(p, c.ti, bid, tid, TT_EPI);
         };
         for (int step = 0; step < p.n_steps; ++step) {
+#ifdef B200LLM_TCD_TRACE
             c.ti = (p.trace != nullptr && step == p.trace_step && (bid == 0 || bid == G - 1)) ? 0 : -1;
+#else
+            c.ti = -1;
+#endif
             tcd_trace(p, c.ti, bid, tid, TT_STEP);
             c.tok = min(max(c.tok, 0), p.vocab_global - 1);
             if (bid == 0 && tid == 0) p.lane_hist[(size_t)p.lane * 64 + (c.pos & 63)] = c.tok;
@@ -75,14 +79,20 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             }
             for (int l = 0; l < p.n_layers; ++l) {
                 const TcdJob &qkv_job = s.jobs[4 * l];
+#ifdef B200LLM_TCD_TRACE
                 int arr_i = (p.trace != nullptr && step == p.trace_step && l == 1 && tid == 0) ? 0 : -1;
+#else
+                constexpr int arr_i = -1;
+#endif
                 auto arrive_stamp = [&]() {  // (debug) when does each CTA reach the barriers of layer 1?
+#ifdef B200LLM_TCD_TRACE
                     if (arr_i >= 0) {
                         unsigned long long t;
                         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
                         p.trace[2048 + arr_i * G + bid] = t;
                         ++arr_i;
                     }
+#endif
                 };
                 tcd_attn_prefetch<HD>(p, qkv_job, s, c, G, bid, tid);
                 phase(4 * l);      // rmsnorm + qkv (raw sums)

@@ -175,7 +175,7 @@ __device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, in
         // with one dependent load after the other.  Relaxed polls and ONE fence at the end: an
         // acquire load per poll costs an L1 invalidate (CCTL.IVALL) per iteration
         unsigned a = tcd_poll(ctr);
-        __nanosleep(300);
+        __nanosleep(300);   // (0 / 100 / 300 ns measure the same, 600 ns costs 1 %)
         for (;;) {
             const unsigned b = tcd_poll(ctr);
             if (a >= target) break;
@@ -287,12 +287,13 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
     }
 }
 
+// Kept small: what lives across the whole step competes with the attention phase for the 128 registers, and a
+// spilled value is reloaded behind a grid barrier at L2 latency.  (The tensor-parallel sequence numbers live in
+// shared memory: s.misc[62] reductions, s.misc[63] token exchanges.)
 struct TcdCtx {
     int tok, pos;
     int ti;               // trace cursor (-1: tracing off for this step)
     uint32_t as;          // accumulator counter, in lock-step with the MMA issuer
-    int att_ns;           // split-T factor of this step's attention phases
-    unsigned ar_s, tok_s; // tensor parallel: sequence numbers of the reductions / token exchanges done so far
     float best;           // lm_head: running (max, argmax) of this thread
     int best_i;
 };
@@ -318,6 +319,11 @@ __device__ __forceinline__ uint32_t tcd_pack_bf16(float a, float b) {
     return (uint32_t)f32_to_bf16_bits(a) | ((uint32_t)f32_to_bf16_bits(b) << 16);
 }
 __device__ __forceinline__ float tcd_bf16_round(float a) { return __uint_as_float((uint32_t)f32_to_bf16_bits(a) << 16); }
+
+// split-T factor of the attention phases at position `pos`: one half-page (one L2 round trip) per warp while splits last
+__device__ __forceinline__ int tcd_att_ns(const TcdParams &p, int pos) {
+    return min(p.n_splits, (2 * (pos / kTPT + 1) + kTW - 1) / kTW);
+}
 
 #include "decode_tc_phase.cuh"
 #include "decode_tc_attn.cuh"

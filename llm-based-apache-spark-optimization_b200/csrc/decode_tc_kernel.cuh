@@ -48,8 +48,8 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
     } else {
         TcdCtx c;
         c.as = 0;
-        c.ar_s = c.tok_s = 0;
-        if (p.tp_size > 1) c.ar_s = __ldcg(p.ar_seq), c.tok_s = __ldcg(p.ar_seq + 2);
+        if (p.tp_size > 1 && tid == 0) s.misc[62] = (int)__ldcg(p.ar_seq), s.misc[63] = (int)__ldcg(p.ar_seq + 2);
+        if (p.tp_size > 1) bar_sync(1, kTC);
         c.tok = __ldcg(p.lane_token + p.lane);
         c.pos = __ldcg(p.lane_pos + p.lane);
         unsigned bar_no = 0;
@@ -71,7 +71,6 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             tcd_trace(p, c.ti, bid, tid, TT_STEP);
             c.tok = min(max(c.tok, 0), p.vocab_global - 1);
             if (bid == 0 && tid == 0) p.lane_hist[(size_t)p.lane * 64 + (c.pos & 63)] = c.tok;
-            c.att_ns = min(p.n_splits, (2 * (c.pos / kTPT + 1) + kTW - 1) / kTW);  // as in tcd_attn_phase
             if (tid < HD / 2) {  // RoPE angles of this position
                 float sn, cs;
                 sincosf((float)c.pos * p.inv_freq[tid], &sn, &cs);
@@ -109,7 +108,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 if (p.tp_size > 1) {   // o_proj is row-parallel: h += sum over ranks of the partial sums
-                    tcd_allreduce_phase(p, c, G, bid, tid);
+                    tcd_allreduce_phase(p, s, G, bid, tid);
                     tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
                 }
                 phase(4 * l + 2);  // rmsnorm + gate/up (raw sums)
@@ -121,7 +120,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 if (p.tp_size > 1) {   // down_proj is row-parallel too
-                    tcd_allreduce_phase(p, c, G, bid, tid);
+                    tcd_allreduce_phase(p, s, G, bid, tid);
                     tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
                 }
             }
@@ -187,8 +186,8 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             }
         }
         if (p.tp_size > 1 && bid == 0 && tid == 0) {   // sequence numbers for the next launch (and for tp_ar.cu's kernel)
-            *reinterpret_cast<volatile unsigned *>(p.ar_seq) = c.ar_s;
-            *reinterpret_cast<volatile unsigned *>(p.ar_seq + 2) = c.tok_s;
+            *reinterpret_cast<volatile unsigned *>(p.ar_seq) = (unsigned)s.misc[62];
+            *reinterpret_cast<volatile unsigned *>(p.ar_seq + 2) = (unsigned)s.misc[63];
         }
     }
     // every role has finished its schedule: all MMAs are committed and read back

@@ -18,6 +18,7 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
     const int kb_start = r.g0 % nkb;
     const int n_slots = min(r.g1 - r.g0, nkb);
     const int x_kind = job.x_src & 0xff;
+    const int att_ns = x_kind == TCD_X_ATT ? tcd_att_ns(p, c.pos) : 1;
     const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
 
     {   // the RMSNorm gain vectors of the next two phases are cold (read once per step): pull them into L2
@@ -79,7 +80,7 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
             v[2] = (b.x / (1.f + expf(-b.x))) * b.y, v[3] = (b.z / (1.f + expf(-b.z))) * b.w;
             v[4] = (cc.x / (1.f + expf(-cc.x))) * cc.y, v[5] = (cc.z / (1.f + expf(-cc.z))) * cc.w;
             v[6] = (d.x / (1.f + expf(-d.x))) * d.y, v[7] = (d.z / (1.f + expf(-d.z))) * d.w;
-        } else if (x_kind == TCD_X_ATT && c.att_ns > 1) {
+        } else if (x_kind == TCD_X_ATT && att_ns > 1) {
             // split-T attention partials of this head -> merged output (running max, fixed split order)
             const int hd = p.head_dim, hq = (chunk * 8) / hd, dd = (chunk * 8) % hd;
             const size_t pb = (size_t)hq * p.n_splits;
@@ -87,7 +88,7 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
 #pragma unroll
             for (int e = 0; e < 8; ++e) v[e] = 0.f;
 #pragma unroll 4
-            for (int sp = 0; sp < c.att_ns; ++sp) {
+            for (int sp = 0; sp < att_ns; ++sp) {
                 const float2 ml = __ldcg(reinterpret_cast<const float2 *>(p.part_ml + (pb + sp) * 2));
                 const float4 a = __ldcg(reinterpret_cast<const float4 *>(p.part_o + (pb + sp) * hd + dd));
                 const float4 b = __ldcg(reinterpret_cast<const float4 *>(p.part_o + (pb + sp) * hd + dd + 4));
@@ -194,8 +195,8 @@ __device__ __forceinline__ void tcd_st_release_sys(unsigned *q, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(q), "r"(v) : "memory");
 }
 
-__device__ void tcd_allreduce_phase(const TcdParams &p, TcdCtx &c, int G, int bid, int tid) {
-    const unsigned sq = ++c.ar_s;
+__device__ void tcd_allreduce_phase(const TcdParams &p, const TcdSmem &s, int G, int bid, int tid) {
+    const unsigned sq = (unsigned)s.misc[62] + 1u;
     const int phase = (int)(sq & 1u);
     const int n_slices = (p.d + 1023) / 1024;
     for (int j = bid; j < n_slices; j += G) {
@@ -229,13 +230,15 @@ __device__ void tcd_allreduce_phase(const TcdParams &p, TcdCtx &c, int G, int bi
             *reinterpret_cast<float4 *>(p.h + i) = hv;
         }
     }
+    bar_sync(1, kTC);   // every thread has read the sequence number
+    if (tid == 0) s.misc[62] = (int)sq;
 }
 
 // ---- tensor parallel: every rank's best (logit, token id) -> the global greedy token ------------------
 // Called by all compute threads of every CTA with this rank's winner; CTA 0 pushes it to the peers, every
 // CTA waits for the peers' entries in local memory and returns the best of all (lowest id on ties).
 __device__ int tcd_token_exchange(const TcdParams &p, TcdCtx &c, const TcdSmem &s, float m, int gi, int bid, int tid) {
-    const unsigned sq = ++c.tok_s;
+    const unsigned sq = (unsigned)s.misc[63] + 1u;
     const int phase = (int)(sq & 1u);
     const unsigned long long mine = (unsigned long long)__float_as_uint(m) | ((unsigned long long)(unsigned)gi << 32);
     if (bid == 0 && tid < p.tp_size && tid != p.tp_rank) {
@@ -260,5 +263,6 @@ __device__ int tcd_token_exchange(const TcdParams &p, TcdCtx &c, const TcdSmem &
     for (int r = 1; r < p.tp_size; ++r)
         if (s.red[48 + r] > bm || (s.red[48 + r] == bm && s.misc[48 + r] < bi)) bm = s.red[48 + r], bi = s.misc[48 + r];
     bar_sync(1, kTC);   // red/misc are reused
+    if (tid == 0) s.misc[63] = (int)sq;   // read again only after the barriers of a whole step
     return bi;
 }

@@ -146,7 +146,7 @@ def run_reference(args):
               f"{PROMPT_LEN}-id workload), torch CPU bf16, {cores} threads")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": min(args.warmup, 4), "ms_per_step": 1000.0 * dt / args.steps, "higher_is_better": True,
-            "scaling": "strong" if tp_mode else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": "strong" if (args.tp and args.gpus > 1) else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload_name(args.model, 1), "l2": "inputs larger than L2"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

@@ -1,6 +1,7 @@
 """CPU tests of the host logic: registry, byte accounting, tokenizer stand-in, the shim's
 call surface (the six reference call sites), weight packing."""
 import inspect
+import os
 
 import numpy as np
 import pytest
@@ -83,3 +84,20 @@ def test_pack_layout_cpu():
     assert torch.equal(torch.cat([p[(_lib.W_DOWN, 0)] for p in parts], 1), sd["model.layers.0.mlp.down_proj.weight"])
     assert torch.equal(torch.cat([p[(_lib.W_LM_HEAD, -1)] for p in parts], 0), sd["model.embed_tokens.weight"])
     assert parts[0][(_lib.W_QKV, 0)].shape[0] == (geo.n_q + 2 * geo.n_kv) * hd // 2
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` (the CPU arm the driver times beside ours) must exit 0 and print one JSON line
+    with the contract's keys; run here on the tiny geometry so that it takes seconds."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--model", "tiny",
+                          "--steps", "2", "--warmup", "1"], capture_output=True, text=True, timeout=300, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "tok/s" and line["value"] > 0
+    for key in ("metric", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "config", "cpu_baseline", "e2e"):
+        assert key in line
+    assert line["cpu_baseline"]["kind"] in ("port", "reference") and line["e2e"]["h2d_bytes_per_step"] == 0

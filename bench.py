@@ -119,6 +119,11 @@ def cpu_decode_tok_s(model, n_prompt, n_steps, n_warm):
     import torch
     from oracle import llama_oracle as lo
     from oracle import weightgen as wg
+    # all host cores: torchrun exports OMP_NUM_THREADS=1 for multi-rank launches, and only rank 0 runs this leg
+    try:
+        torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
+    except (AttributeError, OSError):
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
     geo = lo.GEOMETRIES[model]
     sd = lo.make_weights(geo, 0xB200)
     orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16, compute_dtype=torch.bfloat16)

@@ -1,4 +1,6 @@
 """Debug: phase timeline of the tcgen05 persistent decode kernel (B200LLM_MEGA_TRACE=1).
+Needs the trace build of the library: make -C llm-based-apache-spark-optimization_b200/csrc clean all TRACE=1
+(the default build compiles the stamps out; rebuild without TRACE afterwards).
 Tagged stamps of thread 0 of CTA 0 and of the last CTA; durations are attributed to the tag
 that ENDS the interval."""
 import ctypes as C

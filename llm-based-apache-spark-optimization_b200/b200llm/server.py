@@ -48,6 +48,17 @@ def _resolve(name: str):
     return geometry.resolve(name)
 
 
+def _template_of(name: str) -> str:
+    """The TEMPLATE generate renders for this model: the registered Modelfile template when the model is served
+    from a checkpoint with tokenizer tables, else the stand-in rendering (system, blank line, prompt)."""
+    from . import runtime, tokenizer
+    if name in runtime._checkpoints:
+        tpl = tokenizer.TEMPLATES.get(name) or tokenizer.TEMPLATES.get(name.split(":")[0], "")
+        if tpl:
+            return tpl
+    return "{{ if .System }}{{ .System }}\n\n{{ end }}{{ .Prompt }}"
+
+
 def _details(geo) -> Dict[str, Any]:
     return {"parent_model": "", "format": "b200llm-bf16", "family": "llama", "families": ["llama"],
             "parameter_size": f"{geo.params / 1e9:.1f}B", "quantization_level": "BF16"}
@@ -136,7 +147,7 @@ class OllamaHandler(BaseHTTPRequestHandler):
                 "llama.attention.key_length": geo.head_dim, "llama.feed_forward_length": geo.ffn,
                 "llama.vocab_size": geo.vocab, "llama.rope.freq_base": geo.rope_theta,
                 "llama.attention.layer_norm_rms_epsilon": geo.rms_eps}
-        self._send_json(200, {"modelfile": f"FROM {name}\n", "parameters": "", "template": "{{ .Prompt }}",
+        self._send_json(200, {"modelfile": f"FROM {name}\n", "parameters": "", "template": _template_of(name),
                               "details": _details(geo), "model_info": info})
 
     def _generate(self, body: Dict[str, Any]) -> None:

@@ -33,7 +33,7 @@ METRIC = "decode_tok_s_llama3.2-3b_bs1"
 UNIT = "tok/s"
 PROMPT_LEN = 296          # 20 system + 25 wrapper + ~250 Spark-error tokens
 E2E_NEW_TOKENS = 128
-NCU_DRAM_BYTES_PER_STEP = (19.348707e9 + 6.174e6) / 3   # profiles/tcd_full_r1d_summary.txt (3-step launch)
+NCU_DRAM_BYTES_PER_STEP = (19.343379e9 + 7.5648e6) / 3   # profiles/tcd_full_r1e_summary.txt (3-step launch)
 
 
 def parse_args():
@@ -313,7 +313,7 @@ def run_b200(args):
                                    if (bs == 1 and not args.no_mega) else "CUDA graph of the per-phase kernels",
                          "what": "algorithmic bytes B(bs, mean ctx) of SURVEY.md 8(d) x steps / device time of the "
                                  "timed region; traffic = dram read+write bytes of the same kernel under ncu "
-                                 "(profiles/tcd_full_r1d_summary.txt: 19.35 GB for a 3-step launch), scaled to "
+                                 "(profiles/tcd_full_r1e_summary.txt: 19.34 GB for a 3-step launch), scaled to "
                                  "the steps of this launch",
                          "bytes_per_launch": step_bytes * args.steps, "bytes_per_step": step_bytes},
         }

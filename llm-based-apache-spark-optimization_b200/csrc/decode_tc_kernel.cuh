@@ -77,6 +77,10 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 s.rope[2 * tid] = cs, s.rope[2 * tid + 1] = sn;
             }
             for (int l = 0; l < p.n_layers; ++l) {
+                // CTA-uniform loop state is parked in shared memory across the attention phase (the register peak of the
+                // kernel): left to ptxas it goes to local memory and comes back at L2 latency behind the grid barriers
+                // (7 % of all stall samples sat on ONE such reload, profiles/tcd_full_r1e_summary.txt)
+                if (tid == 0) s.misc[57] = step, s.misc[58] = l, s.misc[59] = (int)bar_no + 1;
                 const TcdJob &qkv_job = s.jobs[4 * l];
 #ifdef B200LLM_TCD_TRACE
                 int arr_i = (p.trace != nullptr && step == p.trace_step && l == 1 && tid == 0) ? 0 : -1;
@@ -99,6 +103,9 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 tcd_attn_phase<HD, GQ>(p, qkv_job, s, c, G, bid, tid);  // rope + kv append + attention
+                step = reinterpret_cast<volatile int *>(s.misc)[57];   // written before the barrier above
+                l = reinterpret_cast<volatile int *>(s.misc)[58];
+                bar_no = (unsigned)reinterpret_cast<volatile int *>(s.misc)[59];
                 tcd_trace(p, c.ti, bid, tid, TT_ATT_DONE);
                 arrive_stamp();
                 tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);

@@ -157,6 +157,16 @@ bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, i
     return tcd_plan(d, ffn, n_q, n_kv, head_dim, vocab, n_layers, &st, &sl);
 }
 
+// The in-kernel sampler keeps kTSampPerThread logit rows per compute thread and its scratch in the attention
+// merge buffer; top-k beyond kTcdSampK (or "no top-k" with a temperature) stays on the stand-alone sample_kernel.
+bool tcd_sampler_supported(int vocab_rows, int head_dim, int gq, float temperature, int top_k) {
+    const int tiles = (vocab_rows + 127) / 128;
+    const int rows_per_cta = (tiles + kNumSMs - 1) / kNumSMs * 128;
+    if (rows_per_cta > 4 * kTC) return false;
+    if (tcd_mrg_bytes(head_dim, gq) < 64 * 4 + 2 * kTW * 8 + kTcdSampK * 8 + kTcdSampK * 4) return false;
+    return temperature <= 0.f || (top_k >= 1 && top_k <= kTcdSampK);
+}
+
 __device__ __forceinline__ bool tcd_whole(const TcdParams &p, int j, int n_jobs) {
     return j == n_jobs - 1 && !p.split_all;
 }
@@ -327,6 +337,7 @@ __device__ __forceinline__ int tcd_att_ns(const TcdParams &p, int pos) {
 
 #include "decode_tc_phase.cuh"
 #include "decode_tc_attn.cuh"
+#include "decode_tc_sample.cuh"
 #include "decode_tc_kernel.cuh"
 
 }  // namespace b200

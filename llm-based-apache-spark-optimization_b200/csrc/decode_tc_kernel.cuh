@@ -134,6 +134,21 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             // ---- final norm + lm_head: logits, per-CTA (max, lowest argmax) ----
             c.best = -INFINITY, c.best_i = 0x7fffffff;
             phase(n_jobs - 1);
+            if (p.sample == 2) {
+                // ---- sampler chain in the kernel: penalty + per-CTA top-k, barrier, redundant merge + draw ----
+                const int k = p.temperature > 0.f ? p.top_k : 1;
+                tcd_sample_local(p, s.jobs[n_jobs - 1], s, k, G, bid, tid);
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                c.tok = tcd_sample_merge(p, s, c, k, G, tid);
+                c.pos += 1;
+                if (bid == 0 && tid == 0) {
+                    p.lane_token[p.lane] = c.tok;
+                    p.lane_pos[p.lane] = c.pos;
+                    p.gen_out[step] = c.tok;
+                }
+                continue;
+            }
             {
                 float m = c.best;
                 int mi = c.best_i;
@@ -235,6 +250,13 @@ static int tcd_launch_t(const TcdParams &p, cudaStream_t stream) {
 int tcd_decode_launch(const TcdParams &p, cudaStream_t stream) {
     B200_REQUIRE(p.n_steps >= 1 && (p.sample || p.n_steps == 1), "tcd: n_steps must be 1 when sampling is external");
     B200_REQUIRE(p.n_splits >= 1, "tcd: n_splits < 1");
+    if (p.sample == 2) {
+        B200_REQUIRE(p.cand != nullptr && !p.split_all && p.tp_size == 1, "tcd: in-kernel sampler needs a candidate buffer, whole lm_head tiles and tp_size 1");
+        B200_REQUIRE(tcd_sampler_supported(p.vocab, p.head_dim, p.n_kv > 0 ? p.n_q / p.n_kv : 1, p.temperature, p.top_k),
+                     "tcd: in-kernel sampler does not take top_k %d at temperature %g (1..%d) or this vocabulary", p.top_k,
+                     (double)p.temperature, kTcdSampK);
+        B200_REQUIRE(p.repeat_penalty > 0.f, "tcd: repeat_penalty must be positive");
+    }
     B200_REQUIRE(4 * p.n_layers + 1 <= kTMaxJobs, "tcd: more than 32 layers");
     const int GQ = p.n_kv > 0 ? p.n_q / p.n_kv : 1;
 #define B200_TCD_CASE(HD_, G_) \

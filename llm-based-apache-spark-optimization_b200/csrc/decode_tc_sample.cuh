@@ -1,0 +1,185 @@
+// decode_tc_sample.cuh -- the sampler as the last phase of the tcgen05 persistent decode kernel (decode_tc.cu).
+//
+// The reference's six ollama.generate call sites pass no `options` (Flask/app.py:102-107,160-166;
+// FastAPI/app.py:85-90,105-111; Model_Evaluation_&_Comparision.py:23-45,114-120), so Ollama's defaults
+// apply: repeat penalty 1.1 over the last 64 tokens -> top-k 40 -> top-p 0.9 -> temperature 0.8 -> draw.
+// Same chain and the same fp32 arithmetic order as sample_kernel (misc.cu) / oracle/sampler.py, so that
+// a sampled decode call is ONE launch like a greedy one:
+//   1. lm_head epilogue has stored this CTA's logit rows (whole 128-row tiles);
+//   2. the CTA that owns the row of a recent token applies the repeat penalty to it in place;
+//   3. every CTA extracts its k best rows (k <= kTSampK) as packed keys, value-descending then
+//      id-ascending, and publishes them; the grid barrier that ends the phase publishes them;
+//   4. every CTA merges the G sorted lists redundantly (k rounds of "largest list head"), so all CTAs
+//      hold the same global top-k without a second barrier, and thread 0 of each runs the short serial
+//      tail (temperature softmax, top-p prefix, draw) bit for bit like the stand-alone sampler.
+// Scratch: the attention merge buffer (s.mrg), idle outside the attention phases.
+#pragma once
+
+constexpr int kTSampK = kTcdSampK; // largest top-k the in-kernel sampler takes (Ollama's default is 40)
+constexpr int kTSampPerThread = 4; // logit rows of the CTA's lm_head share per compute thread (vocab <= 148 * 1536)
+
+__device__ __forceinline__ uint32_t tcd_fkey(float f) {  // order-preserving float -> uint (as misc.cu)
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float tcd_unfkey(uint32_t k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+// larger key = larger logit, then lower token id; 0 = empty
+__device__ __forceinline__ unsigned long long tcd_cand_key(float v, int id) {
+    return ((unsigned long long)tcd_fkey(v) << 32) | (unsigned long long)(0x7fffffffu - (uint32_t)id);
+}
+__device__ __forceinline__ unsigned long long tcd_warp_max64(unsigned long long k) {
+    const uint32_t hi = (uint32_t)(k >> 32);
+    const uint32_t mh = __reduce_max_sync(0xffffffffu, hi);
+    const uint32_t ml = __reduce_max_sync(0xffffffffu, hi == mh ? (uint32_t)k : 0u);
+    return ((unsigned long long)mh << 32) | ml;
+}
+__device__ __forceinline__ uint64_t tcd_mix64(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+
+struct TcdSampScratch {
+    int *hist;                    // [64] the lane's recent tokens
+    unsigned long long *wm;       // [2][kTW] per-warp maxima, double-buffered over the rounds
+    unsigned long long *top;      // [kTSampK] the global top-k keys, best first
+    float *ev;                    // [kTSampK] exp((v_i - v_0) / T)
+};
+__device__ __forceinline__ TcdSampScratch tcd_samp_scratch(const TcdSmem &s) {
+    TcdSampScratch t;
+    t.hist = reinterpret_cast<int *>(s.mrg);
+    t.wm = reinterpret_cast<unsigned long long *>(s.mrg + 64);
+    t.top = t.wm + 2 * kTW;
+    t.ev = reinterpret_cast<float *>(t.top + kTSampK);
+    return t;
+}
+constexpr size_t kTSampScratchBytes = 64 * 4 + 2 * kTW * 8 + kTSampK * 8 + kTSampK * 4;
+
+// One round of "largest key held by any compute thread": every thread passes its candidate, all get the winner.
+__device__ __forceinline__ unsigned long long tcd_block_max64(const TcdSampScratch &t, unsigned long long mine, int round,
+                                                              int warp, int lane) {
+    const unsigned long long wmax = tcd_warp_max64(mine);
+    unsigned long long *buf = t.wm + (round & 1) * kTW;
+    if (lane == 0) buf[warp] = wmax;
+    bar_sync(1, kTC);
+    unsigned long long best = 0;
+#pragma unroll
+    for (int w = 0; w < kTW; ++w) {
+        const unsigned long long o = buf[w];
+        best = o > best ? o : best;
+    }
+    return best;
+}
+
+// Steps 2 and 3: repeat penalty on the rows this CTA owns, then its k best rows -> p.cand[bid][0..k).
+__device__ void tcd_sample_local(const TcdParams &p, const TcdJob &job, const TcdSmem &s, int k, int G, int bid, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const TcdSampScratch t = tcd_samp_scratch(s);
+    const TRange r = tcd_range(job.N, job.K, true, G, bid);
+    const int row0 = (r.g0 / r.nkb) * 128;
+    const int row1 = min((r.g1 / r.nkb) * 128, p.vocab);
+    const int id0 = p.tp_rank * p.vocab;     // global id of this rank's row 0 (vocab-parallel lm_head)
+    bar_sync(1, kTC);                        // the epilogue warps have stored this CTA's logit rows
+    if (p.repeat_penalty != 1.f) {
+        if (tid < 64) t.hist[tid] = __ldcg(p.lane_hist + (size_t)p.lane * 64 + tid);
+        bar_sync(1, kTC);
+        if (tid < 64) {   // each distinct recent token once: logit > 0 ? logit / penalty : logit * penalty
+            const int tk = t.hist[tid];
+            const int row = tk - id0;
+            bool skip = tk < 0 || tk >= p.vocab_global || row < row0 || row >= row1;
+            for (int j = 0; j < tid && !skip; ++j) skip = t.hist[j] == tk;
+            if (!skip) {
+                const float v = __ldcg(p.logits + row);
+                p.logits[row] = v > 0.f ? v / p.repeat_penalty : v * p.repeat_penalty;
+            }
+        }
+        bar_sync(1, kTC);
+    }
+    unsigned long long key[kTSampPerThread];
+#pragma unroll
+    for (int m = 0; m < kTSampPerThread; ++m) {
+        const int n = row0 + tid + m * kTC;
+        key[m] = n < row1 ? tcd_cand_key(__ldcg(p.logits + n), id0 + n) : 0ull;
+    }
+    unsigned long long *out = p.cand + (size_t)bid * kTSampK;
+    for (int round = 0; round < k; ++round) {
+        unsigned long long mx = key[0];
+#pragma unroll
+        for (int m = 1; m < kTSampPerThread; ++m) mx = key[m] > mx ? key[m] : mx;
+        const unsigned long long best = tcd_block_max64(t, mx, round, warp, lane);
+#pragma unroll
+        for (int m = 0; m < kTSampPerThread; ++m) key[m] = key[m] == best ? 0ull : key[m];   // keys are unique (ids are)
+        if (tid == 0) out[round] = best;   // published by thread 0's release in the grid barrier that follows
+    }
+}
+
+// Step 4, after the grid barrier: merge the G lists, then the serial tail.  Returns the token (the same in every CTA).
+__device__ int tcd_sample_merge(const TcdParams &p, const TcdSmem &s, const TcdCtx &c, int k, int G, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const TcdSampScratch t = tcd_samp_scratch(s);
+    const unsigned long long *list = p.cand + (size_t)tid * kTSampK;
+    unsigned long long h0 = 0, h1 = 0, h2 = 0, h3 = 0;
+    int nxt = 0, used = 0;
+    auto refill = [&]() {   // the next four entries of this thread's list (entries past k are stale)
+        const ulonglong2 a = __ldcg(reinterpret_cast<const ulonglong2 *>(list + nxt));
+        const ulonglong2 b = __ldcg(reinterpret_cast<const ulonglong2 *>(list + nxt + 2));
+        h0 = nxt + 0 < k ? a.x : 0ull, h1 = nxt + 1 < k ? a.y : 0ull;
+        h2 = nxt + 2 < k ? b.x : 0ull, h3 = nxt + 3 < k ? b.y : 0ull;
+        nxt += 4, used = 0;
+    };
+    if (tid < G) refill();
+    for (int round = 0; round < k; ++round) {
+        const unsigned long long best = tcd_block_max64(t, h0, round, warp, lane);
+        if (best != 0ull && h0 == best) {   // this thread's list supplied the winner: advance it
+            h0 = h1, h1 = h2, h2 = h3, h3 = 0ull;
+            if (++used == 4 && nxt < k) refill();
+        }
+        if (tid == 0) t.top[round] = best;
+    }
+    bar_sync(1, kTC);
+    int kk = 0;     // candidates that exist (the vocabulary may hold fewer than k rows)
+    for (int i = 0; i < k; ++i) kk += t.top[i] != 0ull ? 1 : 0;
+    const float v0 = tcd_unfkey((uint32_t)(t.top[0] >> 32));
+    int tok = (int)(0x7fffffffu - (uint32_t)t.top[0]);
+    if (p.temperature > 0.f) {
+        const float inv_t = 1.f / p.temperature;
+        if (tid < kk) t.ev[tid] = expf((tcd_unfkey((uint32_t)(t.top[tid] >> 32)) - v0) * inv_t);
+        bar_sync(1, kTC);
+        if (tid == 0) {   // sequential fp32 sums, the order of sample_kernel / oracle/sampler.py
+            float total = 0.f;
+            for (int i = 0; i < kk; ++i) total += t.ev[i];
+            int keep = kk;
+            if (p.top_p < 1.f) {
+                float cum = 0.f;
+                for (int i = 0; i < kk; ++i) {
+                    cum += t.ev[i];
+                    if (cum / total >= p.top_p) {
+                        keep = i + 1;
+                        break;
+                    }
+                }
+            }
+            float mass = 0.f;
+            for (int i = 0; i < keep; ++i) mass += t.ev[i];
+            const uint64_t z = tcd_mix64(p.seed + ((uint64_t)c.pos + 1ULL) * 0x9E3779B97F4A7C15ULL);
+            const float u = (float)(z >> 40) * (1.f / 16777216.f);
+            const float rr = u * mass;
+            float cum = 0.f;
+            int pick = keep - 1;
+            for (int i = 0; i < keep; ++i) {
+                cum += t.ev[i];
+                if (cum > rr) {
+                    pick = i;
+                    break;
+                }
+            }
+            s.misc[56] = (int)(0x7fffffffu - (uint32_t)t.top[pick]);
+        }
+        bar_sync(1, kTC);
+        tok = s.misc[56];
+    }
+    bar_sync(1, kTC);   // the scratch (attention merge buffer) and misc[56] are free again
+    return tok;
+}

@@ -125,6 +125,7 @@ struct b200llm_engine {
     MegaJob *mega_jobs = nullptr;
     unsigned *bar_ctr = nullptr;
     unsigned long long *trace = nullptr;
+    unsigned long long *samp_cand = nullptr;
     // batch / prefill path
     uint16_t *xb = nullptr, *xb2 = nullptr;
     int64_t xb_lo = 0, xb2_lo = 0;   // element offsets of the lo parts inside xb / xb2 (0: single-bf16 activations)
@@ -145,6 +146,7 @@ struct b200llm_engine {
     int ar_slot_floats = 0, ar_max_slices = 0;
     bool ar_ready = false;
     std::vector<b200llm_sampling> samp_host;
+    std::vector<int> lane_pos_host, lane_pages_host;   // host mirror: next position and page-table length of every lane
     b200llm_sampling *lane_samp;
     void *attn_scratch;
     size_t attn_scratch_bytes;
@@ -184,7 +186,7 @@ static int check_cfg(const b200llm_config *c) {
 struct WsLayout {
     size_t h, q, att, act, delta, logits, part_max, part_idx, row_lane, row_pos, row_token, pf_lane, pf_pos,
         pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
-        attn_scratch, mega_jobs, bar_ctr, trace, xb, xb2, qkv_out, gu_out, total;
+        attn_scratch, mega_jobs, bar_ctr, trace, samp_cand, xb, xb2, qkv_out, gu_out, total;
     size_t attn_scratch_bytes;
     size_t xb_lo_off, xb2_lo_off;
     int lm_grid, attn_splits;
@@ -243,6 +245,7 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * (sizeof(MegaJob) > sizeof(TcdJob) ? sizeof(MegaJob) : sizeof(TcdJob)));
     w->bar_ctr = take(256);
     w->trace = take(4096 * 8);
+    w->samp_cand = take((size_t)kNumSMs * kTcdSampK * 8);   // per-CTA candidate keys of the in-kernel sampler
     {   // batch / prefill path (tcgen05 GEMM): bf16 activations and fp32 GEMM outputs
         size_t widest = c->d > (int)(nq_l * c->head_dim) ? c->d : nq_l * c->head_dim;
         if (ffn_l > widest) widest = ffn_l;
@@ -544,12 +547,15 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->mega_jobs = (MegaJob *)(b + w.mega_jobs);
     e->bar_ctr = (unsigned *)(b + w.bar_ctr);
     e->trace = (unsigned long long *)(b + w.trace);
+    e->samp_cand = (unsigned long long *)(b + w.samp_cand);
     const bool hilo = getenv("B200LLM_TC_BF16ACT") == nullptr;  // default: hi + lo operand pairs, ~fp32-accurate activations
     e->xb_lo = hilo ? (int64_t)w.xb_lo_off : 0, e->xb2_lo = hilo ? (int64_t)w.xb2_lo_off : 0;
     e->xb = (uint16_t *)(b + w.xb), e->xb2 = (uint16_t *)(b + w.xb2), e->qkv_out = (float *)(b + w.qkv_out), e->gu_out = (float *)(b + w.gu_out);
     e->mega_ready = false;
     e->tcd_ready = false;
     e->samp_host.assign(e->cfg.max_lanes, b200llm_sampling{0.f, 0, 1.f, 1.f, 0});
+    e->lane_pos_host.assign(e->cfg.max_lanes, 0);
+    e->lane_pages_host.assign(e->cfg.max_lanes, 0);
     // zero everything once: attention tickets must start at zero, lanes at token 0 / pos 0,
     // sampling = greedy, page tables -> page 0
     B200_CUDA_OK(cudaMemsetAsync(b, 0, w.total, e->stream));
@@ -583,12 +589,18 @@ int b200llm_set_page_table(b200llm_engine *e, int32_t lane, const int32_t *pages
                      e->n_pages);
     B200_CUDA_OK(cudaMemcpyAsync(e->page_table + (size_t)lane * e->cfg.max_pages_per_lane, pages, (size_t)n * 4,
                                  cudaMemcpyHostToDevice, e->stream));
+    e->lane_pages_host[lane] = n;
     return B200LLM_OK;
 }
 
 int b200llm_set_sampling(b200llm_engine *e, int32_t lane, const b200llm_sampling *s) {
     B200_REQUIRE(e && e->ws && s && lane >= 0 && lane < e->cfg.max_lanes, "set_sampling: bad arguments");
     B200_REQUIRE(s->temperature >= 0.f && s->repeat_penalty > 0.f, "set_sampling: bad temperature/repeat_penalty");
+    // vocab-parallel lm_head: only the ranks' (max, argmax) partials are exchanged, so a temperature or a repeat
+    // penalty would sample from this rank's vocabulary shard alone
+    B200_REQUIRE(e->cfg.tp_size == 1 || (s->temperature <= 0.f && s->repeat_penalty == 1.f),
+                 "set_sampling: tensor parallel decodes greedily only (temperature 0, repeat_penalty 1); got %g / %g",
+                 (double)s->temperature, (double)s->repeat_penalty);
     B200_CUDA_OK(cudaMemcpyAsync(e->lane_samp + lane, s, sizeof(*s), cudaMemcpyHostToDevice, e->stream));
     e->samp_host[lane] = *s;
     return B200LLM_OK;
@@ -599,6 +611,7 @@ int b200llm_set_lane(b200llm_engine *e, int32_t lane, int32_t next_token, int32_
     B200_REQUIRE(pos >= 0 && pos < e->max_ctx, "set_lane: pos %d out of range", pos);
     B200_CUDA_OK(cudaMemcpyAsync(e->lane_token + lane, &next_token, 4, cudaMemcpyHostToDevice, e->stream));
     B200_CUDA_OK(cudaMemcpyAsync(e->lane_pos + lane, &pos, 4, cudaMemcpyHostToDevice, e->stream));
+    e->lane_pos_host[lane] = pos;
     if (pos == 0)
         B200_CUDA_OK(cudaMemsetAsync(e->lane_hist + (size_t)lane * 64, 0xFF, 64 * 4, e->stream));
     return B200LLM_OK;
@@ -862,7 +875,7 @@ static int tcd_prepare(b200llm_engine *e) {
     return B200LLM_OK;
 }
 
-static int tcd_decode(b200llm_engine *e, int lane, int n_steps) {
+static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sampling &sp, bool in_kernel_sampler) {
     const b200llm_config &c = e->cfg;
     if (!e->tcd_ready) B200_TRY(tcd_prepare(e));
     TcdParams p{};
@@ -892,6 +905,11 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps) {
     p.part_ml = p.part_o + (size_t)e->nq_l * ns * c.head_dim;
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
+    if (in_kernel_sampler) {   // penalty -> top-k -> top-p -> temperature -> draw as the kernel's last phase
+        p.sample = 2, p.cand = e->samp_cand;
+        p.temperature = sp.temperature, p.top_k = sp.top_k, p.top_p = sp.top_p, p.repeat_penalty = sp.repeat_penalty;
+        p.seed = sp.seed;
+    }
     B200_REQUIRE(tcd_plan(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, (e->vocab_l + 127) / 128 * 128, c.n_layers, &p.n_stages, &p.n_bslots),
                  "tcd: geometry does not fit");
     if (const char *ns = getenv("B200LLM_TCD_STAGES")) p.n_stages = atoi(ns) < p.n_stages ? atoi(ns) : p.n_stages;
@@ -1052,6 +1070,10 @@ int b200llm_prefill(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t
     B200_REQUIRE(ids && n >= 1 && lane >= 0 && lane < c.max_lanes, "prefill: bad arguments");
     B200_REQUIRE(pos0 >= 0 && pos0 + n <= e->max_ctx, "prefill: %d tokens at pos %d exceed the lane's %d-token context",
                  n, pos0, e->max_ctx);
+    B200_REQUIRE(pos0 + n <= e->lane_pages_host[lane] * c.page_tokens,
+                 "prefill: %d tokens at pos %d need %d pages, lane %d has %d (b200llm_set_page_table)", n, pos0,
+                 (pos0 + n + c.page_tokens - 1) / c.page_tokens, lane, e->lane_pages_host[lane]);
+    e->lane_pos_host[lane] = pos0 + n;
     std::vector<int32_t> pos(n), lanes(n, lane);
     for (int i = 0; i < n; ++i) pos[i] = pos0 + i;
     B200_CUDA_OK(cudaEventRecord(e->ev[0], e->stream));
@@ -1086,6 +1108,12 @@ int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int
                  kMaxDecodeSteps);
     for (int i = 0; i < n_lanes; ++i)
         B200_REQUIRE(lanes[i] >= 0 && lanes[i] < c.max_lanes, "decode: lane %d out of range", lanes[i]);
+    // every K/V row the call appends must land in a page the caller has put in the lane's table
+    for (int i = 0; i < n_lanes; ++i)
+        B200_REQUIRE(e->lane_pos_host[lanes[i]] + n_steps <= e->lane_pages_host[lanes[i]] * c.page_tokens,
+                     "decode: lane %d at pos %d + %d steps exceeds its %d pages (b200llm_set_page_table)", lanes[i],
+                     e->lane_pos_host[lanes[i]], n_steps, e->lane_pages_host[lanes[i]]);
+    for (int i = 0; i < n_lanes; ++i) e->lane_pos_host[lanes[i]] += n_steps;
     B200_CUDA_OK(cudaMemcpyAsync(e->row_lane, lanes, (size_t)n_lanes * 4, cudaMemcpyHostToDevice, e->stream));
     B200_CUDA_OK(cudaMemsetAsync(e->step_ctr, 0, 4, e->stream));
     PassRows pr{};
@@ -1095,8 +1123,13 @@ int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int
     B200_CUDA_OK(cudaEventRecord(e->ev[2], e->stream));
     const b200llm_sampling &sp0 = e->samp_host[lanes[0]];
     const bool greedy = sp0.temperature <= 0.f && sp0.repeat_penalty == 1.f;
-    if (c.use_megakernel && n_lanes == 1 && greedy && tcd_usable(e)) {
-        B200_TRY(tcd_decode(e, lanes[0], n_steps));
+    // the reference's calls pass no options (Ollama's defaults: temperature 0.8, top-k 40, top-p 0.9, penalty 1.1):
+    // the persistent kernel samples in its last phase, so they are one launch per call like greedy ones
+    const bool in_kernel = !greedy && c.tp_size == 1 && getenv("B200LLM_NO_TCD_SAMPLER") == nullptr &&
+                           tcd_sampler_supported((e->vocab_l + 127) / 128 * 128, c.head_dim, e->nq_l / e->nkv_l,
+                                                 sp0.temperature, sp0.top_k);
+    if (c.use_megakernel && n_lanes == 1 && (greedy || in_kernel) && tcd_usable(e)) {
+        B200_TRY(tcd_decode(e, lanes[0], n_steps, sp0, in_kernel));
         e->timing.kernel_launches = 1;
     } else if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy &&
                mega_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim)) {

@@ -51,7 +51,14 @@ struct TcdParams {
     unsigned *tickets;    // [n_kv]
     int32_t n_splits;
     unsigned *bar_ctr;    // grid barrier counter (zeroed before every launch)
-    int32_t sample;       // 1: greedy argmax + feedback inside the kernel; 0: stop after the logits
+    int32_t sample;       // 1: greedy argmax + feedback inside the kernel; 0: stop after the logits;
+                          // 2: the sampler chain inside the kernel (decode_tc_sample.cuh): repeat penalty over the lane's
+                          //    last 64 tokens -> top-k (1..64) -> top-p -> temperature -> draw; temperature 0 = argmax of
+                          //    the penalised logits
+    float temperature, top_p, repeat_penalty;
+    int32_t top_k;
+    uint64_t seed;
+    unsigned long long *cand;   // [grid][64] per-CTA candidate keys of the sampler (sample == 2)
     int32_t n_stages;     // ring stages of 16 KB (<= 10) and operand blocks of 1 KB (<= 64) in shared memory: tcd_plan()
     int32_t n_bslots;
     int32_t split_all;    // (test hook) k-split the last job too instead of giving whole tiles
@@ -77,5 +84,8 @@ int tcd_job_slots(int N, int K, bool whole_tiles);
 int tcd_stages_for(int head_dim, int gq, int n_jobs, int n_bslots);
 // per-phase check that the activation operand of one CTA fits its 64 k-block buffer
 bool tcd_job_fits(int N, int K, bool whole_tiles);
+// can the in-kernel sampler (sample == 2) take these settings for a lm_head of `vocab_rows` (padded) rows?
+bool tcd_sampler_supported(int vocab_rows, int head_dim, int gq, float temperature, int top_k);
+constexpr int kTcdSampK = 64;   // largest top-k of the in-kernel sampler = candidate keys per CTA in TcdParams::cand
 
 }  // namespace b200

@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import datetime
 import os
+import secrets
 import time
 from typing import Any, Dict, Optional, Sequence
 
@@ -25,7 +26,8 @@ _list = list          # the module exports its own `list()` (upstream name) belo
 __all__ = ["generate", "ResponseError", "GenerateResponse", "Client", "list"]
 
 # Ollama's documented defaults: the reference passes no `options`, so these apply.
-DEFAULT_OPTIONS = {"temperature": 0.8, "top_k": 40, "top_p": 0.9, "repeat_penalty": 1.1, "seed": 0,
+# No default seed: like Ollama, a call without options["seed"] draws a fresh one, so repeated identical prompts differ.
+DEFAULT_OPTIONS = {"temperature": 0.8, "top_k": 40, "top_p": 0.9, "repeat_penalty": 1.1, "seed": None,
                    "num_predict": int(os.environ.get("B200LLM_NUM_PREDICT", "128")), "num_ctx": 4096, "stop": []}
 
 
@@ -103,7 +105,8 @@ def generate(model: str = "", prompt: str = "", suffix: str = "", system: str = 
     ids = ids[-(max_ctx - 1):]                    # Ollama truncates over-long prompts to num_ctx
     num_predict = max(1, min(num_predict, max_ctx - len(ids)))
     sp = SamplingParams(temperature=float(opt["temperature"]), top_k=int(opt["top_k"]), top_p=float(opt["top_p"]),
-                        repeat_penalty=float(opt["repeat_penalty"]), seed=int(opt["seed"]))
+                        repeat_penalty=float(opt["repeat_penalty"]),
+                        seed=int(opt["seed"]) if opt.get("seed") is not None else secrets.randbits(63))
     try:
         toks, tm = m.scheduler.generate_ids(ids, num_predict, sp, stop_ids=m.tokenizer.stop_ids)
     except B200LLMError as e:

@@ -25,9 +25,8 @@ def uniform(seed: int, ctr: int) -> np.float32:
     return np.float32(z >> 40) * np.float32(1.0 / 16777216.0)
 
 
-def sample(logits: np.ndarray, temperature: float, top_k: int, top_p: float, repeat_penalty: float,
-           seed: int, ctr: int, history=None, cap: int = 1024):
-    """Returns (token, candidate ids kept after top-k/top-p, their unnormalised probs)."""
+def apply_penalty(logits: np.ndarray, repeat_penalty: float, history=None) -> np.ndarray:
+    """fp32 copy of the logits with each distinct recent token penalised once: logit > 0 ? logit / p : logit * p."""
     lg = logits.astype(np.float32).copy()
     V = lg.shape[0]
     if repeat_penalty != 1.0 and history is not None:
@@ -39,6 +38,14 @@ def sample(logits: np.ndarray, temperature: float, top_k: int, top_p: float, rep
             seen.add(t)
             pen = np.float32(repeat_penalty)
             lg[t] = lg[t] / pen if lg[t] > 0 else lg[t] * pen
+    return lg
+
+
+def sample(logits: np.ndarray, temperature: float, top_k: int, top_p: float, repeat_penalty: float,
+           seed: int, ctr: int, history=None, cap: int = 1024):
+    """Returns (token, candidate ids kept after top-k/top-p, their unnormalised probs)."""
+    lg = apply_penalty(logits, repeat_penalty, history)
+    V = lg.shape[0]
     if temperature <= 0:
         return int(np.argmax(lg)), None, None           # first maximal index = lowest id
     k = min(top_k if top_k > 0 else cap, cap, V)

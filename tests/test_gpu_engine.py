@@ -345,3 +345,131 @@ def test_shim_replays_reference_call_sites():
     assert ei.value.status_code == 404
     from b200llm import runtime
     runtime.unload_all()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Sampling: the reference's calls pass no `options`, so Ollama's defaults apply (temperature 0.8, top-k 40,
+# top-p 0.9, repeat penalty 1.1).  The persistent kernel runs that chain as its last phase.
+def _oracle_sampled(orc, prompt, n_new, sp):
+    """Oracle forward + oracle/sampler.py, free-running.  Returns (tokens, per step: the penalised logits, slack,
+    margin).  slack = distance of the uniform draw from the nearest edge of the kept candidates' cumulative mass,
+    relative to that mass; margin = top-1 minus top-2 of the penalised logits."""
+    from oracle import sampler
+    st = orc.new_state()
+    seq = [int(t) for t in prompt]
+    logits = orc.forward(torch.as_tensor(seq, dtype=torch.int64), st)
+    toks, pen, slack, margin = [], [], [], []
+    for _ in range(n_new):
+        ctr = len(seq) - 1                       # position of the token that was fed last
+        lg = sampler.apply_penalty(logits.numpy(), sp.repeat_penalty, seq[-64:])
+        tok, ids, probs = sampler.sample(logits.numpy(), sp.temperature, sp.top_k, sp.top_p, sp.repeat_penalty,
+                                         sp.seed, ctr, history=seq[-64:])
+        top2 = np.sort(lg)[-2:]
+        margin.append(float(top2[1] - top2[0]))
+        if probs is not None:
+            mass = float(probs.sum())
+            r = float(sampler.uniform(sp.seed, ctr)) * mass
+            slack.append(float(np.abs(np.cumsum(probs.astype(np.float64)) - r).min() / mass))
+        else:
+            slack.append(1.0)
+        pen.append(lg)
+        toks.append(tok)
+        seq.append(tok)
+        if len(toks) < n_new:
+            logits = orc.forward(torch.tensor([tok], dtype=torch.int64), st)
+    return toks, pen, slack, margin
+
+
+@pytest.mark.parametrize("name,sigma", [("tiny", 0.08), ("small", 0.06)])
+@pytest.mark.parametrize("opts", [dict(temperature=0.8, top_k=40, top_p=0.9, repeat_penalty=1.1, seed=0),      # Ollama defaults
+                                  dict(temperature=1.3, top_k=64, top_p=1.0, repeat_penalty=1.0, seed=77),
+                                  dict(temperature=0.0, top_k=40, top_p=0.9, repeat_penalty=1.5, seed=5),      # penalised argmax
+                                  dict(temperature=0.5, top_k=1, top_p=0.5, repeat_penalty=1.3, seed=9)])
+def test_sampled_decode_in_the_persistent_kernel_matches_oracle(name, sigma, opts):
+    """64 sampled tokens at a fixed seed against the CPU oracle forward + oracle/sampler.py.
+    (1) Along the oracle's token path (b200llm_set_lane forces its token, one launch of the persistent kernel with
+        the sampler as its last phase per step): the penalised logits agree within TIGHT_TOL and every draw is the
+        oracle's, except where the MEASURED logit deviation can move the draw across a boundary (the cumulative
+        masses move by at most exp(2 dev / T) - 1; for the penalised argmax, a top-2 margin below 2 dev): those
+        are counted and printed, and must be few.
+    (2) Free-running, all 63 steps in ONE launch: the oracle's tokens up to the first such boundary case, then the
+        token (1) drew there; bit-identical to 63 launches of one step.
+    (3) The per-phase kernels + stand-alone sample_kernel (B200LLM_NO_TCD_SAMPLER) draw the same tokens."""
+    from b200llm import SamplingParams
+    geo = lo.GEOMETRIES[name]
+    sd = lo.make_weights(geo, 0xB200, sigma=sigma)
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    prompt = wg.gen_tokens(90, 31, geo.vocab)
+    sp = SamplingParams(**opts)
+    want, pen, slack, margin = _oracle_sampled(orc, prompt, 64, sp)
+    assert len(set(want)) > 4                                            # the chain really samples
+    eng = _engine(name, sd, max_lanes=2, max_ctx=256, max_rows=16, use_megakernel=True)
+    # (1) teacher-forced
+    lane = eng.open_lane()
+    eng.set_sampling(lane, sp)
+    eng.prefill(lane, prompt)
+    forced, cases, worst = [], [], 0.0
+    for s in range(64):
+        if s == 0:
+            tok = eng.read_lane(lane)[0]
+        else:
+            eng.set_lane(lane, want[s - 1], len(prompt) + s - 1)
+            tok = int(eng.decode([lane], 1)[0, 0])
+            assert eng.timing().kernel_launches == 1, "sampled decode must be one launch of the persistent kernel"
+        got_lg = eng.logits(0)                                           # the kernel penalises the logits in place
+        dev = float(np.abs(got_lg - pen[s]).max())
+        worst = max(worst, dev / float(np.abs(pen[s]).max()))
+        forced.append(tok)
+        if tok != want[s]:
+            explained = (slack[s] < np.expm1(2 * dev / sp.temperature) + 1e-6) if sp.temperature > 0 else (margin[s] <= 2 * dev)
+            assert explained, (f"step {s}: drew {tok}, oracle {want[s]}; draw slack {slack[s]:.2e}, top-2 margin "
+                               f"{margin[s]:.2e}, logit deviation {dev:.2e}")
+            cases.append(s)
+    eng.close_lane(lane)
+    print(f"{name} {opts}: {64 - len(cases)}/64 draws identical to oracle forward + oracle/sampler.py along the oracle's "
+          f"path; {len(cases)} boundary case(s) at steps {cases}; penalised logits within {worst:.1e} of the oracle's")
+    assert worst <= TIGHT_TOL and len(cases) <= 4
+    # (2) free-running, one launch
+    toks, tm = eng.generate_ids(prompt, 64, sp)
+    assert tm.kernel_launches == 1
+    n_ok = cases[0] if cases else 64
+    assert toks[:n_ok] == want[:n_ok] and (n_ok == 64 or toks[n_ok] == forced[n_ok])
+    lane = eng.open_lane()
+    eng.set_sampling(lane, sp)
+    eng.prefill(lane, prompt)
+    single = [eng.read_lane(lane)[0]] + [int(eng.decode([lane], 1)[0, 0]) for _ in range(63)]
+    eng.close_lane(lane)
+    assert single == toks
+    eng.close()
+    # (3) the multi-kernel path (CUDA graph + stand-alone sample_kernel) draws the same tokens
+    os.environ["B200LLM_NO_TCD_SAMPLER"] = "1"
+    try:
+        eng2 = _engine(name, sd, max_lanes=2, max_ctx=256, max_rows=16, use_megakernel=True)
+        toks2, tm2 = eng2.generate_ids(prompt, 64, sp)
+        eng2.close()
+    finally:
+        del os.environ["B200LLM_NO_TCD_SAMPLER"]
+    assert tm2.kernel_launches > 1
+    assert toks2[:n_ok] == toks[:n_ok]
+
+
+def test_sampled_decode_full_size_one_launch(golden_dir):
+    """Llama-3.2-3B with Ollama's default options: one launch per decode call, in-kernel sampler == stand-alone
+    sample_kernel on the same engine logits for 48 tokens (two roundings of the same chain must agree)."""
+    from b200llm import SamplingParams
+    g = np.load(os.path.join(golden_dir, "llama3.2.npz"))
+    sp = SamplingParams(temperature=0.8, top_k=40, top_p=0.9, repeat_penalty=1.1, seed=20250211)
+    eng = _engine("llama3.2", None, seed=int(g["seed"]), sigma=float(g["sigma"]), max_lanes=1,
+                  max_ctx=len(g["prompt"]) + 128, max_rows=64, use_megakernel=True)
+    toks, tm = eng.generate_ids(g["prompt"], 48, sp)
+    assert tm.kernel_launches == 1
+    os.environ["B200LLM_NO_TCD_SAMPLER"] = "1"
+    try:
+        ref, tm2 = eng.generate_ids(g["prompt"], 48, sp)
+    finally:
+        del os.environ["B200LLM_NO_TCD_SAMPLER"]
+    assert tm2.kernel_launches > 1
+    same = next((i for i, (a, b) in enumerate(zip(toks, ref)) if a != b), len(ref))
+    print(f"3B sampled: {same}/48 tokens identical between the in-kernel sampler and per-phase kernels + sample_kernel")
+    assert same >= 24 and len(set(toks)) > 8     # the two paths' logits differ by ~1e-4: a late boundary flip is possible
+    eng.close()

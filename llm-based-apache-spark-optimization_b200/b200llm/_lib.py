@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200llm.so")
+# B200LLM_LIB: another build of the same sources (the trace build of scripts/tcd_trace.py); there is no non-CUDA substitute
+LIB_PATH = os.environ.get("B200LLM_LIB") or os.path.join(_HERE, "libb200llm.so")
 
 ABI_VERSION = 1
 OK, EINVAL, ENODEV, ECUDA, ESTATE, ENCCL, ENOMEM = 0, -1, -2, -3, -4, -5, -6

@@ -42,11 +42,26 @@ constexpr int kTIssuers = 1;           // MMA issuer threads (one warp each): st
                                        // Two issuers are ~3 % faster (a prefilled ring drains at 39 instead of 64 clk per MMA) but
                                        // rare launch failures / hangs appeared with them, so one is the default
 constexpr int kTThreads = kTC + 32 * kTIssuers + 32;   // + MMA issuer warps + producer warp
+static_assert(kTIssuers == 1, "the TMEM overflow queue below is kept by ONE issuer thread");
 constexpr int kTMaxStages = 10;        // ring stages: as many as fit beside the operand blocks (TcdParams::n_stages)
 constexpr int kTStageBytes = 16384;   // [128 rows x 64 k] bf16
 constexpr int kTBSlots = 64;          // most activation operand blocks ([8 x 64 k] bf16 = 1 KB each) a CTA may need (TcdParams::n_bslots)
 constexpr int kTAcc = 8;              // accumulators in flight (16 TMEM columns apart)
 constexpr int kTAccCols = 16;
+// Overflow of the weight ring, in TENSOR MEMORY.  While the MMA issuer waits for a phase's activation operand (grid
+// barrier + activation re-load, or the whole attention phase) the shared-memory ring is full and the HBM stream of
+// this SM stalls.  Instead of idling, the issuer moves landed stages out of shared memory with tcgen05.cp
+// (4 x 128x256b = the [128 x 64] bf16 tile as 128 lanes x 32 columns, the layout tcgen05.mma takes an A operand
+// in from TMEM) and hands the shared-memory stage back to the producer, so the stream keeps running: 512 columns -
+// 128 of accumulators = 12 more stages of 16 KB, ~4.3 us of this SM's share of the stream.  Moved stages are
+// multiplied from TMEM, in order, before the ones still in shared memory (scripts/ubench_tmem_a.cu checks copy + MMA
+// bit for bit; a copy costs as many tcgen05 issue slots as the MMAs of its stage, so stages are only moved while
+// the issuer has nothing to multiply).
+constexpr int kTSlots = 12;           // TMEM weight slots
+constexpr int kTSlotCols = 32;
+constexpr int kTSlotCol0 = kTAcc * kTAccCols;
+constexpr int kTTmemCols = 512;
+static_assert(kTSlotCol0 + kTSlots * kTSlotCols <= kTTmemCols, "tensor memory over-committed");
 constexpr int kTPT = 16;              // tokens per KV page
 constexpr int kTMaxPtab = 448;        // page-table entries kept in shared memory
 constexpr int kTMaxJobs = 4 * 32 + 1;
@@ -54,7 +69,7 @@ constexpr int kTMaxJobs = 4 * 32 + 1;
 struct TcdSmem {
     uint8_t *ring, *bop;
     float *mrg;            // attention merge buffer [kTW][GQ][HD + 2]
-    uint64_t *full, *empty, *acc_full, *acc_empty;
+    uint64_t *full, *empty, *acc_full, *acc_empty, *tempty, *xrdy;
     uint32_t *tmem_slot;
     float *red;
     int *misc;
@@ -76,7 +91,9 @@ __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int 
     s.empty = s.full + kTMaxStages;
     s.acc_full = s.empty + kTMaxStages;
     s.acc_empty = s.acc_full + kTAcc;
-    s.tmem_slot = reinterpret_cast<uint32_t *>(s.acc_empty + kTAcc);
+    s.tempty = s.acc_empty + kTAcc;
+    s.xrdy = s.tempty + kTSlots;
+    s.tmem_slot = reinterpret_cast<uint32_t *>(s.xrdy + 2);
     s.red = reinterpret_cast<float *>(s.tmem_slot + 4);
     s.misc = reinterpret_cast<int *>(s.red + 64);
     s.rope = reinterpret_cast<float *>(s.misc + 64);
@@ -89,7 +106,7 @@ __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int 
 }
 
 static size_t tcd_fixed_smem_bytes(int hd, int gq, int n_jobs) {  // everything but the ring and the operand blocks
-    return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + (2 * kTMaxStages + 2 * kTAcc) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 +
+    return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + (2 * kTMaxStages + 2 * kTAcc + kTSlots + 2) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 +
            kTMaxPtab * 4 + (size_t)n_jobs * sizeof(TcdJob) + 2 * 1024;  // slack: 1024-byte alignment of the base and of the operand blocks
 }
 static size_t tcd_smem_bytes(int hd, int gq, int n_jobs, int n_stages, int n_bslots) {
@@ -177,22 +194,23 @@ __device__ __forceinline__ unsigned tcd_poll(unsigned *ctr) {
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
     return v;
 }
-__device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, int tid) {
+__device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, int tid, volatile unsigned *done, int n_poll) {
     bar_sync(1, kTC);
-    if (tid == 0) {
-        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
-        // two polls in flight, half a round trip apart: the last arrival is seen ~0.2 us sooner than
-        // with one dependent load after the other.  Relaxed polls and ONE fence at the end: an
-        // acquire load per poll costs an L1 invalidate (CCTL.IVALL) per iteration
-        unsigned a = tcd_poll(ctr);
-        __nanosleep(300);   // (0 / 100 / 300 ns measure the same, 600 ns costs 1 %)
+    if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+    // Lane 0 of the first n_poll warps polls, each with one relaxed load in flight, started a fraction of a round trip
+    // apart: the last arrival is seen by whichever poll reaches L2 next (~RTT / n_poll later instead of ~RTT / 2 with
+    // one poller); the finder fences once (an acquire load per poll would cost an L1 invalidate, CCTL.IVALL, per
+    // iteration) and tells the others through shared memory.
+    if ((tid & 31) == 0 && (tid >> 5) < n_poll) {
+        if (tid) __nanosleep((unsigned)(tid >> 5) * 1200u / (unsigned)n_poll);
         for (;;) {
-            const unsigned b = tcd_poll(ctr);
-            if (a >= target) break;
-            a = tcd_poll(ctr);
-            if (b >= target) break;
+            if (*done >= target) break;
+            if (tcd_poll(ctr) >= target) {
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                *done = target;
+                break;
+            }
         }
-        asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     bar_sync(1, kTC);
 }
@@ -205,12 +223,26 @@ __device__ void tcd_producer(const TcdParams &p, const TcdSmem &s, int G, int bi
     int slot = 0;
     uint32_t par = 0;
     bool first_round = true;
+    // in-flight limit: copy i is issued only once copy i - n_inflight has landed.  A full ring of copies in flight on
+    // every SM is 3x what the HBM pipe needs (Little: ~6.4 MB at ~1 us) and queues in front of the latency-bound
+    // traffic of the phase boundaries (barrier polls, activation re-loads)
+    const int lim = (p.n_inflight > 0 && p.n_inflight < p.n_stages) ? p.n_inflight : 0;
+    int wslot = 0, ahead = 0;
+    uint32_t wpar = 0;
     for (int step = 0; step < p.n_steps; ++step) {
         for (int j = 0; j < n_jobs; ++j) {
             const TcdJob &job = s.jobs[j];
             const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
             const uint8_t *src = reinterpret_cast<const uint8_t *>(job.w) + (size_t)r.g0 * kTStageBytes;
             for (int g = r.g0; g < r.g1; ++g, src += kTStageBytes) {
+                if (lim) {
+                    if (ahead == lim) {
+                        mbar_wait(&s.full[wslot], wpar);
+                        if (++wslot == p.n_stages) wslot = 0, wpar ^= 1;
+                    } else {
+                        ++ahead;
+                    }
+                }
                 if (!first_round) mbar_wait(&s.empty[slot], par ^ 1);
                 mbar_expect_tx(&s.full[slot], kTStageBytes);
                 tma_load_1d_hint(s.ring + (size_t)slot * kTStageBytes, src, kTStageBytes, &s.full[slot], pol);
@@ -231,70 +263,237 @@ __device__ __forceinline__ uint64_t tcd_desc(uint32_t smem_addr, uint32_t sbo) {
     d |= (uint64_t)2 << 61;
     return d;
 }
+// one lane of a converged warp
+__device__ __forceinline__ bool tcd_elect() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.b32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tcd_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
 }
 
-// Issuer `me` (0 or 1) takes every second stage of the CTA's range.  One thread sustains a
-// tcgen05.mma every ~64 clk, two threads together one every ~39 clk (scripts/ubench_umma.cu), which
-// is what drains a prefetched ring quickly after a barrier.  The issuers accumulate into separate
-// column groups of the segment's accumulator (columns 0..7 and 8..15); the epilogue adds them.
-__device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem, int me) {
+// The MMA issuer warp.  A = a weight tile (in its ring stage, or in a TMEM slot if it was moved there while the
+// issuer waited), B = the activation operand block in shared memory, D[128, 8] fp32 in TMEM.
+// The WHOLE warp walks the schedule, converged, and one elected lane issues the tcgen05 instructions: every operand
+// (descriptors, TMEM addresses, barrier addresses) is then the same in all lanes and derives from kernel parameters
+// only, so ptxas keeps it in uniform registers.  Run by a single lane of a diverged warp, the same code cost
+// ~145 clk per MMA (each UTCHMMA sat in an ELECT / 5 x R2UR.BROADCAST / BRA.U.ANY loop over "possibly different"
+// lane values): 0.3 us per 16 KB stage, as slow as this SM's share of the HBM stream delivers them, so nothing the
+// ring had prefetched during a barrier was ever caught up on (profiles/tcd_trace_r2a.txt).
+// The loop carries no integer division.
+struct TcdIssuer {
+    int slot;          // ring stage that leaves shared memory next (moved or multiplied), and the parity of its use
+    uint32_t par;
+    int t_head, t_n;   // TMEM queue: oldest filled slot, number of filled slots
+    int t_tail;        // next TMEM slot to fill (slots are filled and multiplied in ring order)
+    uint32_t t_use;    // completed laps of t_tail = earlier fills of slot t_tail (phase of its tempty barrier)
+};
+
+// shape of phase j's matrix from the kernel parameters (the descriptors in shared memory hold the same numbers, but a
+// value that went through a load is not provably warp-uniform)
+__device__ __forceinline__ void tcd_job_shape(const TcdParams &p, int j, int n_jobs, int &N, int &K) {
+    const int q = j & 3;
+    if (j == n_jobs - 1) {
+        N = (p.vocab + 127) / 128 * 128, K = p.d;
+    } else if (q == 0) {
+        N = (p.n_q + 2 * p.n_kv) * p.head_dim, K = p.d;
+    } else if (q == 1) {
+        N = p.d, K = p.n_q * p.head_dim;
+    } else if (q == 2) {
+        N = 2 * p.ffn, K = p.d;
+    } else {
+        N = p.d, K = p.ffn;
+    }
+}
+
+// The four K = 16 MMAs of one [128 x 64] stage.  Descriptors come as (low, high) words: stepping 32 bytes along K only
+// touches the 14-bit address field of the low word (tiles are 1024-byte aligned), so the step is a 32-bit immediate add.
+__device__ __forceinline__ void tcd_mma4_ss(uint32_t d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                            uint32_t first) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b64 ra, rb;\n\tsetp.eq.b32 p, %6, 0;\n\t"
+            "mov.b64 ra, {%1, %2};\n\tmov.b64 rb, {%3, %4};\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], ra, rb, %5, p;\n\t}" ::"r"(d),
+            "r"(a_lo + 2 * k), "r"(a_hi), "r"(b_lo + 2 * k), "r"(b_hi), "r"(idesc), "r"(k == 0 ? first : 0u)
+            : "memory");
+}
+__device__ __forceinline__ void tcd_mma4_ts(uint32_t d, uint32_t ta, uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t first) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b64 rb;\n\tsetp.eq.b32 p, %5, 0;\n\t"
+            "mov.b64 rb, {%2, %3};\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], rb, %4, p;\n\t}" ::"r"(d),
+            "r"(ta + 8 * k), "r"(b_lo + 2 * k), "r"(b_hi), "r"(idesc), "r"(k == 0 ? first : 0u)
+            : "memory");
+}
+
+__device__ __forceinline__ void tcd_cp_stage(uint32_t ta, uint64_t adesc) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(ta + 8 * k), "l"(adesc + (uint64_t)(2 * k)) : "memory");
+}
+
+// Move the oldest landed ring stage into a free TMEM slot, if there is one of each.  Never blocks.  (Converged warp.)
+__device__ __forceinline__ bool tcd_try_move(const TcdParams &p, const TcdSmem &s, TcdIssuer &q, uint32_t tmem, uint32_t ring_a,
+                                             int &left) {
+    if (left == 0 || q.t_n >= p.tmem_slots) return false;
+    if (!mbar_test_wait(&s.full[q.slot], q.par)) return false;
+    // the MMAs that read this slot's previous tile were issued by this warp before (tcgen05 ops run in issue order);
+    // the barrier check keeps the re-use safe whatever the pipeline does
+    if (q.t_use > 0 && !mbar_test_wait(&s.tempty[q.t_tail], (q.t_use - 1) & 1)) return false;
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    if (tcd_elect()) {
+        tcd_cp_stage(tmem + kTSlotCol0 + (uint32_t)q.t_tail * kTSlotCols, tcd_desc(ring_a + (uint32_t)q.slot * kTStageBytes, 1024));
+        tcd_commit(&s.empty[q.slot]);   // the ring stage goes back to the producer once the copies have read it
+    }
+    __syncwarp();
+    if (++q.slot == p.n_stages) q.slot = 0, q.par ^= 1;
+    if (++q.t_tail == kTSlots) q.t_tail = 0, ++q.t_use;
+    ++q.t_n;
+    --left;
+    return true;
+}
+
+#ifdef B200LLM_TCD_TRACE
+#define TCD_ISTAMP(tag_)                                                                                          \
+    do {                                                                                                          \
+        if (tr_on && lane == 0 && tr_n < 500) {                                                                   \
+            unsigned long long t_;                                                                                \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                \
+            p.trace[1536 + tr_n++] = (t_ & 0xFFFFFFFFFFFFull) | ((unsigned long long)(tag_) << 48);               \
+        }                                                                                                         \
+    } while (0)
+#ifdef B200LLM_TCD_TRACE_DEEP   // per-stage cycle accounting and stamps: slows the issuer loop itself
+#define TCD_ICLK(var_) const long long var_ = clock64()
+#define TCD_IACC(i_, v_) tr_acc[i_] += (v_)
+#define TCD_ISTAMP_STAGE(tag_) TCD_ISTAMP(tag_)
+#else
+#define TCD_ICLK(var_) do { } while (0)
+#define TCD_IACC(i_, v_) do { } while (0)
+#define TCD_ISTAMP_STAGE(tag_) do { } while (0)
+#endif
+#else
+#define TCD_ISTAMP(tag_) do { } while (0)
+#define TCD_ISTAMP_STAGE(tag_) do { } while (0)
+#define TCD_ICLK(var_) do { } while (0)
+#define TCD_IACC(i_, v_) do { } while (0)
+#endif
+
+__device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem_in, int me) {
+    (void)me, (void)lane;
+#ifdef B200LLM_TCD_TRACE
+    bool tr_on = false;
+    int tr_n = 0;
+    long long tr_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long tr_t0 = clock64();
+#endif
     const int n_jobs = 4 * p.n_layers + 1;
     // D fp32, A/B bf16, both K-major, M = 128, N = 8
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((8u >> 3) << 17) | ((128u >> 4) << 24);
+    const uint32_t tmem = __shfl_sync(0xffffffffu, tmem_in, 0);   // (read from shared memory: make it warp-uniform)
     const uint32_t ring_a = smem_u32(s.ring), bop_a = smem_u32(s.bop);
+    // descriptor words (tcd_desc): address >> 4 | 1 << 16 below; 8-row group stride >> 4, version 1, 128-byte swizzle above
+    const uint32_t a_lo0 = ((ring_a & 0x3FFFFu) >> 4) | (1u << 16), a_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    const uint32_t b_lo0 = ((bop_a & 0x3FFFFu) >> 4) | (1u << 16), b_hi = (1u << 14) | (2u << 29);
     uint32_t as = 0;
-    int slot = 0;      // ring position and the parity of its current use, in lock-step with the producer
-    uint32_t par = 0;
+    TcdIssuer q;
+    q.slot = 0, q.par = 0, q.t_head = 0, q.t_n = 0, q.t_use = 0, q.t_tail = 0;
+    // stages the producer will still deliver (the mover must not wait for a copy that is never issued)
+    int left = 0;
+    for (int j = 0; j < n_jobs; ++j) {
+        int N, K;
+        tcd_job_shape(p, j, n_jobs, N, K);
+        const TRange r = tcd_range(N, K, tcd_whole(p, j, n_jobs), G, bid);
+        left += r.g1 - r.g0;
+    }
+    left *= p.n_steps;
+    const bool use_tmem = p.tmem_slots > 0;
+    uint32_t xph = 0;
     for (int step = 0; step < p.n_steps; ++step) {
         for (int j = 0; j < n_jobs; ++j) {
-            const TcdJob &job = s.jobs[j];
-            const TRange r = tcd_range(job.N, job.K, tcd_whole(p, j, n_jobs), G, bid);
-            bar_sync(2, kTC + 32 * kTIssuers);  // the activation operand of this phase is in shared memory
+            int N, K;
+            tcd_job_shape(p, j, n_jobs, N, K);
+            const TRange r = tcd_range(N, K, tcd_whole(p, j, n_jobs), G, bid);
+#ifdef B200LLM_TCD_TRACE
+            tr_on = p.trace != nullptr && bid == 0 && step == p.trace_step && j >= 4 && j < 8;
+#endif
+            TCD_ICLK(c0);
+            // wait for the activation operand of this phase; meanwhile keep this SM's weight stream moving
+            if (use_tmem) {
+                while (!mbar_test_wait(s.xrdy, xph & 1))
+                    if (!tcd_try_move(p, s, q, tmem, ring_a, left) && p.poll_ns > 0) __nanosleep((unsigned)p.poll_ns);
+            } else {
+                mbar_wait(s.xrdy, xph & 1);
+            }
+            ++xph;
+            __syncwarp();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            TCD_ICLK(c1);
+            TCD_IACC(1, c1 - c0);
+            TCD_ISTAMP(10);
             // operand slot of the stage's k block: (kb - kb_start) mod nkb = stages since the range began, mod nkb
             // (kept incrementally: an integer division per stage would cost the issuer ~40 clk)
             int bslot = 0;
-            for (int g = r.g0, t = r.g0 / r.nkb; lane == 0 && g < r.g1; ++t) {
+            for (int g = r.g0, t = r.g0 / r.nkb; g < r.g1; ++t) {
                 const int seg_end = min(r.g1, (t + 1) * r.nkb);
                 const uint32_t aslot = as % kTAcc;
+                TCD_ICLK(c2);
                 if (as >= kTAcc) {
                     mbar_wait(&s.acc_empty[aslot], ((as / kTAcc) - 1) & 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 }
-                const uint32_t d_addr = tmem + aslot * kTAccCols + me * 8;
-                bool first = true;
-                for (int u = 0; g < seg_end; ++g, ++u, bslot = (bslot + 1 == r.nkb ? 0 : bslot + 1),
-                         par ^= (slot + 1 == p.n_stages), slot = (slot + 1 == p.n_stages ? 0 : slot + 1)) {
-                    if ((u % kTIssuers) != me) continue;
-                    mbar_wait(&s.full[slot], par);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint64_t adesc = tcd_desc(ring_a + (uint32_t)slot * kTStageBytes, 1024);
-                    const uint64_t bdesc = tcd_desc(bop_a + (uint32_t)bslot * 1024, 0);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint32_t accum = (first && k == 0) ? 0u : 1u;
-                        asm volatile(
-                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_addr),
-                            "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc + (uint64_t)(2 * k)), "r"(idesc), "r"(accum)
-                            : "memory");
+                TCD_ICLK(c3);
+                TCD_IACC(3, c3 - c2);
+                const uint32_t d_addr = tmem + aslot * kTAccCols;
+                uint32_t first = 1u;
+                for (; g < seg_end; ++g, bslot = (bslot + 1 == r.nkb ? 0 : bslot + 1)) {
+                    const uint32_t b_lo = b_lo0 + (uint32_t)bslot * 64u;
+                    if (q.t_n > 0) {   // the oldest stage was moved to TMEM (its copies precede these MMAs in issue order)
+                        if (tcd_elect()) {
+                            tcd_mma4_ts(d_addr, tmem + kTSlotCol0 + (uint32_t)q.t_head * kTSlotCols, b_lo, b_hi, idesc, first);
+                            tcd_commit(&s.tempty[q.t_head]);   // the slot may be refilled once these MMAs have read it
+                        }
+                        if (++q.t_head == kTSlots) q.t_head = 0;
+                        --q.t_n;
+                    } else {
+                        TCD_ICLK(c4);
+                        mbar_wait(&s.full[q.slot], q.par);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        TCD_ICLK(c5);
+                        TCD_IACC(0, c5 - c4);
+                        TCD_IACC(4, 1);
+                        TCD_ISTAMP_STAGE(11);
+                        if (tcd_elect()) {
+                            tcd_mma4_ss(d_addr, a_lo0 + (uint32_t)q.slot * 1024u, a_hi, b_lo, b_hi, idesc, first);
+                            tcd_commit(&s.empty[q.slot]);  // frees the ring stage once the MMAs above have read it
+                        }
+                        if (++q.slot == p.n_stages) q.slot = 0, q.par ^= 1;
+                        --left;
                     }
-                    first = false;
-                    tcd_commit(&s.empty[slot]);  // frees the ring stage once the MMAs above have read it
+                    first = 0u;
                 }
-                if (first) {
-                    mbar_arrive(&s.acc_full[aslot]);  // a one-stage segment: nothing for this issuer
-                } else {
-                    tcd_commit(&s.acc_full[aslot]);
-                }
+                if (tcd_elect()) tcd_commit(&s.acc_full[aslot]);
+                __syncwarp();
+                TCD_ISTAMP_STAGE(13);
                 ++as;
             }
-            __syncwarp();
+            TCD_ISTAMP(12);
         }
     }
+#ifdef B200LLM_TCD_TRACE
+    if (p.trace != nullptr && bid == 0 && lane == 0) {
+#ifdef B200LLM_TCD_TRACE_DEEP
+        tr_acc[6] = clock64() - tr_t0;
+        tr_acc[2] = tr_acc[6] - tr_acc[0] - tr_acc[1] - tr_acc[3];
+        for (int i = 0; i < 7; ++i) p.trace[4000 + i] = (unsigned long long)tr_acc[i];
+#endif
+    }
+#endif
 }
 
 // Kept small: what lives across the whole step competes with the attention phase for the 128 registers, and a

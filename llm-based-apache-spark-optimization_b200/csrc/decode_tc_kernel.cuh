@@ -20,11 +20,13 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
             mbar_init(&s.acc_full[i], kTIssuers);
             mbar_init(&s.acc_empty[i], 4);
         }
+        for (int i = 0; i < kTSlots; ++i) mbar_init(&s.tempty[i], 1);
+        mbar_init(s.xrdy, kTW);
         mbar_fence_init();
     }
-    if (warp == kTW) {  // TMEM: kTAcc accumulators of kTAccCols columns
+    if (warp == kTW) {  // TMEM, all of it: kTAcc accumulators of kTAccCols columns, then kTSlots weight slots of kTSlotCols
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s.tmem_slot)),
-                     "r"((uint32_t)(kTAcc * kTAccCols))
+                     "r"((uint32_t)kTTmemCols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -53,6 +55,8 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
         c.tok = __ldcg(p.lane_token + p.lane);
         c.pos = __ldcg(p.lane_pos + p.lane);
         unsigned bar_no = 0;
+        volatile unsigned *bar_done = reinterpret_cast<volatile unsigned *>(s.misc + 60);   // last barrier seen complete
+        if (tid == 0) *bar_done = 0u;
         // one weight-streaming phase, compute-warp side
         auto phase = [&](int j) {
             const TcdJob &job = s.jobs[j];
@@ -100,7 +104,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 tcd_attn_prefetch<HD>(p, qkv_job, s, c, G, bid, tid);
                 phase(4 * l);      // rmsnorm + qkv (raw sums)
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 tcd_attn_phase<HD, GQ>(p, qkv_job, s, c, G, bid, tid);  // rope + kv append + attention
                 step = reinterpret_cast<volatile int *>(s.misc)[57];   // written before the barrier above
@@ -108,27 +112,27 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 bar_no = (unsigned)reinterpret_cast<volatile int *>(s.misc)[59];
                 tcd_trace(p, c.ti, bid, tid, TT_ATT_DONE);
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 phase(4 * l + 1);  // o_proj + residual
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 if (p.tp_size > 1) {   // o_proj is row-parallel: h += sum over ranks of the partial sums
                     tcd_allreduce_phase(p, s, G, bid, tid);
-                    tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                    tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 }
                 phase(4 * l + 2);  // rmsnorm + gate/up (raw sums)
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 phase(4 * l + 3);  // swiglu + down + residual
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 if (p.tp_size > 1) {   // down_proj is row-parallel too
                     tcd_allreduce_phase(p, s, G, bid, tid);
-                    tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                    tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 }
             }
             // ---- final norm + lm_head: logits, per-CTA (max, lowest argmax) ----
@@ -138,7 +142,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 // ---- sampler chain in the kernel: penalty + per-CTA top-k, barrier, redundant merge + draw ----
                 const int k = p.temperature > 0.f ? p.top_k : 1;
                 tcd_sample_local(p, s.jobs[n_jobs - 1], s, k, G, bid, tid);
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 c.tok = tcd_sample_merge(p, s, c, k, G, tid);
                 c.pos += 1;
@@ -168,7 +172,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                     p.part_idx[bid] = mi;
                 }
             }
-            tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid);
+            tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
             tcd_trace(p, c.ti, bid, tid, TT_BAR);
             if (!p.sample) break;  // caller samples from the logits (temperature > 0)
             // ---- greedy sampling: every CTA reduces the G partials redundantly (no extra barrier) ----
@@ -216,7 +220,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == kTW)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)(kTAcc * kTAccCols))
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kTTmemCols)
                      : "memory");
 }
 

@@ -136,7 +136,9 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
         if (lane == 0) s.red[warp] = ss;
     }
     tcd_trace(p, c.ti, bid, tid, TT_XCONV);
-    bar_sync(2, kTC + 32 * kTIssuers);  // with the MMA issuer warps: operand blocks (and the norm partials) are complete
+    __syncwarp();
+    if (lane == 0) mbar_arrive(s.xrdy);   // to the MMA issuer (which polls, moving weight stages meanwhile): this warp's operand blocks are complete
+    bar_sync(1, kTC);                     // the norm partials of all warps
     float sc = 1.f;
     if (gain != nullptr) {
         float tot = 0.f;

@@ -913,6 +913,13 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
     B200_REQUIRE(tcd_plan(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, (e->vocab_l + 127) / 128 * 128, c.n_layers, &p.n_stages, &p.n_bslots),
                  "tcd: geometry does not fit");
     if (const char *ns = getenv("B200LLM_TCD_STAGES")) p.n_stages = atoi(ns) < p.n_stages ? atoi(ns) : p.n_stages;
+    if (const char *nf = getenv("B200LLM_TCD_INFLIGHT")) p.n_inflight = atoi(nf);
+    p.tmem_slots = 0;   // measured: parking stages in tensor memory during the gaps loses 1-3 % (profiles/tcd_tmem_overflow_r2.txt)
+    if (const char *ts = getenv("B200LLM_TCD_TMEM")) p.tmem_slots = atoi(ts) < 0 ? 0 : (atoi(ts) > 12 ? 12 : atoi(ts));
+    p.poll_ns = 100;
+    if (const char *pn = getenv("B200LLM_TCD_POLL_NS")) p.poll_ns = atoi(pn);
+    p.n_poll = 1;
+    if (const char *np = getenv("B200LLM_TCD_POLL")) p.n_poll = atoi(np) < 1 ? 1 : (atoi(np) > 12 ? 12 : atoi(np));
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     // the qkv and gate/up phases ADD into these rows; later layers find them cleared by the o_proj phase
     B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim * 4, e->stream));
@@ -1267,6 +1274,7 @@ int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, 
     p.gen_out = reinterpret_cast<int32_t *>(scr + 3712), p.n_steps = 1, p.n_splits = 1;
     p.bar_ctr = reinterpret_cast<unsigned *>(scr + 3776);
     p.sample = 0, p.split_all = k_split ? 1 : 0;
+    p.n_poll = 1, p.tmem_slots = 0;
     p.n_bslots = tcd_job_slots(N, K, !k_split);
     p.n_stages = tcd_stages_for(128, 1, 1, p.n_bslots);
     rc = tcd_decode_launch(p, st);

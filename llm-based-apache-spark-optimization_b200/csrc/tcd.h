@@ -61,6 +61,10 @@ struct TcdParams {
     unsigned long long *cand;   // [grid][64] per-CTA candidate keys of the sampler (sample == 2)
     int32_t n_stages;     // ring stages of 16 KB (<= 10) and operand blocks of 1 KB (<= 64) in shared memory: tcd_plan()
     int32_t n_bslots;
+    int32_t n_poll;       // warps whose lane 0 polls the grid-barrier counter (1..12)
+    int32_t tmem_slots;   // weight stages (0..12) the issuer may park in tensor memory while it waits (decode_tc.cu)
+    int32_t poll_ns;      // pause of the issuer between two probes while it waits for a phase's operand
+    int32_t n_inflight;   // bulk copies a CTA keeps in flight (0: the whole ring)
     int32_t split_all;    // (test hook) k-split the last job too instead of giving whole tiles
     // ---- tensor parallel (tp_size > 1): row-parallel phases (bit 10 of x_src) add into `delta`, then an
     // all-reduce phase pushes delta to the peers' inboxes and adds all ranks' partials to h (see tp_ar.cu)

@@ -1,6 +1,6 @@
 """Debug: phase timeline of the tcgen05 persistent decode kernel (B200LLM_MEGA_TRACE=1).
-Needs the trace build of the library: make -C llm-based-apache-spark-optimization_b200/csrc clean all TRACE=1
-(the default build compiles the stamps out; rebuild without TRACE afterwards).
+Needs the trace build of the library: make -C llm-based-apache-spark-optimization_b200/csrc TRACE=1
+(libb200llm_trace.so beside the default build, which compiles the stamps out).
 Tagged stamps of thread 0 of CTA 0 and of the last CTA; durations are attributed to the tag
 that ENDS the interval."""
 import ctypes as C
@@ -11,6 +11,7 @@ import numpy as np
 
 os.environ["B200LLM_MEGA_TRACE"] = "1"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+os.environ.setdefault("B200LLM_LIB", os.path.join(ROOT, "llm-based-apache-spark-optimization_b200", "b200llm", "libb200llm_trace.so"))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "llm-based-apache-spark-optimization_b200")]
 from b200llm import Engine, _lib, geometry, weights  # noqa: E402
 

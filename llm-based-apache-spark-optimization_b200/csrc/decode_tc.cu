@@ -38,11 +38,16 @@ namespace b200 {
 
 constexpr int kTC = 384;              // compute threads
 constexpr int kTW = kTC / 32;         // compute warps
-constexpr int kTIssuers = 1;           // MMA issuer threads (one warp each): stage u of a segment goes to issuer u % kTIssuers.
-                                       // Two issuers are ~3 % faster (a prefilled ring drains at 39 instead of 64 clk per MMA) but
-                                       // rare launch failures / hangs appeared with them, so one is the default
+constexpr int kTIssuers = 2;           // MMA issuer warps.  Stage i of the CTA's weight stream (counted over the whole launch) goes to
+                                       // issuer i % 2 and lands in ring slot i % n_stages; n_stages is EVEN, so every ring slot belongs
+                                       // to one issuer for good.  That matters: an mbarrier waiter tells phases apart by parity only, so
+                                       // it has to see every phase of a barrier it waits on.  (Round 1 gave an issuer every second stage
+                                       // of each SEGMENT; with an odd ring a slot changed hands, an issuer far ahead of the producer --
+                                       // it is held back only by the 8 accumulators -- took a barrier still in its previous phase for
+                                       // "landed", multiplied stale bytes and freed the stage early: rare faults in short phases, a
+                                       // certain one in the 336-stage lm_head phase.)
 constexpr int kTThreads = kTC + 32 * kTIssuers + 32;   // + MMA issuer warps + producer warp
-static_assert(kTIssuers == 1, "the TMEM overflow queue below is kept by ONE issuer thread");
+// (the optional TMEM overflow queue is kept by ONE issuer: it is compiled in only when kTIssuers == 1)
 constexpr int kTMaxStages = 10;        // ring stages: as many as fit beside the operand blocks (TcdParams::n_stages)
 constexpr int kTStageBytes = 16384;   // [128 rows x 64 k] bf16
 constexpr int kTBSlots = 64;          // most activation operand blocks ([8 x 64 k] bf16 = 1 KB each) a CTA may need (TcdParams::n_bslots)
@@ -144,7 +149,7 @@ int tcd_stages_for(int head_dim, int gq, int n_jobs, int n_bslots) {
     const size_t fixed = tcd_fixed_smem_bytes(head_dim, gq, n_jobs) + (size_t)n_bslots * 1024;
     if (fixed + 4 * (size_t)kTStageBytes > kTSmemLimit) return 0;
     const int st = (int)((kTSmemLimit - fixed) / kTStageBytes);
-    return st > kTMaxStages ? kTMaxStages : st;
+    return (st > kTMaxStages ? kTMaxStages : st) & ~(kTIssuers - 1);   // a multiple of the issuer count (see kTIssuers)
 }
 
 // ring stages and operand blocks of a model: the operand buffer is sized for the neediest matrix,
@@ -161,7 +166,7 @@ bool tcd_plan(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_
     const size_t fixed = tcd_fixed_smem_bytes(head_dim, n_kv > 0 ? n_q / n_kv : 1, 4 * n_layers + 1) + (size_t)slots * 1024;
     if (fixed + 4 * (size_t)kTStageBytes > kTSmemLimit) return false;
     int st = (int)((kTSmemLimit - fixed) / kTStageBytes);
-    *n_stages = st > kTMaxStages ? kTMaxStages : st;
+    *n_stages = (st > kTMaxStages ? kTMaxStages : st) & ~(kTIssuers - 1);
     *n_bslots = slots;
     return true;
 }
@@ -385,7 +390,7 @@ __device__ __forceinline__ bool tcd_try_move(const TcdParams &p, const TcdSmem &
 #endif
 
 __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem_in, int me) {
-    (void)me, (void)lane;
+    (void)lane;
 #ifdef B200LLM_TCD_TRACE
     bool tr_on = false;
     int tr_n = 0;
@@ -412,18 +417,19 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
         left += r.g1 - r.g0;
     }
     left *= p.n_steps;
-    const bool use_tmem = p.tmem_slots > 0;
+    const bool use_tmem = kTIssuers == 1 && p.tmem_slots > 0;
     uint32_t xph = 0;
+    uint32_t turn = 0;   // stream index of the next stage, mod kTIssuers: whose stage it is
     for (int step = 0; step < p.n_steps; ++step) {
         for (int j = 0; j < n_jobs; ++j) {
             int N, K;
             tcd_job_shape(p, j, n_jobs, N, K);
             const TRange r = tcd_range(N, K, tcd_whole(p, j, n_jobs), G, bid);
 #ifdef B200LLM_TCD_TRACE
-            tr_on = p.trace != nullptr && bid == 0 && step == p.trace_step && j >= 4 && j < 8;
+            tr_on = p.trace != nullptr && bid == 0 && me == 0 && step == p.trace_step && j >= 4 && j < 8;
 #endif
             TCD_ICLK(c0);
-            // wait for the activation operand of this phase; meanwhile keep this SM's weight stream moving
+            // wait for the activation operand of this phase; meanwhile (one issuer only) keep this SM's weight stream moving
             if (use_tmem) {
                 while (!mbar_test_wait(s.xrdy, xph & 1))
                     if (!tcd_try_move(p, s, q, tmem, ring_a, left) && p.poll_ns > 0) __nanosleep((unsigned)p.poll_ns);
@@ -449,18 +455,23 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
                 }
                 TCD_ICLK(c3);
                 TCD_IACC(3, c3 - c2);
-                const uint32_t d_addr = tmem + aslot * kTAccCols;
+                // each issuer accumulates its stages of the segment into its own column group (columns 0..7 / 8..15 of the
+                // segment's accumulator) and the epilogue adds the groups; a one-stage segment goes to group 0 whoever has it
+                const uint32_t d_addr = tmem + aslot * kTAccCols + (seg_end - g > 1 ? (uint32_t)me * 8u : 0u);
                 uint32_t first = 1u;
-                for (; g < seg_end; ++g, bslot = (bslot + 1 == r.nkb ? 0 : bslot + 1)) {
+                for (; g < seg_end; ++g, turn = (turn + 1 == kTIssuers ? 0 : turn + 1), bslot = (bslot + 1 == r.nkb ? 0 : bslot + 1)) {
                     const uint32_t b_lo = b_lo0 + (uint32_t)bslot * 64u;
-                    if (q.t_n > 0) {   // the oldest stage was moved to TMEM (its copies precede these MMAs in issue order)
+                    if (kTIssuers == 1 && q.t_n > 0) {   // the oldest stage was moved to TMEM (its copies precede these MMAs in issue order)
                         if (tcd_elect()) {
                             tcd_mma4_ts(d_addr, tmem + kTSlotCol0 + (uint32_t)q.t_head * kTSlotCols, b_lo, b_hi, idesc, first);
                             tcd_commit(&s.tempty[q.t_head]);   // the slot may be refilled once these MMAs have read it
                         }
                         if (++q.t_head == kTSlots) q.t_head = 0;
                         --q.t_n;
-                    } else {
+                        first = 0u;
+                        continue;
+                    }
+                    if (kTIssuers == 1 || turn == (uint32_t)me) {
                         TCD_ICLK(c4);
                         mbar_wait(&s.full[q.slot], q.par);
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -472,12 +483,18 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
                             tcd_mma4_ss(d_addr, a_lo0 + (uint32_t)q.slot * 1024u, a_hi, b_lo, b_hi, idesc, first);
                             tcd_commit(&s.empty[q.slot]);  // frees the ring stage once the MMAs above have read it
                         }
-                        if (++q.slot == p.n_stages) q.slot = 0, q.par ^= 1;
-                        --left;
+                        first = 0u;
                     }
-                    first = 0u;
+                    if (++q.slot == p.n_stages) q.slot = 0, q.par ^= 1;
+                    --left;
                 }
-                if (tcd_elect()) tcd_commit(&s.acc_full[aslot]);
+                if (tcd_elect()) {
+                    if (first) {
+                        mbar_arrive(&s.acc_full[aslot]);   // a one-stage segment: nothing for this issuer
+                    } else {
+                        tcd_commit(&s.acc_full[aslot]);
+                    }
+                }
                 __syncwarp();
                 TCD_ISTAMP_STAGE(13);
                 ++as;
@@ -486,7 +503,7 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
         }
     }
 #ifdef B200LLM_TCD_TRACE
-    if (p.trace != nullptr && bid == 0 && lane == 0) {
+    if (p.trace != nullptr && bid == 0 && lane == 0 && me == 0) {
 #ifdef B200LLM_TCD_TRACE_DEEP
         tr_acc[6] = clock64() - tr_t0;
         tr_acc[2] = tr_acc[6] - tr_acc[0] - tr_acc[1] - tr_acc[3];

@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
 
 template <int HD, int GQ>
 static int tcd_launch_t(const TcdParams &p, cudaStream_t stream) {
-    B200_REQUIRE(p.n_stages >= 4 && p.n_stages <= kTMaxStages && p.n_bslots >= 1 && p.n_bslots <= kTBSlots,
+    B200_REQUIRE(p.n_stages >= 4 && p.n_stages <= kTMaxStages && p.n_stages % kTIssuers == 0 && p.n_bslots >= 1 && p.n_bslots <= kTBSlots,
                  "tcd: bad ring plan (%d stages, %d operand blocks)", p.n_stages, p.n_bslots);
     const size_t smem = tcd_smem_bytes(HD, GQ, 4 * p.n_layers + 1, p.n_stages, p.n_bslots);
     B200_REQUIRE(smem <= kTSmemLimit, "tcd: %zu bytes of shared memory needed", smem);

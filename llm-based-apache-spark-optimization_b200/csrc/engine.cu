@@ -912,7 +912,7 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
     }
     B200_REQUIRE(tcd_plan(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, (e->vocab_l + 127) / 128 * 128, c.n_layers, &p.n_stages, &p.n_bslots),
                  "tcd: geometry does not fit");
-    if (const char *ns = getenv("B200LLM_TCD_STAGES")) p.n_stages = atoi(ns) < p.n_stages ? atoi(ns) : p.n_stages;
+    if (const char *ns = getenv("B200LLM_TCD_STAGES")) p.n_stages = (atoi(ns) < p.n_stages ? atoi(ns) : p.n_stages) & ~1;
     if (const char *nf = getenv("B200LLM_TCD_INFLIGHT")) p.n_inflight = atoi(nf);
     p.tmem_slots = 0;   // measured: parking stages in tensor memory during the gaps loses 1-3 % (profiles/tcd_tmem_overflow_r2.txt)
     if (const char *ts = getenv("B200LLM_TCD_TMEM")) p.tmem_slots = atoi(ts) < 0 ? 0 : (atoi(ts) > 12 ? 12 : atoi(ts));

@@ -199,13 +199,16 @@ __device__ __forceinline__ unsigned tcd_poll(unsigned *ctr) {
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
     return v;
 }
-__device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, int tid, volatile unsigned *done, int n_poll) {
+// Two halves, so that the trace build can stamp between them: arrive = CTA barrier + thread 0's release (a fence that
+// waits for the CTA's global writes to be performed, then the add); wait = poll, one fence, CTA barrier.
+__device__ __forceinline__ void tcd_grid_arrive(unsigned *ctr, int tid) {
     bar_sync(1, kTC);
     if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
-    // Lane 0 of the first n_poll warps polls, each with one relaxed load in flight, started a fraction of a round trip
-    // apart: the last arrival is seen by whichever poll reaches L2 next (~RTT / n_poll later instead of ~RTT / 2 with
-    // one poller); the finder fences once (an acquire load per poll would cost an L1 invalidate, CCTL.IVALL, per
-    // iteration) and tells the others through shared memory.
+}
+__device__ __forceinline__ void tcd_grid_wait(unsigned *ctr, unsigned target, int tid, volatile unsigned *done, int n_poll) {
+    // Lane 0 of the first n_poll warps polls, each with one relaxed load in flight (measured: more than one poller per
+    // CTA only adds contention on the counter's line, profiles/sweep_poll_r2.txt); the finder fences once (an acquire
+    // load per poll would cost an L1 invalidate, CCTL.IVALL, per iteration) and tells the others through shared memory.
     if ((tid & 31) == 0 && (tid >> 5) < n_poll) {
         if (tid) __nanosleep((unsigned)(tid >> 5) * 1200u / (unsigned)n_poll);
         for (;;) {
@@ -218,6 +221,10 @@ __device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, in
         }
     }
     bar_sync(1, kTC);
+}
+__device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, int tid, volatile unsigned *done, int n_poll) {
+    tcd_grid_arrive(ctr, tid);
+    tcd_grid_wait(ctr, target, tid, done, n_poll);
 }
 
 // ---------------------------------------------------------------- producer: the weight stream
@@ -526,7 +533,7 @@ struct TcdCtx {
 
 // (debug) tagged globaltimer stamps of thread 0: tag in bits 48.., nanoseconds below
 enum { TT_STEP = 1, TT_XCONV = 2, TT_XREADY = 3, TT_EPI = 4, TT_BAR = 5, TT_ATT_Q = 6, TT_ATT_KV = 7, TT_ATT_WARPS = 8,
-       TT_ATT_DONE = 9 };
+       TT_ATT_DONE = 9, TT_BAR_ARRIVED = 14 };
 // Compiled in only with -DB200LLM_TCD_TRACE (make TRACE=1): the cursor and the stamps cost registers, and what the
 // 128-register kernel spills it reloads right behind the grid barriers (an L2 round trip each, L1 was just invalidated).
 __device__ __forceinline__ void tcd_trace(const TcdParams &p, int &ti, int bid, int tid, int tag) {

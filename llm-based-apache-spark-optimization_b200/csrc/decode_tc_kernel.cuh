@@ -104,7 +104,9 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 tcd_attn_prefetch<HD>(p, qkv_job, s, c, G, bid, tid);
                 phase(4 * l);      // rmsnorm + qkv (raw sums)
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                tcd_grid_arrive(p.bar_ctr, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 tcd_attn_phase<HD, GQ>(p, qkv_job, s, c, G, bid, tid);  // rope + kv append + attention
                 step = reinterpret_cast<volatile int *>(s.misc)[57];   // written before the barrier above
@@ -112,11 +114,15 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 bar_no = (unsigned)reinterpret_cast<volatile int *>(s.misc)[59];
                 tcd_trace(p, c.ti, bid, tid, TT_ATT_DONE);
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                tcd_grid_arrive(p.bar_ctr, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 phase(4 * l + 1);  // o_proj + residual
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                tcd_grid_arrive(p.bar_ctr, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 if (p.tp_size > 1) {   // o_proj is row-parallel: h += sum over ranks of the partial sums
                     tcd_allreduce_phase(p, s, G, bid, tid);
@@ -124,11 +130,15 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 }
                 phase(4 * l + 2);  // rmsnorm + gate/up (raw sums)
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                tcd_grid_arrive(p.bar_ctr, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 phase(4 * l + 3);  // swiglu + down + residual
                 arrive_stamp();
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                tcd_grid_arrive(p.bar_ctr, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 if (p.tp_size > 1) {   // down_proj is row-parallel too
                     tcd_allreduce_phase(p, s, G, bid, tid);
@@ -142,7 +152,9 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 // ---- sampler chain in the kernel: penalty + per-CTA top-k, barrier, redundant merge + draw ----
                 const int k = p.temperature > 0.f ? p.top_k : 1;
                 tcd_sample_local(p, s.jobs[n_jobs - 1], s, k, G, bid, tid);
-                tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                tcd_grid_arrive(p.bar_ctr, tid);
+                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 c.tok = tcd_sample_merge(p, s, c, k, G, tid);
                 c.pos += 1;

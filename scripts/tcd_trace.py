@@ -15,7 +15,7 @@ os.environ.setdefault("B200LLM_LIB", os.path.join(ROOT, "llm-based-apache-spark-
 sys.path[:0] = [ROOT, os.path.join(ROOT, "llm-based-apache-spark-optimization_b200")]
 from b200llm import Engine, _lib, geometry, weights  # noqa: E402
 
-TAGS = {1: "step", 2: "x_conv", 3: "x_ready", 4: "epilogue", 5: "barrier", 6: "att_q", 7: "att_kv", 8: "att_warps", 9: "att_done", 10: "mma_phase", 11: "full", 12: "issued", 13: "seg"}
+TAGS = {1: "step", 2: "x_conv", 3: "x_ready", 4: "epilogue", 5: "barrier", 6: "att_q", 7: "att_kv", 8: "att_warps", 9: "att_done", 10: "mma_phase", 11: "full", 12: "issued", 13: "seg", 14: "bar_arrive"}
 name = sys.argv[1] if len(sys.argv) > 1 else "llama3.2"
 ctx = int(sys.argv[2]) if len(sys.argv) > 2 else 296
 geo = geometry.resolve(name)

@@ -130,10 +130,12 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 }
                 phase(4 * l + 2);  // rmsnorm + gate/up (raw sums)
                 arrive_stamp();
-                tcd_grid_arrive(p.bar_ctr, tid);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
-                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                if (!(p.dataflow & 1)) {   // (data-flow mode: the down_proj prologue polls the (sum, count) pairs it needs)
+                    tcd_grid_arrive(p.bar_ctr, tid);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                    tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                }
                 phase(4 * l + 3);  // swiglu + down + residual
                 arrive_stamp();
                 tcd_grid_arrive(p.bar_ctr, tid);

@@ -11,6 +11,17 @@
 // (kb - kb_start) mod nkb, where kb_start is the k block of the range's first unit.
 // Returns the RMSNorm scale rsqrt(mean(x^2) + eps) (1 when the phase has no norm); the scale
 // is applied in the epilogue (it is a scalar factor of the whole dot product).
+// How many CTAs add partial sums to the rows of row tile `tile` of an [N, K] phase split stream-K over G CTAs
+// (unit = tile * nkb + kb; the first `rem` CTAs take base + 1 units, the others base).
+__device__ __forceinline__ float tcd_tile_contributors(int N, int K, int tile, int G) {
+    const int nkb = K / 64, n_units = (N / 128) * nkb;
+    const int base = n_units / G, rem = n_units % G, cut = rem * (base + 1);
+    const int u0 = tile * nkb, u1 = u0 + nkb - 1;
+    const int c0 = u0 < cut ? u0 / (base + 1) : rem + (u0 - cut) / base;
+    const int c1 = u1 < cut ? u1 / (base + 1) : rem + (u1 - cut) / base;
+    return (float)(c1 - c0 + 1);
+}
+
 __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSmem &s, TcdCtx &c, const TRange &r,
                               int G, int bid, int tid) {
     const int warp = tid >> 5, lane = tid & 31;
@@ -35,9 +46,10 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
         for (int i = bid * kTC + tid; i < p.d / 4; i += G * kTC) reinterpret_cast<float4 *>(p.delta)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     if (job.x_src & 0x100) {  // clear the sum buffers the next qkv / gate-up phases add into
-        const int nq4 = (p.n_q + 2 * p.n_kv) * p.head_dim / 4, ng4 = 2 * p.ffn / 4;
+        const int nq4 = (p.n_q + 2 * p.n_kv) * p.head_dim / 4, ng4 = (p.dataflow & 1) ? 4 * p.ffn / 4 : 2 * p.ffn / 4;
+        float4 *gz = (p.dataflow & 1) ? reinterpret_cast<float4 *>(p.gu2) : reinterpret_cast<float4 *>(p.gu);
         for (int i = bid * kTC + tid; i < nq4 + ng4; i += G * kTC) {
-            float4 *dst = i < nq4 ? reinterpret_cast<float4 *>(p.qkv) + i : reinterpret_cast<float4 *>(p.gu) + (i - nq4);
+            float4 *dst = i < nq4 ? reinterpret_cast<float4 *>(p.qkv) + i : gz + (i - nq4);
             *dst = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
@@ -73,6 +85,30 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
                 *reinterpret_cast<float4 *>(p.h + chunk * 8) = make_float4(v[0], v[1], v[2], v[3]);
                 *reinterpret_cast<float4 *>(p.h + chunk * 8 + 4) = make_float4(v[4], v[5], v[6], v[7]);
             }
+        } else if (x_kind == TCD_X_SWIGLU && (p.dataflow & 1)) {
+            // (sum, count) pairs of 8 gate/up pairs: poll until every count says its tile's contributors are all in
+            const float want = tcd_tile_contributors(2 * p.ffn, p.d, chunk >> 3, G);
+            const float2 *gp = p.gu2 + (size_t)chunk * 16;
+            float4 q[8];
+            for (;;) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(q[e].x), "=f"(q[e].y), "=f"(q[e].z), "=f"(q[e].w) : "l"(gp + 2 * e) : "memory");
+                bool ok = true;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) ok = ok && q[e].y == want && q[e].w == want;
+                if (ok) break;
+                // not there yet: watch one pair of counts (16 bytes instead of 128 per probe) until it is, then look again
+                float4 w1;
+                do {
+                    __nanosleep(64);
+                    asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(w1.x), "=f"(w1.y), "=f"(w1.z), "=f"(w1.w) : "l"(gp + 14) : "memory");
+                } while (w1.y != want || w1.w != want);
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = (q[e].x / (1.f + expf(-q[e].x))) * q[e].z;
         } else if (x_kind == TCD_X_SWIGLU) {
             const float4 *gp = reinterpret_cast<const float4 *>(p.gu + (size_t)chunk * 16);
             const float4 a = __ldcg(gp), b = __ldcg(gp + 1), cc = __ldcg(gp + 2), d = __ldcg(gp + 3);
@@ -175,6 +211,8 @@ __device__ void tcd_epilogue(const TcdParams &p, const TcdJob &job, const TcdSme
         const int n = t * 128 + warp * 32 + lane;
         if (job.epi == TCD_EPI_ADD) {
             asm volatile("red.global.add.f32 [%0], %1;" ::"l"(job.out + n), "f"(v) : "memory");
+        } else if (job.epi == TCD_EPI_ADD_CNT) {   // sum and contribution count in one 8-byte vector red
+            asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(reinterpret_cast<float2 *>(job.out) + n), "f"(v), "f"(1.f) : "memory");
         } else if (n < p.vocab) {   // rows past the vocabulary pad the last tile
             job.out[n] = v;
             if (v > c.best) c.best = v, c.best_i = n;

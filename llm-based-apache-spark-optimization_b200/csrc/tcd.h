@@ -19,7 +19,7 @@ struct TcdJob {
     int32_t epi;          // TCD_EPI_*
     int32_t x_src;        // TCD_X_* in the low byte; bit 8: this phase also clears the qkv and gate/up sum buffers
 };
-enum { TCD_EPI_ADD = 0, TCD_EPI_LOGITS = 1 };
+enum { TCD_EPI_ADD = 0, TCD_EPI_LOGITS = 1, TCD_EPI_ADD_CNT = 2 };   // ADD_CNT: out is float2 [N]: (partial sum, 1) is added, see TcdParams::dataflow
 enum { TCD_X_H = 0, TCD_X_ATT = 1, TCD_X_SWIGLU = 2, TCD_X_EMBED = 3 };
 
 struct TcdParams {
@@ -62,6 +62,13 @@ struct TcdParams {
     int32_t n_stages;     // ring stages of 16 KB (<= 10) and operand blocks of 1 KB (<= 64) in shared memory: tcd_plan()
     int32_t n_bslots;
     int32_t n_poll;       // warps whose lane 0 polls the grid-barrier counter (1..12)
+    // Data-flow synchronisation (tp_size 1): a phase whose bit is set adds (partial sum, 1.0f) pairs with ONE vector
+    // red per row instead of a bare fp32 red, and its consumer polls the pairs of the rows it needs until each count
+    // equals the number of CTAs that contribute to the row's tile: the data says when it is complete, so the grid
+    // barrier between producer and consumer phase (release fence + counter + poll, then the re-load: three dependent
+    // L2 round trips) becomes one polling load.  bit 0: gate/up sums -> down_proj.
+    int32_t dataflow;
+    float2 *gu2;          // [2 ffn] (sum, count) pairs of the gate/up phase
     int32_t tmem_slots;   // weight stages (0..12) the issuer may park in tensor memory while it waits (decode_tc.cu)
     int32_t poll_ns;      // pause of the issuer between two probes while it waits for a phase's operand
     int32_t n_inflight;   // bulk copies a CTA keeps in flight (0: the whole ring)

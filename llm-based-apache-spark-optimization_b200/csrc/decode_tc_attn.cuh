@@ -252,7 +252,17 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
                 }
             }
             const int hq = hk * GQ + g;
-            if (ns == 1) {
+            if (p.dataflow & 2) {   // (value, tag) pairs, 8-byte stores: o_proj's prologue polls for this layer's tag
+                const float tag = (float)(reinterpret_cast<volatile int *>(s.misc)[57] * p.n_layers + reinterpret_cast<volatile int *>(s.misc)[58] + 1);
+                float2 *part_o2 = p.att2 + (size_t)p.n_q * HD;
+                if (ns == 1) {
+                    p.att2[(size_t)hq * HD + dd] = make_float2(O / L, tag);
+                } else {
+                    const size_t pi = (size_t)hq * p.n_splits + split;
+                    part_o2[pi * HD + dd] = make_float2(O, tag);
+                    if (dd == 0) reinterpret_cast<float4 *>(part_o2 + (size_t)p.n_q * p.n_splits * HD)[pi] = make_float4(M, L, tag, 0.f);
+                }
+            } else if (ns == 1) {
                 p.att[(size_t)hq * HD + dd] = O / L;
             } else {
                 const size_t pi = (size_t)hq * p.n_splits + split;

@@ -114,10 +114,12 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 bar_no = (unsigned)reinterpret_cast<volatile int *>(s.misc)[59];
                 tcd_trace(p, c.ti, bid, tid, TT_ATT_DONE);
                 arrive_stamp();
-                tcd_grid_arrive(p.bar_ctr, tid);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
-                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                if (!(p.dataflow & 2)) {   // (data-flow mode: the o_proj prologue polls the (value, tag) pairs it needs)
+                    tcd_grid_arrive(p.bar_ctr, tid);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                    tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                }
                 phase(4 * l + 1);  // o_proj + residual
                 arrive_stamp();
                 tcd_grid_arrive(p.bar_ctr, tid);

@@ -31,6 +31,7 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
     const int x_kind = job.x_src & 0xff;
     const int att_ns = x_kind == TCD_X_ATT ? tcd_att_ns(p, c.pos) : 1;
     const uint16_t *gain = reinterpret_cast<const uint16_t *>(job.gain);
+    const int jidx = (int)(&job - s.jobs);
 
     {   // the RMSNorm gain vectors of the next two phases are cold (read once per step): pull them into L2
         const TcdJob *first = s.jobs, *last = s.jobs + 4 * p.n_layers;
@@ -45,13 +46,18 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
     if ((job.x_src & 0x400) && p.tp_size > 1) {  // tensor parallel: clear the partial-sum vector of the next row-parallel phase
         for (int i = bid * kTC + tid; i < p.d / 4; i += G * kTC) reinterpret_cast<float4 *>(p.delta)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    if (job.x_src & 0x100) {  // clear the sum buffers the next qkv / gate-up phases add into
-        const int nq4 = (p.n_q + 2 * p.n_kv) * p.head_dim / 4, ng4 = (p.dataflow & 1) ? 4 * p.ffn / 4 : 2 * p.ffn / 4;
+    // Clear the sum buffers the next qkv / gate-up phases add into, each while nobody can be reading it and a grid barrier
+    // before it is added to again: gate/up's in the o_proj phase (bit 8; its readers were the previous layer's down_proj
+    // prologues), qkv's in the gate/up phase (bit 9; its readers were this layer's attention items: after the barrier that
+    // ends the o_proj phase every CTA is past its attention item, and the barrier after down_proj comes before the next adds).
+    if (job.x_src & 0x100) {
+        const int ng4 = (p.dataflow & 1) ? 4 * p.ffn / 4 : 2 * p.ffn / 4;
         float4 *gz = (p.dataflow & 1) ? reinterpret_cast<float4 *>(p.gu2) : reinterpret_cast<float4 *>(p.gu);
-        for (int i = bid * kTC + tid; i < nq4 + ng4; i += G * kTC) {
-            float4 *dst = i < nq4 ? reinterpret_cast<float4 *>(p.qkv) + i : gz + (i - nq4);
-            *dst = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+        for (int i = bid * kTC + tid; i < ng4; i += G * kTC) gz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (job.x_src & 0x200) {
+        const int nq4 = (p.n_q + 2 * p.n_kv) * p.head_dim / 4;
+        for (int i = bid * kTC + tid; i < nq4; i += G * kTC) reinterpret_cast<float4 *>(p.qkv)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     // phases with a norm (or that seed the residual stream from the embedding) read the whole
     // vector; the others only the chunks (8 values) of the k blocks this CTA streams
@@ -116,6 +122,65 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
             v[2] = (b.x / (1.f + expf(-b.x))) * b.y, v[3] = (b.z / (1.f + expf(-b.z))) * b.w;
             v[4] = (cc.x / (1.f + expf(-cc.x))) * cc.y, v[5] = (cc.z / (1.f + expf(-cc.z))) * cc.w;
             v[6] = (d.x / (1.f + expf(-d.x))) * d.y, v[7] = (d.z / (1.f + expf(-d.z))) * d.w;
+        } else if (x_kind == TCD_X_ATT && (p.dataflow & 2)) {
+            // (value, tag) pairs written by the attention items of this layer: poll for the layer's tag (no grid barrier
+            // between the attention phase and this one); split-T partials are merged as below
+            const float tag = (float)(reinterpret_cast<volatile int *>(s.misc)[57] * p.n_layers + (jidx >> 2) + 1);
+            const int hd = p.head_dim, hq = (chunk * 8) / hd, dd = (chunk * 8) % hd;
+            if (att_ns == 1) {
+                const float2 *ap = p.att2 + (size_t)chunk * 8;
+                float4 q[4];
+                for (;;) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                     : "=f"(q[e].x), "=f"(q[e].y), "=f"(q[e].z), "=f"(q[e].w) : "l"(ap + 2 * e) : "memory");
+                    bool ok = true;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) ok = ok && q[e].y == tag && q[e].w == tag;
+                    if (ok) break;
+                    __nanosleep(32);
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) v[2 * e] = q[e].x, v[2 * e + 1] = q[e].z;
+            } else {
+                const float2 *part_o2 = p.att2 + (size_t)p.n_q * hd;
+                const float4 *part_ml2 = reinterpret_cast<const float4 *>(part_o2 + (size_t)p.n_q * p.n_splits * hd);
+                const size_t pb = (size_t)hq * p.n_splits;
+                float M = -INFINITY, L = 0.f;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = 0.f;
+                for (int sp = 0; sp < att_ns; ++sp) {
+                    float4 ml, q[4];
+                    for (;;) {
+                        asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                     : "=f"(ml.x), "=f"(ml.y), "=f"(ml.z), "=f"(ml.w) : "l"(part_ml2 + pb + sp) : "memory");
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                         : "=f"(q[e].x), "=f"(q[e].y), "=f"(q[e].z), "=f"(q[e].w)
+                                         : "l"(part_o2 + (pb + sp) * hd + dd + 2 * e) : "memory");
+                        bool ok = ml.z == tag;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) ok = ok && q[e].y == tag && q[e].w == tag;
+                        if (ok) break;
+                        __nanosleep(32);
+                    }
+                    const float mn = fmaxf(M, ml.x);
+                    const float c_old = mn == -INFINITY ? 1.f : exp2f(M - mn);
+                    const float c_new = mn == -INFINITY ? 0.f : exp2f(ml.x - mn);
+                    L = L * c_old + ml.y * c_new;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        v[2 * e] = v[2 * e] * c_old + q[e].x * c_new;
+                        v[2 * e + 1] = v[2 * e + 1] * c_old + q[e].z * c_new;
+                    }
+                    M = mn;
+                }
+                const float inv = 1.f / L;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] *= inv;
+            }
         } else if (x_kind == TCD_X_ATT && att_ns > 1) {
             // split-T attention partials of this head -> merged output (running max, fixed split order)
             const int hd = p.head_dim, hq = (chunk * 8) / hd, dd = (chunk * 8) % hd;

@@ -66,9 +66,12 @@ struct TcdParams {
     // red per row instead of a bare fp32 red, and its consumer polls the pairs of the rows it needs until each count
     // equals the number of CTAs that contribute to the row's tile: the data says when it is complete, so the grid
     // barrier between producer and consumer phase (release fence + counter + poll, then the re-load: three dependent
-    // L2 round trips) becomes one polling load.  bit 0: gate/up sums -> down_proj.
+    // L2 round trips) becomes one polling load.  bit 0: gate/up sums -> down_proj.  bit 1: attention -> o_proj: the
+    // attention items (one writer per value) store (value, tag) pairs, tag = step * n_layers + layer + 1 of this launch
+    // (the host clears the buffer before a launch), and o_proj's prologue polls the pairs of its k-slices for the tag.
     int32_t dataflow;
     float2 *gu2;          // [2 ffn] (sum, count) pairs of the gate/up phase
+    float2 *att2;         // [n_q head_dim] (value, tag) | part_o2 [n_q, n_splits, head_dim] (value, tag) | part_ml2 [n_q, n_splits] float4 (max, sum, tag, -)
     int32_t tmem_slots;   // weight stages (0..12) the issuer may park in tensor memory while it waits (decode_tc.cu)
     int32_t poll_ns;      // pause of the issuer between two probes while it waits for a phase's operand
     int32_t n_inflight;   // bulk copies a CTA keeps in flight (0: the whole ring)

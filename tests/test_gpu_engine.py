@@ -390,7 +390,7 @@ def test_sampled_decode_in_the_persistent_kernel_matches_oracle(name, sigma, opt
     (1) Along the oracle's token path (b200llm_set_lane forces its token, one launch of the persistent kernel with
         the sampler as its last phase per step): the penalised logits agree within TIGHT_TOL and every draw is the
         oracle's, except where the MEASURED logit deviation can move the draw across a boundary (the cumulative
-        masses move by at most exp(2 dev / T) - 1; for the penalised argmax, a top-2 margin below 2 dev): those
+        masses, as fractions of the kept mass, move by at most 2 (exp(2 dev / T) - 1); for the penalised argmax, a top-2 margin below 2 dev): those
         are counted and printed, and must be few.
     (2) Free-running, all 63 steps in ONE launch: the oracle's tokens up to the first such boundary case, then the
         token (1) drew there; bit-identical to 63 launches of one step.
@@ -421,7 +421,7 @@ def test_sampled_decode_in_the_persistent_kernel_matches_oracle(name, sigma, opt
         worst = max(worst, dev / float(np.abs(pen[s]).max()))
         forced.append(tok)
         if tok != want[s]:
-            explained = (slack[s] < np.expm1(2 * dev / sp.temperature) + 1e-6) if sp.temperature > 0 else (margin[s] <= 2 * dev)
+            explained = (slack[s] < 2 * np.expm1(2 * dev / sp.temperature) + 1e-6) if sp.temperature > 0 else (margin[s] <= 2 * dev)
             assert explained, (f"step {s}: drew {tok}, oracle {want[s]}; draw slack {slack[s]:.2e}, top-2 margin "
                                f"{margin[s]:.2e}, logit deviation {dev:.2e}")
             cases.append(s)
@@ -469,23 +469,28 @@ def test_sampled_decode_full_size_one_launch(golden_dir):
     eng.set_sampling(lane, sp)
     eng.prefill(lane, prompt)
     toks = [eng.read_lane(lane)[0]]
-    n_close = 0
+    n_close, slacks = 0, [1.0]
     for s in range(32):
         tok = int(eng.decode([lane], 1)[0, 0])
         assert eng.timing().kernel_launches == 1
         lg = eng.logits(0)
         ctr = len(prompt) + s                       # position of the token that was fed
         want, ids, probs = sampler.sample(lg, sp.temperature, sp.top_k, sp.top_p, 1.0, sp.seed, ctr)
+        mass = float(probs.sum())
+        r = float(sampler.uniform(sp.seed, ctr)) * mass
+        slack = float(np.abs(np.cumsum(probs.astype(np.float64)) - r).min() / mass)
         if tok != want:                             # only an expf ulp at a cumulative-mass edge may differ
-            mass = float(probs.sum())
-            r = float(sampler.uniform(sp.seed, ctr)) * mass
-            slack = float(np.abs(np.cumsum(probs.astype(np.float64)) - r).min() / mass)
             assert slack < 1e-5, f"step {s}: kernel drew {tok}, oracle sampler on the same logits {want} (slack {slack:.2e})"
             n_close += 1
         toks.append(tok)
+        slacks.append(slack)
     eng.close_lane(lane)
     print(f"3B sampled: 32/32 draws equal oracle/sampler.py on the kernel's own logits ({n_close} within an expf ulp of an edge)")
     assert len(set(toks)) > 8
+    # the same 32 steps as ONE launch.  Split-K partial sums meet in fp32 atomics, whose order differs from run to run, so the
+    # logits agree to ~1e-6 only: a draw within 1e-4 of a cumulative-mass edge may legitimately flip (and the sequences part there)
     again, tm = eng.generate_ids(prompt, 33, sp)
-    assert tm.kernel_launches == 1 and again == toks
+    assert tm.kernel_launches == 1
+    first = next((i for i, (a, b) in enumerate(zip(again, toks)) if a != b), None)
+    assert first is None or slacks[first] < 1e-4, f"one launch differs from 32 launches at step {first} (slack {slacks[first]:.2e})"
     eng.close()

@@ -74,6 +74,7 @@ constexpr int kTMaxJobs = 4 * 32 + 1;
 struct TcdSmem {
     uint8_t *ring, *bop;
     float *mrg;            // attention merge buffer [kTW][GQ][HD + 2]
+    float *qst;            // q | k | v sums of this CTA's attention item [(GQ + 2) * HD] (data-flow mode)
     uint64_t *full, *empty, *acc_full, *acc_empty, *tempty, *xrdy;
     uint32_t *tmem_slot;
     float *red;
@@ -84,6 +85,7 @@ struct TcdSmem {
 };
 
 __host__ __device__ __forceinline__ size_t tcd_mrg_bytes(int hd, int gq) { return (size_t)kTW * gq * (hd + 2) * 4; }
+__host__ __device__ __forceinline__ size_t tcd_qst_bytes(int hd, int gq) { return (size_t)(gq + 2) * hd * 4; }
 
 // Layout: everything the compute warps address sits at COMPILE-TIME offsets from the base (merge buffer,
 // barriers, scratch, page table, phase descriptors), so those pointers cost no registers; the operand blocks
@@ -91,7 +93,8 @@ __host__ __device__ __forceinline__ size_t tcd_mrg_bytes(int hd, int gq) { retur
 __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int n_jobs, int n_bslots) {
     TcdSmem s;
     s.mrg = reinterpret_cast<float *>(base);
-    uint8_t *q = base + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15);
+    s.qst = reinterpret_cast<float *>(base + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15));
+    uint8_t *q = reinterpret_cast<uint8_t *>(s.qst) + tcd_qst_bytes(hd, gq);
     s.full = reinterpret_cast<uint64_t *>(q);
     s.empty = s.full + kTMaxStages;
     s.acc_full = s.empty + kTMaxStages;
@@ -111,7 +114,7 @@ __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int 
 }
 
 static size_t tcd_fixed_smem_bytes(int hd, int gq, int n_jobs) {  // everything but the ring and the operand blocks
-    return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + (2 * kTMaxStages + 2 * kTAcc + kTSlots + 2) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 +
+    return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + tcd_qst_bytes(hd, gq) + (2 * kTMaxStages + 2 * kTAcc + kTSlots + 2) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 +
            kTMaxPtab * 4 + (size_t)n_jobs * sizeof(TcdJob) + 2 * 1024;  // slack: 1024-byte alignment of the base and of the operand blocks
 }
 static size_t tcd_smem_bytes(int hd, int gq, int n_jobs, int n_stages, int n_bslots) {

@@ -42,6 +42,40 @@ __device__ __forceinline__ void tcd_attn_prefetch(const TcdParams &p, const TcdJ
     }
 }
 
+// Data-flow mode (TcdParams::dataflow bit 2): instead of a grid barrier after the qkv phase, a CTA that has an attention
+// item waits until the (sum, count) pairs of its kv head's rows -- the GQ q heads, k and v -- carry the full count of
+// their tile's contributors.  One row per thread and round; the polling load IS the load of q, k and v: the sums go
+// to shared memory (s.qst), so the phase starts without another L2 round trip.  (One item per CTA: n_kv * splits <= G.)
+template <int HD, int GQ>
+__device__ __forceinline__ void tcd_attn_wait_qkv(const TcdParams &p, const TcdJob &qkv_job, const TcdSmem &s, const TcdCtx &c, int G,
+                                                  int bid, int tid) {
+    const int n_pages = c.pos / kTPT + 1;
+    const int ns = min(p.n_splits, (2 * n_pages + kTW - 1) / kTW);
+    const int n_items = p.n_kv * ns;
+    const int qrows = p.n_q * HD, krows = p.n_kv * HD;
+    for (int item = bid; item < n_items; item += G) {
+        const int hk = item / ns;
+        for (int i = tid; i < (GQ + 2) * HD; i += kTC) {
+            const int row = i < GQ * HD ? hk * GQ * HD + i : (i < (GQ + 1) * HD ? qrows + hk * HD + (i - GQ * HD) : qrows + krows + hk * HD + (i - (GQ + 1) * HD));
+            const float want = tcd_tile_contributors(qkv_job.N, qkv_job.K, row / 128, G);
+            float sum, cnt;
+            for (;;) {
+                asm volatile("ld.relaxed.gpu.global.v2.f32 {%0, %1}, [%2];" : "=f"(sum), "=f"(cnt) : "l"(p.qkv2 + row) : "memory");
+                if (cnt == want) break;
+                __nanosleep(32);
+            }
+            s.qst[i] = sum;
+        }
+    }
+    bar_sync(1, kTC);
+}
+// four consecutive q | k | v sums of the item's head (index i0 into [GQ q heads | k | v] x HD, `row` the same position in the
+// qkv buffer): staged in shared memory by tcd_attn_wait_qkv in data-flow mode, else read from the plain buffer
+__device__ __forceinline__ float4 tcd_ld_sums4(const TcdParams &p, const TcdSmem &s, int i0, size_t row) {
+    if (p.dataflow & 4) return *reinterpret_cast<const float4 *>(s.qst + i0);
+    return __ldcg(reinterpret_cast<const float4 *>(p.qkv + row));
+}
+
 template <int HD, int GQ>
 __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const TcdSmem &s, TcdCtx &c,
                                 int G, int bid, int tid) {
@@ -64,10 +98,10 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
         float q[GQ][EL], m[GQ], l[GQ], o[GQ][EL];
 #pragma unroll
         for (int g = 0; g < GQ; ++g) {
-            const float *qp = p.qkv + (size_t)(hk * GQ + g) * HD + p16 * EL;
+            const size_t qrow = (size_t)(hk * GQ + g) * HD + p16 * EL;
 #pragma unroll
             for (int e = 0; e < EL; e += 4) {
-                const float4 v = __ldcg(reinterpret_cast<const float4 *>(qp + e));
+                const float4 v = tcd_ld_sums4(p, s, g * HD + p16 * EL + e, qrow + e);
                 const float *rp = s.rope + p16 * EL + e;  // (cos, sin) of the pairs (e, e+1), (e+2, e+3)
                 q[g][e] = (v.x * rp[0] - v.y * rp[1]) * p.scale_log2, q[g][e + 1] = (v.y * rp[0] + v.x * rp[1]) * p.scale_log2;
                 q[g][e + 2] = (v.z * rp[2] - v.w * rp[3]) * p.scale_log2, q[g][e + 3] = (v.w * rp[2] + v.z * rp[3]) * p.scale_log2;
@@ -80,13 +114,12 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
         if (split == own_split && warp == 0) {
             // the current token: k (RoPE) and v of this kv head from the raw sums, rounded to bf16 as
             // the cache holds them; both half-warps compute it, lanes 0..15 adopt and append it
-            const float *kraw = p.qkv + qrows + (size_t)hk * HD + p16 * EL;
-            const float *vraw = kraw + krows;
+            const size_t krow = (size_t)qrows + (size_t)hk * HD + p16 * EL;
             float kf[EL], vf[EL];
 #pragma unroll
             for (int e = 0; e < EL; e += 4) {
-                const float4 kv = __ldcg(reinterpret_cast<const float4 *>(kraw + e));
-                const float4 vv = __ldcg(reinterpret_cast<const float4 *>(vraw + e));
+                const float4 kv = tcd_ld_sums4(p, s, GQ * HD + p16 * EL + e, krow + e);
+                const float4 vv = tcd_ld_sums4(p, s, (GQ + 1) * HD + p16 * EL + e, krow + krows + e);
                 const float *rp = s.rope + p16 * EL + e;
                 kf[e] = tcd_bf16_round(kv.x * rp[0] - kv.y * rp[1]), kf[e + 1] = tcd_bf16_round(kv.y * rp[0] + kv.x * rp[1]);
                 kf[e + 2] = tcd_bf16_round(kv.z * rp[2] - kv.w * rp[3]), kf[e + 3] = tcd_bf16_round(kv.w * rp[2] + kv.z * rp[3]);

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 // CTA-uniform loop state is parked in shared memory across the attention phase (the register peak of the
                 // kernel): left to ptxas it goes to local memory and comes back at L2 latency behind the grid barriers
                 // (7 % of all stall samples sat on ONE such reload, profiles/tcd_full_r1e_summary.txt)
-                if (tid == 0) s.misc[57] = step, s.misc[58] = l, s.misc[59] = (int)bar_no + 1;
+                if (tid == 0) s.misc[57] = step, s.misc[58] = l, s.misc[59] = (int)bar_no + ((p.dataflow & 4) ? 0 : 1);
                 const TcdJob &qkv_job = s.jobs[4 * l];
 #ifdef B200LLM_TCD_TRACE
                 int arr_i = (p.trace != nullptr && step == p.trace_step && l == 1 && tid == 0) ? 0 : -1;
@@ -104,9 +104,13 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 tcd_attn_prefetch<HD>(p, qkv_job, s, c, G, bid, tid);
                 phase(4 * l);      // rmsnorm + qkv (raw sums)
                 arrive_stamp();
-                tcd_grid_arrive(p.bar_ctr, tid);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
-                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                if (!(p.dataflow & 4)) {
+                    tcd_grid_arrive(p.bar_ctr, tid);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                    tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                } else {   // data-flow mode: only the CTAs with an attention item wait, for their head's rows
+                    tcd_attn_wait_qkv<HD, GQ>(p, qkv_job, s, c, G, bid, tid);
+                }
                 tcd_trace(p, c.ti, bid, tid, TT_BAR);
                 tcd_attn_phase<HD, GQ>(p, qkv_job, s, c, G, bid, tid);  // rope + kv append + attention
                 step = reinterpret_cast<volatile int *>(s.misc)[57];   // written before the barrier above

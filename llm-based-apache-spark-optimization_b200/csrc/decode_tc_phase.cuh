@@ -56,8 +56,9 @@ __device__ float tcd_prologue(const TcdParams &p, const TcdJob &job, const TcdSm
         for (int i = bid * kTC + tid; i < ng4; i += G * kTC) gz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     if (job.x_src & 0x200) {
-        const int nq4 = (p.n_q + 2 * p.n_kv) * p.head_dim / 4;
-        for (int i = bid * kTC + tid; i < nq4; i += G * kTC) reinterpret_cast<float4 *>(p.qkv)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int nq4 = (p.n_q + 2 * p.n_kv) * p.head_dim / ((p.dataflow & 4) ? 2 : 4);
+        float4 *qz = (p.dataflow & 4) ? reinterpret_cast<float4 *>(p.qkv2) : reinterpret_cast<float4 *>(p.qkv);
+        for (int i = bid * kTC + tid; i < nq4; i += G * kTC) qz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     // phases with a norm (or that seed the residual stream from the embedding) read the whole
     // vector; the others only the chunks (8 values) of the k blocks this CTA streams

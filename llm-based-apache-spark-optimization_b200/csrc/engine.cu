@@ -126,7 +126,7 @@ struct b200llm_engine {
     unsigned *bar_ctr = nullptr;
     unsigned long long *trace = nullptr;
     unsigned long long *samp_cand = nullptr;
-    float2 *tcd_gu2 = nullptr, *tcd_att2 = nullptr;
+    float2 *tcd_gu2 = nullptr, *tcd_att2 = nullptr, *tcd_qkv2 = nullptr;
     size_t tcd_att2_bytes = 0;
     // batch / prefill path
     uint16_t *xb = nullptr, *xb2 = nullptr;
@@ -189,7 +189,7 @@ static int check_cfg(const b200llm_config *c) {
 struct WsLayout {
     size_t h, q, att, act, delta, logits, part_max, part_idx, row_lane, row_pos, row_token, pf_lane, pf_pos,
         pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
-        attn_scratch, mega_jobs, bar_ctr, trace, samp_cand, tcd_gu2, tcd_att2, xb, xb2, qkv_out, gu_out, total;
+        attn_scratch, mega_jobs, bar_ctr, trace, samp_cand, tcd_gu2, tcd_att2, tcd_qkv2, xb, xb2, qkv_out, gu_out, total;
     size_t attn_scratch_bytes, tcd_att2_bytes;
     size_t xb_lo_off, xb2_lo_off;
     int lm_grid, attn_splits;
@@ -250,6 +250,7 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->trace = take(4096 * 8);
     w->samp_cand = take((size_t)kNumSMs * kTcdSampK * 8);   // per-CTA candidate keys of the in-kernel sampler
     w->tcd_gu2 = take((size_t)2 * ffn_l * 8);                  // (sum, count) pairs of the persistent kernel's gate/up phase
+    w->tcd_qkv2 = take((size_t)(nq_l + 2 * nkv_l) * c->head_dim * 8);   // ... and of its qkv phase
     {   // (value, tag) pairs of its attention phase: outputs, split-T partials, their (max, sum, tag, -)
         const size_t ns = (size_t)(kNumSMs / (nkv_l > 0 ? nkv_l : 1) < 1 ? 1 : kNumSMs / (nkv_l > 0 ? nkv_l : 1));
         w->tcd_att2_bytes = nq_l * c->head_dim * 8 + nq_l * ns * c->head_dim * 8 + nq_l * ns * 16;
@@ -558,6 +559,7 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->trace = (unsigned long long *)(b + w.trace);
     e->samp_cand = (unsigned long long *)(b + w.samp_cand);
     e->tcd_gu2 = (float2 *)(b + w.tcd_gu2);
+    e->tcd_qkv2 = (float2 *)(b + w.tcd_qkv2);
     e->tcd_att2 = (float2 *)(b + w.tcd_att2), e->tcd_att2_bytes = w.tcd_att2_bytes;
     const bool hilo = getenv("B200LLM_TC_BF16ACT") == nullptr;  // default: hi + lo operand pairs, ~fp32-accurate activations
     e->xb_lo = hilo ? (int64_t)w.xb_lo_off : 0, e->xb2_lo = hilo ? (int64_t)w.xb2_lo_off : 0;
@@ -862,7 +864,7 @@ static bool tcd_usable(const b200llm_engine *e) {
 static int tcd_dataflow_bits(const b200llm_engine *e) {
     if (e->cfg.tp_size > 1) return 0;   // the tensor-parallel phases keep their grid barriers
     const char *df = getenv("B200LLM_TCD_DATAFLOW");
-    return df ? atoi(df) : 3;
+    return df ? atoi(df) : 7;
 }
 
 static int tcd_prepare(b200llm_engine *e) {
@@ -878,8 +880,9 @@ static int tcd_prepare(b200llm_engine *e) {
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW &w = e->layers[l];
         uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
-        jobs[4 * l + 0] = TcdJob{w.wqkv_tm, w.attn_norm, kl, kl + e->kv_half_stride, e->qkv_out,
-                                 (nq + 2 * nkv) * c.head_dim, c.d, TCD_EPI_ADD, (l == 0 ? TCD_X_EMBED : TCD_X_H) | 0x400};
+        jobs[4 * l + 0] = TcdJob{w.wqkv_tm, w.attn_norm, kl, kl + e->kv_half_stride,
+                                 (e->tcd_dataflow & 4) ? reinterpret_cast<float *>(e->tcd_qkv2) : e->qkv_out, (nq + 2 * nkv) * c.head_dim, c.d,
+                                 (e->tcd_dataflow & 4) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD, (l == 0 ? TCD_X_EMBED : TCD_X_H) | 0x400};
         jobs[4 * l + 1] = TcdJob{w.wo_tm, nullptr, nullptr, nullptr, row_out, c.d, qd, TCD_EPI_ADD, TCD_X_ATT | 0x100};   // 0x100: clears the gate/up sums
         jobs[4 * l + 2] = TcdJob{w.wgu_tm, w.mlp_norm, nullptr, nullptr, (e->tcd_dataflow & 1) ? reinterpret_cast<float *>(e->tcd_gu2) : e->gu_out,
                                  2 * ffn, c.d, (e->tcd_dataflow & 1) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD, TCD_X_H | 0x400 | 0x200};   // 0x200: clears the qkv sums
@@ -898,7 +901,7 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
     const b200llm_config &c = e->cfg;
     if (!e->tcd_ready || e->tcd_dataflow != tcd_dataflow_bits(e)) B200_TRY(tcd_prepare(e));
     TcdParams p{};
-    p.dataflow = e->tcd_dataflow, p.gu2 = e->tcd_gu2, p.att2 = e->tcd_att2;
+    p.dataflow = e->tcd_dataflow, p.gu2 = e->tcd_gu2, p.att2 = e->tcd_att2, p.qkv2 = e->tcd_qkv2;
     p.jobs = reinterpret_cast<const TcdJob *>(e->mega_jobs), p.n_layers = c.n_layers;
     p.d = c.d, p.n_q = e->nq_l, p.n_kv = e->nkv_l, p.head_dim = c.head_dim, p.ffn = e->ffn_l, p.vocab = e->vocab_l;
     p.vocab_global = c.vocab, p.tp_rank = c.tp_rank, p.tp_size = c.tp_size;
@@ -945,7 +948,8 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
     B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim * 4, e->stream));
     B200_CUDA_OK(cudaMemsetAsync(e->gu_out, 0, (size_t)2 * e->ffn_l * 4, e->stream));
     if (p.dataflow & 1) B200_CUDA_OK(cudaMemsetAsync(e->tcd_gu2, 0, (size_t)2 * e->ffn_l * 8, e->stream));
-    if (p.dataflow & 2) B200_CUDA_OK(cudaMemsetAsync(e->tcd_att2, 0, e->tcd_att2_bytes, e->stream));   // no tag of an earlier launch survives
+    if (p.dataflow & 2) B200_CUDA_OK(cudaMemsetAsync(e->tcd_att2, 0, e->tcd_att2_bytes, e->stream));
+    if (p.dataflow & 4) B200_CUDA_OK(cudaMemsetAsync(e->tcd_qkv2, 0, (size_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim * 8, e->stream));   // no tag of an earlier launch survives
     e->last_rows = 1, e->last_logit_rows = 1;
     return tcd_decode_launch(p, e->stream);
 }

@@ -69,8 +69,10 @@ struct TcdParams {
     // L2 round trips) becomes one polling load.  bit 0: gate/up sums -> down_proj.  bit 1: attention -> o_proj: the
     // attention items (one writer per value) store (value, tag) pairs, tag = step * n_layers + layer + 1 of this launch
     // (the host clears the buffer before a launch), and o_proj's prologue polls the pairs of its k-slices for the tag.
+    // bit 2: q|k|v sums -> attention: a CTA with an attention item polls the counts of its head's rows, then runs the item.
     int32_t dataflow;
     float2 *gu2;          // [2 ffn] (sum, count) pairs of the gate/up phase
+    float2 *qkv2;         // [(n_q + 2 n_kv) head_dim] (sum, count) pairs of the qkv phase
     float2 *att2;         // [n_q head_dim] (value, tag) | part_o2 [n_q, n_splits, head_dim] (value, tag) | part_ml2 [n_q, n_splits] float4 (max, sum, tag, -)
     int32_t tmem_slots;   // weight stages (0..12) the issuer may park in tensor memory while it waits (decode_tc.cu)
     int32_t poll_ns;      // pause of the issuer between two probes while it waits for a phase's operand

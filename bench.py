@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--max-rows", type=int, default=256, help="rows per forward pass (prefill chunk size / batch limit)")
     ap.add_argument("--no-mega", action="store_true", help="multi-kernel CUDA-graph path instead of the persistent kernel")
     ap.add_argument("--attn-splits", type=int, default=0)
+    ap.add_argument("--no-tp-leg", action="store_true", help="skip the tp_7b leg (duckdb-nsql-7B tensor parallel over the --gpus ranks, config 4)")
     ap.add_argument("--no-batch", action="store_true", help="skip the bs64 leg (Llama-3.2-1B, 64 sequences, config 2)")
     return ap.parse_args()
 
@@ -245,6 +246,58 @@ def bench_batch(model, bs, steps, device):
             "steps": steps, "mean_ctx": mean_ctx, "gpu_launches": int(launches)}
 
 
+def bench_tp_7b(rank, world, local, n_new=64):
+    """Config 4: duckdb-nsql-7B, 2048 + 24 synthetic prompt ids, 64 new tokens, tensor parallel over all
+    `world` ranks of the node (one sequence, strong scaling).  Collective: every rank calls it."""
+    import ctypes as C
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from b200llm import Engine, _lib, geometry, tp, weights
+    geo = geometry.resolve("duckdb-nsql")
+    n_prompt = 2048 + 24
+    w = weights.random_init(geo, 0xB200, local, tp_rank=rank, tp_size=world)
+    eng = Engine(geo, w, device=local, max_lanes=2, max_ctx=n_prompt + n_new + 64, max_rows=256, tp_rank=rank, tp_size=world,
+                 nccl_id=tp.exchange_unique_id())
+    tp.connect_peers(eng)
+    prompt = np.random.default_rng(4).integers(0, geo.vocab, n_prompt, dtype=np.int32)      # the same stream on every rank
+    lane = eng.open_lane()
+    eng.prefill(lane, prompt)
+    eng.sync()
+    eng.prefill(lane, prompt)            # timed warm (the first pass pays tensor-map creation / connection set-up)
+    eng.sync()
+    ttft = eng.timing().prefill_ms
+    eng.decode([lane], 8, read=False)    # warm-up
+    eng.set_lane(lane, int(prompt[0]), n_prompt)
+    eng._ensure_pages(lane, n_prompt + n_new)
+    eng.sync()
+    dist.barrier()
+    torch.cuda.synchronize()
+    eng.decode([lane], n_new, read=False)
+    eng.sync()
+    tm = eng.timing()
+    us = C.c_float()
+    _lib.check(_lib.lib.b200llm_debug_tp_allreduce_us(eng._h, 1, 256, C.byref(us)))
+    t = torch.tensor([tm.decode_ms / n_new, ttft, us.value], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ttft, ar_us = float(t[0]), float(t[1]), float(t[2])
+    mean_ctx = n_prompt + (n_new - 1) / 2.0
+    per_gpu_gbs = geo.step_bytes(1, mean_ctx) / world / (ms * 1e-3) / 1e9
+    fl = prefill_flops(geo, n_prompt)
+    out = {"model": "duckdb-nsql", "tp": world, "prompt_ids": n_prompt, "new_tokens": n_new, "ms_per_step": ms, "tok_s": 1000.0 / ms,
+           "ttft_ms": ttft, "ttft_frac_of_sustained": fl / (ttft * 1e-3) / 1e12 / sustained_tflops() / world,
+           "frac_per_gpu": per_gpu_gbs / peaks()[0], "achieved_gbs_per_gpu": per_gpu_gbs,
+           "allreduce_us": ar_us, "allreduce_share": 2 * geo.n_layers * ar_us * 1e-3 / ms,
+           "allreduce_share_what": "2 x n_layers reductions per token x the time of one [1, d] fp32 all-reduce through the engine's "
+                                   "peer-memory kernel, measured back to back in this run, over the step time (an estimate: inside the "
+                                   "persistent kernel the reduction is a phase between two grid barriers)",
+           "gpu_launches": int(tm.kernel_launches)}
+    eng.close()
+    del eng, w
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_b200(args):
     import numpy as np
     import torch
@@ -413,6 +466,17 @@ def run_b200(args):
                                   "repeat_penalty 1.1, random seed)",
                        "decode_tok_s": stats["sampled"]["eval_count"] / (stats["sampled"]["eval_ns"] * 1e-9), "what": what}
 
+    tp_7b = None
+    if world > 1 and not tp_mode and args.model == "llama3.2" and bs == 1 and not args.no_tp_leg:
+        if model_rt is not None:
+            from b200llm import runtime
+            runtime.unload_all()
+            model_rt = None
+        else:
+            eng.close()
+        torch.cuda.empty_cache()
+        tp_7b = bench_tp_7b(rank, world, local)
+
     bs64 = None
     if rank == 0 and world == 1 and bs == 1 and args.model == "llama3.2" and not args.no_batch:
         if model_rt is not None:
@@ -463,6 +527,8 @@ def run_b200(args):
             line["e2e_sampled"] = e2e_sampled
         if bs64 is not None:
             line["bs64"] = bs64
+        if tp_7b is not None:
+            line["tp_7b"] = tp_7b
         if not args.no_cpu_baseline and world == 1:
             v, dt, cores = cpu_decode_tok_s(args.model, 64, 24, 2)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
@@ -471,7 +537,7 @@ def run_b200(args):
     if model_rt is not None:
         from b200llm import runtime
         runtime.unload_all()
-    elif not via_runtime:
+    elif not via_runtime and tp_7b is None:
         eng.close()
     if world > 1:
         dist.destroy_process_group()

@@ -179,6 +179,12 @@ int b200llm_set_lane(b200llm_engine *e, int32_t lane, int32_t next_token, int32_
  * cache): the window must hold what a full prefill of the same prompt would have left in it. */
 int b200llm_set_history(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t n, int32_t pos0);
 
+/* Tensor parallel, measurement only (no counterpart in the reference): time `iters` back-to-back all-reduces of a
+ * [rows, d] fp32 block through the engine's own reduction path (the one-shot kernel over NVLink peer memory once
+ * b200llm_tp_import has run, else ncclAllReduce + add).  Collective: every rank of the group calls it with the same
+ * arguments.  The residual stream is used as scratch.  bench.py reports the all-reduce share of a decode step from it. */
+int b200llm_debug_tp_allreduce_us(b200llm_engine *e, int32_t rows, int32_t iters, float *us_per_call);
+
 /* ---- the hot path ---------------------------------------------------------------- */
 /* Prefill: run `n` prompt ids (host buffer) of `lane` starting at position pos0, append
  * their K/V to the lane's pages, sample the first new token into the lane. Asynchronous. */
@@ -280,8 +286,12 @@ int b200llm_op_attn_scratch_bytes(int32_t bs, int32_t n_q, int32_t n_kv, int32_t
  * the sizes -- use b200llm_op_attn_decode with your own scratch then.
  *
  * No cudaMalloc, cudaFree or other allocating call is made.  The first call on a device looks
- * up the buffer's device address (cudaGetSymbolAddress, with that device current); make that
- * first call outside any stream capture.  Every call shares the one buffer and clears its
+ * up the buffer's device address (cudaGetSymbolAddress, with that device current), and if it is
+ * also the first use of this library on that device, the CUDA runtime loads the library's module
+ * there at that moment, which does reserve device memory for the code and for the 4 MiB buffer:
+ * make that first call early, outside any stream capture, while memory can still be had.  It
+ * returns B200LLM_ENODEV, before touching `stream`, when the current device is not an sm_100
+ * part.  Every call shares the one buffer and clears its
  * ticket area on `stream` before launching, so calls that may overlap on the GPU (different
  * streams, or different threads) race with each other: serialise them. */
 int b200llm_op_attn_decode_static(const b200llm_attn_args *a, void *stream);

@@ -98,6 +98,7 @@ SYMBOLS = {
     "b200llm_tp_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200llm_tp_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "b200llm_debug_read_trace": (C.c_int, [C.c_void_p, _P(C.c_uint64), C.c_int32]),
+    "b200llm_debug_tp_allreduce_us": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _P(C.c_float)]),
     "b200llm_op_gemv": (C.c_int, [_P(GemvArgs), C.c_void_p]),
     "b200llm_op_gemv_grid": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P(C.c_int32)]),
     "b200llm_op_gemv_tm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),

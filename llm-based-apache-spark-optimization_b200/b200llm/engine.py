@@ -69,7 +69,7 @@ class Engine:
         torch.cuda.set_device(device)
         self.stream = torch.cuda.Stream(device)
         self._id_buf = C.create_string_buffer(nccl_id, 128) if nccl_id else None
-        cfg = _lib.Config(_lib.ABI_VERSION, geo.d, geo.n_layers, geo.n_q, geo.n_kv, geo.head_dim, geo.ffn, geo.vocab,
+        cfg = _lib.Config(_lib.ABI_VERSION, geo.d, geo.n_layers, geo.n_q, geo.n_kv, geo.head_dim, weights.ffn_cfg, geo.vocab,
                           geo.rms_eps, PAGE_TOKENS, max_lanes, self.max_pages_per_lane, max_rows, tp_rank, tp_size,
                           device, int(use_graphs), int(use_pdl), attn_splits, int(use_megakernel), int(use_tc), self.stream.cuda_stream,
                           C.cast(self._id_buf, C.c_void_p) if self._id_buf else None)

@@ -14,7 +14,8 @@ from collections import deque
 from dataclasses import dataclass, field
 from typing import Deque, Dict, Iterable, List, Optional, Sequence
 
-from .engine import Engine, GenTiming, SamplingParams
+from ._lib import EINVAL, B200LLMError
+from .engine import MAX_DECODE_STEPS, PAGE_TOKENS, Engine, GenTiming, SamplingParams
 from .prefix_cache import PrefixCache
 
 
@@ -86,6 +87,12 @@ class Scheduler:
     def _admit(self, req: Request):
         eng = self.engine
         try:
+            # a request is checked against the lane context here, so that it alone fails (or is cut to what fits):
+            # found later, inside a batched decode call, the error would take every co-batched request with it
+            max_ctx = eng.max_pages_per_lane * PAGE_TOKENS
+            if len(req.prompt_ids) < 1 or len(req.prompt_ids) >= max_ctx:
+                raise B200LLMError(EINVAL, f"prompt of {len(req.prompt_ids)} ids does not fit the {max_ctx}-token context")
+            req.max_new = max(1, min(req.max_new, max_ctx - len(req.prompt_ids)))
             req.lane = eng.open_lane()
             eng.set_sampling(req.lane, req.sampling)
             shared, pages = self.cache.lookup(req.prompt_ids) if self.cache else (0, [])
@@ -128,11 +135,21 @@ class Scheduler:
             # a lone request with no stop ids can run to its budget in one call; otherwise step in
             # chunks so that finished lanes leave and queued requests join
             lone = len(lanes) == 1 and not self._queue and not self._active[lanes[0]].stop_ids
-            n = max(1, budget if lone else min(budget, self.chunk))
+            n = min(MAX_DECODE_STEPS, max(1, budget if lone else min(budget, self.chunk)))
+            # pages for the whole call, lane by lane: a lane that cannot get them (pool exhausted while other lanes pin
+            # prefix pages) is retired with its own error, the others decode on
+            for ln in list(lanes):
+                try:
+                    eng._ensure_pages(ln, eng.pos[ln] + n)
+                except BaseException as e:  # noqa: BLE001
+                    self._finish(self._active[ln], e)
+                    lanes.remove(ln)
+            if not lanes:
+                continue
             try:
                 out = eng.decode(lanes, n)
                 t = eng.timing()
-            except BaseException as e:  # noqa: BLE001
+            except BaseException as e:  # noqa: BLE001 - an engine fault: nothing in the batch can be trusted
                 for ln in list(lanes):
                     self._finish(self._active[ln], e)
                 continue

@@ -52,6 +52,20 @@ class PackedWeights:
     tp_size: int
     tensors: List[Tuple[int, int, torch.Tensor]] = field(default_factory=list)   # (kind, layer, tensor)
 
+    @property
+    def ffn_local(self) -> int:
+        """MLP units of this rank's shard.  Under tensor parallel the shard is padded with zero units to a multiple of
+        64 (duckdb-nsql over 8 ranks: 11008 / 8 = 1376 -> 1408), so that gate/up rows come in whole 128-row tiles and
+        down_proj's K in whole 64-wide blocks: the tcgen05 kernels then serve every TP degree.  A zero gate/up unit
+        gives silu(0) * 0 = 0 and meets zero down_proj columns, so results are unchanged bit for bit."""
+        ffn_l = self.geo.ffn // self.tp_size
+        return ffn_l if self.tp_size == 1 else (ffn_l + 63) // 64 * 64
+
+    @property
+    def ffn_cfg(self) -> int:
+        """The `ffn` to put into b200llm_config (the engine divides it by tp_size)."""
+        return self.ffn_local * self.tp_size
+
     def descs(self):
         arr = (_lib.TensorDesc * len(self.tensors))()
         for i, (kind, layer, t) in enumerate(self.tensors):
@@ -114,6 +128,8 @@ def tile_major(w: torch.Tensor) -> torch.Tensor:
 def tile_major_ok(geo, tp_size: int = 1) -> bool:
     """Can every matrix of one rank's shard be cut into [128 x 64] tiles?"""
     nq, nkv, ffn, vocab = geo.n_q // tp_size, geo.n_kv // tp_size, geo.ffn // tp_size, geo.vocab // tp_size
+    if tp_size > 1:
+        ffn = (ffn + 63) // 64 * 64     # PackedWeights.ffn_local: the shard is padded with zero units
     qkv = (nq + 2 * nkv) * geo.head_dim
     shapes = [(qkv, geo.d), (geo.d, nq * geo.head_dim), (2 * ffn, geo.d), (geo.d, ffn)]
     # the lm_head's rows are padded to the next tile (tile_major), the other matrices must fit as they are
@@ -166,9 +182,13 @@ def pack_layer(geo: Geometry, layer: int, sd: Dict[str, torch.Tensor], tp_rank: 
                         sd[p + "self_attn.o_proj.weight"][:, tp_rank * nq_l * hd:(tp_rank + 1) * nq_l * hd].contiguous()))
     g = sd[p + "mlp.gate_proj.weight"][tp_rank * ffn_l:(tp_rank + 1) * ffn_l]
     u = sd[p + "mlp.up_proj.weight"][tp_rank * ffn_l:(tp_rank + 1) * ffn_l]
-    out.tensors.append((_lib.W_GATE_UP, layer, torch.stack((g, u), 1).reshape(2 * ffn_l, geo.d).contiguous()))
-    out.tensors.append((_lib.W_DOWN, layer,
-                        sd[p + "mlp.down_proj.weight"][:, tp_rank * ffn_l:(tp_rank + 1) * ffn_l].contiguous()))
+    dn = sd[p + "mlp.down_proj.weight"][:, tp_rank * ffn_l:(tp_rank + 1) * ffn_l]
+    pad = out.ffn_local - ffn_l if tp_size > 1 else 0   # zero MLP units that round the shard up to whole tiles (PackedWeights.ffn_local)
+    if pad > 0:
+        g, u = torch.cat((g, g.new_zeros(pad, geo.d))), torch.cat((u, u.new_zeros(pad, geo.d)))
+        dn = torch.cat((dn, dn.new_zeros(geo.d, pad)), 1)
+    out.tensors.append((_lib.W_GATE_UP, layer, torch.stack((g, u), 1).reshape(2 * (ffn_l + pad), geo.d).contiguous()))
+    out.tensors.append((_lib.W_DOWN, layer, dn.contiguous()))
     out.tensors.append((_lib.W_ATTN_NORM, layer, sd[p + "input_layernorm.weight"].contiguous()))
     out.tensors.append((_lib.W_MLP_NORM, layer, sd[p + "post_attention_layernorm.weight"].contiguous()))
 

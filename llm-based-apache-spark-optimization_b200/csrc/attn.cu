@@ -315,12 +315,8 @@ template <int HD, int G>
 static int launch_attn(const AttnDev &d, cudaStream_t stream, bool pdl) {
     constexpr size_t smem = (size_t)kAttnWarps * kAttnStages * 2 * kPT * HD * 2 +
                             (size_t)kAttnWarps * G * (HD + 2) * 4 + kAttnWarps * kAttnStages * 8;
-    static bool attr_set = false;
-    if (!attr_set) {
-        B200_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)smem));
-        attr_set = true;
-    }
+    // per launch: the attribute belongs to the (function, device) pair, and callers may use several devices and threads
+    B200_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     LaunchCfg lc(dim3(d.a.n_splits, d.a.n_kv, d.a.bs), dim3(kAttnWarps * 32), smem, stream, pdl);
     B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, attn_decode_kernel<HD, G>, d));
     return B200LLM_OK;
@@ -399,11 +395,22 @@ extern "C" int b200llm_op_attn_decode_static(const b200llm_attn_args *a, void *s
     B200_REQUIRE(a && a->q && a->out && a->k_pages && a->v_pages && a->row_lane && a->row_pos && a->page_table,
                  "op_attn_decode_static: NULL argument");
     {
-        int n_dev = 0;
+        int n_dev = 0, cur = 0, major = 0;
         if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
             set_error("no CUDA device: this library has no CPU fallback");
             return B200LLM_ENODEV;
         }
+        B200_CUDA_OK(cudaGetDevice(&cur));
+        B200_CUDA_OK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, cur));
+        if (major != 10) {
+            set_error("current device is sm_%dx; this library is built for sm_100a (B200) only", major);
+            return B200LLM_ENODEV;
+        }
+    }
+    {
+        const int G = a->n_kv > 0 ? a->n_q / a->n_kv : 0;
+        const bool known = (a->head_dim == 128 && G >= 1 && G <= 4) || (a->head_dim == 64 && (G == 1 || G == 2 || G == 4));
+        B200_REQUIRE(known, "attn static: unsupported head_dim %d / group %d", a->head_dim, G);   // before anything is queued on the stream
     }
     B200_REQUIRE(a->page_tokens == kPT, "attn static: page_tokens must be %d (got %d)", kPT, a->page_tokens);
     B200_REQUIRE(a->n_kv > 0 && a->n_q % a->n_kv == 0, "attn static: n_q %d not a multiple of n_kv %d", a->n_q, a->n_kv);

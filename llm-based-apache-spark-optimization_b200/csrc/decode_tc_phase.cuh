@@ -301,6 +301,21 @@ __device__ __forceinline__ void tcd_st_release_sys(unsigned *q, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(q), "r"(v) : "memory");
 }
 
+// bounded wait for a peer's flag (see tp_wait_flag in tp_ar.cu): 2 s, then the local error word is set and the kernel goes on
+__device__ __forceinline__ bool tcd_wait_flag(const unsigned *f, unsigned want, unsigned *err) {
+    if (tcd_ld_acquire_sys(f) == want) return true;
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (tcd_ld_acquire_sys(f) != want) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > 2000000000ull) {
+            atomicExch(err, 1u);
+            return false;
+        }
+    }
+    return true;
+}
+
 __device__ void tcd_allreduce_phase(const TcdParams &p, const TcdSmem &s, int G, int bid, int tid) {
     const unsigned sq = (unsigned)s.misc[62] + 1u;
     const int phase = (int)(sq & 1u);
@@ -319,8 +334,7 @@ __device__ void tcd_allreduce_phase(const TcdParams &p, const TcdSmem &s, int G,
         if (tid < p.tp_size && tid != p.tp_rank) {
             tcd_st_release_sys(p.ar_flags[tid] + ((size_t)phase * p.tp_size + p.tp_rank) * p.ar_max_slices + j, sq);
             const unsigned *f = p.ar_flags[p.tp_rank] + ((size_t)phase * p.tp_size + tid) * p.ar_max_slices + j;
-            while (tcd_ld_acquire_sys(f) != sq) {
-            }
+            tcd_wait_flag(f, sq, p.ar_seq + 3);
         }
         bar_sync(1, kTC);
         if (live) {
@@ -356,8 +370,7 @@ __device__ int tcd_token_exchange(const TcdParams &p, TcdCtx &c, const TcdSmem &
         unsigned long long v = mine;
         if (tid != p.tp_rank) {
             const unsigned *f = p.tok_flags[p.tp_rank] + (size_t)phase * p.tp_size + tid;
-            while (tcd_ld_acquire_sys(f) != sq) {
-            }
+            tcd_wait_flag(f, sq, p.ar_seq + 3);
             v = *reinterpret_cast<volatile unsigned long long *>(p.tok_inbox[p.tp_rank] + (size_t)phase * p.tp_size + tid);
         }
         s.red[48 + tid] = __uint_as_float((unsigned)(v & 0xffffffffull));

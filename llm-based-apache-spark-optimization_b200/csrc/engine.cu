@@ -691,6 +691,19 @@ static int tp_allreduce_add(b200llm_engine *e, int rows) {
     return B200LLM_OK;
 }
 
+// Tensor parallel: did a wait for a peer time out in one of the kernels queued so far?  (Call with the stream drained.)
+static int tp_check_peers(b200llm_engine *e) {
+    if (e->cfg.tp_size <= 1 || !e->ar_seq) return B200LLM_OK;
+    unsigned err = 0;
+    B200_CUDA_OK(cudaMemcpy(&err, e->ar_seq + 3, 4, cudaMemcpyDeviceToHost));
+    if (err) {
+        set_error("tensor parallel: rank %d waited 2 s for a peer inside a kernel (a rank left the lock-step); results of "
+                  "this engine are invalid from that call on", e->cfg.tp_rank);
+        return B200LLM_ENCCL;
+    }
+    return B200LLM_OK;
+}
+
 // final norm + lm_head GEMV + sampler (vocab-parallel under tensor parallel: the ranks' (max, argmax) partials are gathered)
 static int lm_head_and_sample(b200llm_engine *e, const PassRows &pr, bool advance) {
     const b200llm_config &c = e->cfg;
@@ -1205,7 +1218,7 @@ int b200llm_read_tokens(b200llm_engine *e, int32_t *out, int32_t n_steps, int32_
                  "read_tokens: bad arguments");
     B200_CUDA_OK(cudaMemcpyAsync(out, e->gen_out, (size_t)n_steps * n_lanes * 4, cudaMemcpyDeviceToHost, e->stream));
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));
-    return B200LLM_OK;
+    return tp_check_peers(e);
 }
 
 int b200llm_read_lane(b200llm_engine *e, int32_t lane, int32_t *next_token, int32_t *pos) {
@@ -1234,7 +1247,7 @@ int b200llm_step_logits(b200llm_engine *e, int32_t row, float *out, int32_t n) {
 int b200llm_sync(b200llm_engine *e) {
     B200_REQUIRE(e, "engine is NULL");
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));
-    return B200LLM_OK;
+    return tp_check_peers(e);
 }
 
 int b200llm_last_timing(b200llm_engine *e, b200llm_timing *t) {
@@ -1248,6 +1261,27 @@ int b200llm_last_timing(b200llm_engine *e, b200llm_timing *t) {
 }
 
 void *b200llm_stream(b200llm_engine *e) { return e ? (void *)e->stream : nullptr; }
+
+int b200llm_debug_tp_allreduce_us(b200llm_engine *e, int32_t rows, int32_t iters, float *us_per_call) {
+    B200_TRY(require_ready(e));
+    B200_REQUIRE(us_per_call && e->cfg.tp_size > 1 && rows >= 1 && rows <= e->cfg.max_rows && iters >= 1 && iters <= 100000,
+                 "debug_tp_allreduce_us: needs a tensor-parallel engine, 1 <= rows <= max_rows, 1 <= iters <= 100000");
+    // `iters` reductions of a [rows, d] fp32 block back to back, as the per-phase path issues them (collective: every
+    // rank calls this with the same arguments); the residual stream is scratch here and is left changed
+    cudaEvent_t a, b;
+    B200_CUDA_OK(cudaEventCreate(&a));
+    B200_CUDA_OK(cudaEventCreate(&b));
+    B200_CUDA_OK(cudaMemsetAsync(e->delta, 0, (size_t)rows * e->cfg.d * 4, e->stream));
+    B200_CUDA_OK(cudaEventRecord(a, e->stream));
+    for (int i = 0; i < iters; ++i) B200_TRY(tp_allreduce_add(e, rows));
+    B200_CUDA_OK(cudaEventRecord(b, e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+    float ms = 0.f;
+    B200_CUDA_OK(cudaEventElapsedTime(&ms, a, b));
+    cudaEventDestroy(a), cudaEventDestroy(b);
+    *us_per_call = ms * 1000.f / (float)iters;
+    return tp_check_peers(e);
+}
 
 int b200llm_debug_read_trace(b200llm_engine *e, uint64_t *out, int32_t n) {
     B200_REQUIRE(e && e->ws && out && n >= 1 && n <= 4096, "debug_read_trace: bad arguments");

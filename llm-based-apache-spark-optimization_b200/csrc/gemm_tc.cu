@@ -296,11 +296,8 @@ int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out
     int stages = (200 * 1024) / stage_bytes;
     p.stages = stages > 8 ? 8 : (stages < 2 ? 2 : stages);
     const size_t smem = (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16 + 1024;
-    static bool attr_set = false;
-    if (!attr_set) {
-        B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
+    // per launch: the attribute belongs to the (function, device) pair, and callers may use several devices and threads
+    B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     LaunchCfg lc(dim3(tiles, ks), dim3(kTcThreads), smem, stream, pdl);
     B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, gemm_tc_kernel, *reinterpret_cast<const CUtensorMap *>(map_w),
                                     *reinterpret_cast<const CUtensorMap *>(map_x),

@@ -331,12 +331,8 @@ gemv_kernel(const __grid_constant__ GemvDev p) {
 
 template <int BS, int UPT>
 static int launch_one(const GemvDev &dev, const GemvPlan &pl, cudaStream_t stream, bool pdl) {
-    static bool attr_set = false;  // per (BS, UPT) instantiation
-    if (!attr_set) {
-        B200_CUDA_OK(cudaFuncSetAttribute(gemv_kernel<BS, UPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          220 * 1024));
-        attr_set = true;
-    }
+    // per launch: the attribute belongs to the (function, device) pair, and callers may use several devices and threads
+    B200_CUDA_OK(cudaFuncSetAttribute(gemv_kernel<BS, UPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
     LaunchCfg lc(dim3(pl.grid), dim3(pl.nt + 32), pl.smem, stream, pdl);
     B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, gemv_kernel<BS, UPT>, dev));
     return B200LLM_OK;

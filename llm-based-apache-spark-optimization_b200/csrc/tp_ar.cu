@@ -28,7 +28,7 @@ struct TpArArgs {
     const float *delta;    // [n] this rank's partial result
     float *inbox[kTpMaxRanks];      // inbox base of every rank (own included), peer-mapped
     unsigned *flags[kTpMaxRanks];   // flag base of every rank
-    unsigned *seq;         // [2]: launch sequence number, finished-CTA ticket (local)
+    unsigned *seq;         // local: [0] launch sequence number, [1] finished-CTA ticket, [2] token exchanges, [3] error word
     int32_t n;             // floats, multiple of 4
     int32_t rank, size;
     int32_t slot_floats;   // capacity of one inbox slot (floats)
@@ -42,6 +42,24 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
 }
 __device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Bounded wait for a peer's flag: a rank that has left the lock-step (a failed call, a crash, a different code path)
+// must not leave its peers spinning inside a kernel that cannot be cancelled.  After 2 s the waiter records the
+// failure in the local error word (seq[3]; the engine reports it as B200LLM_ENCCL on the next read / sync) and goes
+// on, so the launch ends; its results are garbage and flagged as such.
+__device__ __forceinline__ bool tp_wait_flag(const unsigned *f, unsigned want, unsigned *err) {
+    if (ld_acquire_sys(f) == want) return true;
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (ld_acquire_sys(f) != want) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > 2000000000ull) {
+            atomicExch(err, 1u);
+            return false;
+        }
+    }
+    return true;
 }
 
 constexpr int kArThreads = 256;
@@ -69,8 +87,7 @@ __global__ void __launch_bounds__(kArThreads) tp_allreduce_add_kernel(const __gr
         // wait for the same slice of every peer in my own inbox
         if (threadIdx.x < a.size && threadIdx.x != a.rank) {
             const unsigned *f = a.flags[a.rank] + ((size_t)phase * a.size + threadIdx.x) * a.max_slices + j;
-            while (ld_acquire_sys(f) != s) {
-            }
+            tp_wait_flag(f, s, a.seq + 3);
         }
         __syncthreads();
         if (live) {
@@ -107,8 +124,8 @@ int tp_allreduce_add_launch(float *h, const float *delta, int n, float *const *i
     a.h = h, a.delta = delta, a.seq = seq, a.n = n, a.rank = rank, a.size = size;
     a.slot_floats = slot_floats, a.max_slices = max_slices;
     for (int r = 0; r < size; ++r) a.inbox[r] = inbox[r], a.flags[r] = flags[r];
-    // every CTA of the launch must see the same sequence number, i.e. start before the last one finishes: keep the
-    // grid small enough to be resident at once (it is: <= 148 CTAs of 256 threads, no shared memory)
+    // every CTA of the launch reads the same sequence number: it is advanced only by the LAST CTA to finish (ticket
+    // in seq[1]), and CTAs of the next launch on the stream start after this one has ended
     const int grid = n_slices < kNumSMs ? n_slices : kNumSMs;
     tp_allreduce_add_kernel<<<grid, kArThreads, 0, stream>>>(a);
     B200_CUDA_OK(cudaGetLastError());

@@ -175,8 +175,18 @@ def test_golden_parity_full_size(fname, name, mega, tc, golden_dir):
             pytest.xfail(f"near-tie at step {s} (oracle margin {margins[s]:.2e}); tokens equal before it")
     assert got == toks
     l63 = eng.logits(0)
-    assert float(np.abs(l63[probe] - g["probe_kvbf16"][63]).max() / g["absmax_kvbf16"][63]) <= TIGHT_TOL
+    d_first = float(np.abs(l0[probe] - g["probe_kvbf16"][0]).max() / g["absmax_kvbf16"][0])
+    d_last = float(np.abs(l63[probe] - g["probe_kvbf16"][63]).max() / g["absmax_kvbf16"][63])
+    assert d_last <= TIGHT_TOL
     assert float(np.abs(l63[g["top_ids"][63]] - g["top_vals"][63]).max() / g["absmax_kvbf16"][63]) <= TIGHT_TOL
+    # distance to the nothing-rounded fp32 oracle (north_star: 1e-2), bounded by twice the oracle's own bf16-KV distance
+    # where that alone exceeds it (DESIGN.md "Parity"); the measured distances go to the test log
+    truth = max(float(np.abs(l0[probe] - g["probe_fp32"][0]).max() / g["absmax_fp32"][0]),
+                float(np.abs(l63[probe] - g["probe_fp32"][63]).max() / g["absmax_fp32"][63]))
+    oracle_own = float((np.abs(g["probe_kvbf16"] - g["probe_fp32"]).max(1) / g["absmax_fp32"]).max())
+    print(f"{name} mega={mega} tc={tc}: logits vs the oracle in the engine's storage model {d_first:.1e} (step 0) / {d_last:.1e} "
+          f"(step 63); vs the fp32 oracle {truth:.1e} (the oracle's own bf16-KV mode is {oracle_own:.1e} away from it)")
+    assert truth <= max(LOGIT_TOL, 2 * oracle_own)
     eng.close()
 
 
@@ -493,4 +503,40 @@ def test_sampled_decode_full_size_one_launch(golden_dir):
     assert tm.kernel_launches == 1
     first = next((i for i, (a, b) in enumerate(zip(again, toks)) if a != b), None)
     assert first is None or slacks[first] < 1e-4, f"one launch differs from 32 launches at step {first} (slack {slacks[first]:.2e})"
+    eng.close()
+
+
+def test_scheduler_fails_only_the_offending_request():
+    """A request that does not fit the lane context gets its own error; requests batched with it finish normally,
+    and a token budget beyond the context is cut to what fits instead of failing the batch."""
+    import threading
+    from b200llm import SamplingParams, _lib
+    from b200llm.scheduler import Scheduler
+    geo = lo.GEOMETRIES["tiny"]
+    sd = lo.make_weights(geo, 0xB200, sigma=0.08)
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    eng = _engine("tiny", sd, max_lanes=4, max_ctx=96, max_rows=8)
+    sched = Scheduler(eng, chunk=4)
+    good = [wg.gen_tokens(12 + 5 * i, 700 + i, geo.vocab) for i in range(3)]
+    want = [orc.greedy(p, 10)[0] for p in good]
+    too_long = wg.gen_tokens(200, 9, geo.vocab)                  # > 96-token context
+    res = {}
+
+    def call(key, prompt, n):
+        try:
+            res[key] = sched.generate_ids(prompt, n, SamplingParams(temperature=0.0))[0]
+        except Exception as e:  # noqa: BLE001
+            res[key] = e
+    ts = [threading.Thread(target=call, args=(i, good[i], 10)) for i in range(3)]
+    ts.append(threading.Thread(target=call, args=("long", too_long, 10)))
+    ts.append(threading.Thread(target=call, args=("greedy_budget", good[0], 10_000)))   # budget >> context: cut, not failed
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=120)
+    assert isinstance(res["long"], _lib.B200LLMError) and res["long"].code == _lib.EINVAL
+    assert [res[i] for i in range(3)] == want
+    assert isinstance(res["greedy_budget"], list) and len(res["greedy_budget"]) == 96 - len(good[0])
+    assert res["greedy_budget"][:10] == want[0]
+    sched.shutdown()
     eng.close()

@@ -123,7 +123,11 @@ def test_gemv_qkv_rope_kv_append(name, bs):
         # exactly-rounded in all but borderline elements
         same = (kp[page, :, slot].cpu().view(torch.int16) == kr[:, perm].to(torch.bfloat16).view(torch.int16)).float().mean()
         assert same > 0.97
-    assert int((kp != 0).any(-1).any(1).sum()) == bs * 1 * 1 * 1 or True
+    # nothing but the appended rows was written: one (page, token slot) per batch row, every kv head of it
+    written = (kp != 0).any(-1).cpu()                            # [page, kv head, slot]
+    assert int(written.sum()) == bs * nkv
+    for b in range(bs):
+        assert bool(written[2 + b, :, int(pos[b]) % 16].all())
 
 
 @pytest.mark.parametrize("V,K,bs", [(1024, 256, 1), (32000, 4096, 2), (128256, 2048, 1), (128256, 3072, 4)])

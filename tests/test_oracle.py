@@ -70,6 +70,26 @@ def test_oracle_matches_hf_llama(name):
     assert hf == toks
 
 
+@pytest.mark.parametrize("name", sorted(lo.GEOMETRIES))
+def test_inv_freq_bit_equal_to_transformers_for_every_geometry(name):
+    """The RoPE table of every served geometry (head_dim 64 + llama3 scaling of the 1B, head_dim 128 + llama3 of the 3B,
+    head_dim 128 default of the 7B, ...) is bit-equal to LlamaRotaryEmbedding's, in the oracle AND in the product's
+    host-side table (b200llm.geometry.inv_freq, what the engine uploads).  No model weights needed."""
+    from transformers import LlamaConfig
+    from transformers.models.llama.modeling_llama import LlamaRotaryEmbedding
+    from b200llm import geometry
+    geo = lo.GEOMETRIES[name]
+    rp = {"rope_type": "llama3", "rope_theta": geo.rope_theta, "factor": 32.0, "low_freq_factor": 1.0,
+          "high_freq_factor": 4.0, "original_max_position_embeddings": 8192} if geo.rope_llama3 else \
+         {"rope_type": "default", "rope_theta": geo.rope_theta}
+    cfg = LlamaConfig(vocab_size=geo.vocab, hidden_size=geo.d, intermediate_size=geo.ffn, num_hidden_layers=1,
+                      num_attention_heads=geo.n_q, num_key_value_heads=geo.n_kv, head_dim=geo.head_dim,
+                      max_position_embeddings=131072, rope_parameters=rp)
+    ref = LlamaRotaryEmbedding(cfg).inv_freq
+    assert torch.equal(ref, lo.inv_freq(geo))
+    assert torch.equal(ref, geometry.inv_freq(geometry.resolve(name)))
+
+
 @pytest.mark.parametrize("name", ["tiny", "small"])
 def test_golden_reproduces(name, golden_dir):
     """tests/golden/*.npz are outputs of this oracle (oracle/make_golden.py)."""

@@ -36,6 +36,22 @@ def _case(seed, nq, nkv, hd, ctx):
     return q, kp, vp, lanes, pos, ptab.cuda()
 
 
+def _torch_reference(q, kp, vp, pos, ptab, nq, nkv, hd):
+    """Plain fp32 softmax(q k^T / sqrt(hd)) v over each row's paged context (GQA: q head h reads kv head h // group)."""
+    out = torch.empty_like(q)
+    rep = nq // nkv
+    for b in range(q.shape[0]):
+        n = int(pos[b]) + 1
+        pages = ptab[b, :(n + 15) // 16].long()
+        K = kp[pages].float().permute(1, 0, 2, 3).reshape(nkv, -1, hd)[:, :n]      # [kv head, token, dim]
+        V = vp[pages].float().permute(1, 0, 2, 3).reshape(nkv, -1, hd)[:, :n]
+        qb = q[b].view(nq, hd)
+        for h in range(nq):
+            s_ = (K[h // rep] @ qb[h]) / (hd ** 0.5)
+            out[b, h * hd:(h + 1) * hd] = torch.softmax(s_, dim=0) @ V[h // rep]
+    return out
+
+
 def test_static_scratch_attention_matches_regular_entry_point_twice():
     from gpu_util import attn_decode
     nq, nkv, hd, splits = 24, 8, 128, 8
@@ -46,6 +62,9 @@ def test_static_scratch_attention_matches_regular_entry_point_twice():
         scale = float(want.abs().max())
         err = float((got - want).abs().max()) / scale
         assert err <= 1e-4, f"call {call}: rel err {err:.3e}"           # tolerance of test_attn_decode_matches_oracle
+        ref = _torch_reference(q, kp, vp, pos, ptab, nq, nkv, hd)        # and directly against fp32 attention in torch
+        err_ref = float((got - ref).abs().max()) / float(ref.abs().max())
+        assert err_ref <= 1e-4, f"call {call}: rel err vs torch fp32 {err_ref:.3e}"
     # same inputs again: the shared buffer kept the previous call's partials, the result must not change
     again = attn_decode(q, kp, vp, lanes, pos, ptab, nq, nkv, hd, splits, entry="b200llm_op_attn_decode_static")
     assert torch.equal(again, got)

@@ -875,7 +875,7 @@ static bool tcd_usable(const b200llm_engine *e) {
 }
 
 static int tcd_dataflow_bits(const b200llm_engine *e) {
-    if (e->cfg.tp_size > 1) return 0;   // the tensor-parallel phases keep their grid barriers
+    // (tensor parallel: the three edges below are local to a rank; the all-reduce phases keep their grid barriers)
     const char *df = getenv("B200LLM_TCD_DATAFLOW");
     return df ? atoi(df) : 7;
 }

@@ -127,6 +127,54 @@ def engine_bench(model: str, batch_sizes, prompt_len: int, new_tokens: int, n_tt
     return out
 
 
+def config3_sweep(model: str, device_counts, policy: str, n_requests: int, new_tokens: int, max_lanes: int):
+    """BASELINE.json config 3 / SURVEY.md 8(d): `n_requests` synthetic Spark error logs, prompt lengths log-uniform in
+    [64, 1024] ids (seed 3), `new_tokens` greedy tokens each, routed over one replica per GPU by b200llm.router.Router
+    (one process, one scheduler thread per GPU, continuous batching of up to `max_lanes` requests per replica).
+    Stands for the concurrent callers of the reference's threaded server (Flask/app.py:239) on its error path
+    (Flask/app.py:151-166).  Returns one row per GPU count: aggregate tok/s, efficiency vs one GPU, routing counts."""
+    import numpy as np
+    import torch
+    from b200llm import Engine, SamplingParams, geometry, weights
+    from b200llm.router import Router
+    from b200llm.scheduler import Scheduler
+    geo = geometry.resolve(model)
+    rng = np.random.default_rng(3)
+    lens = np.exp(rng.uniform(np.log(64), np.log(1024), n_requests)).astype(int)
+    prompts = [rng.integers(0, min(geo.vocab, 128000), int(n), dtype=np.int32) for n in lens]
+    rows, base = [], None
+    for n_gpu in device_counts:
+        engines = []
+        for d in range(n_gpu):
+            torch.cuda.set_device(d)
+            engines.append(Engine(geo, weights.random_init(geo, 0xB200, d), device=d, max_lanes=max_lanes,
+                                  max_ctx=1024 + new_tokens + 32, max_rows=256))
+        router = Router([Scheduler(e, chunk=16, prefix_cache=False) for e in engines], policy)
+        warm = [router.submit(prompts[i % n_requests][:64], 4, SamplingParams(temperature=0.0)) for i in range(2 * n_gpu)]
+        for r in warm:
+            router.wait(r)
+        router.routed = [0] * n_gpu
+        for d in range(n_gpu):
+            torch.cuda.synchronize(d)
+        t0 = time.perf_counter()
+        reqs = [router.submit(p, new_tokens, SamplingParams(temperature=0.0)) for p in prompts]
+        n_tok = sum(len(router.wait(r)[0]) for r in reqs)
+        dt = time.perf_counter() - t0
+        ttft = statistics.median(r.timing.prefill_ms for r in reqs)
+        row = {"gpus": n_gpu, "requests": n_requests, "prompt_ids_total": int(lens.sum()), "new_tokens": n_tok, "wall_s": dt,
+               "tok_s": n_tok / dt, "prefill_ms_p50": ttft, "routed": list(router.routed), "policy": policy,
+               "max_lanes_per_replica": max_lanes}
+        base = base or row["tok_s"] / n_gpu
+        row["efficiency_vs_1gpu"] = row["tok_s"] / (base * n_gpu)
+        rows.append(row)
+        router.shutdown()
+        for e in engines:
+            e.close()
+        del engines, router
+        torch.cuda.empty_cache()
+    return rows
+
+
 def cpu_row(model: str):
     import bench
     v, dt, cores = bench.cpu_decode_tok_s(model, 64, 12, 1)
@@ -141,7 +189,25 @@ def main():
     ap.add_argument("--new-tokens", type=int, default=128)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-text", action="store_true")
+    ap.add_argument("--config3", action="store_true", help="config 3: 512 mixed-length requests routed over 1/2/4/8 replicas "
+                    "(single process; do not run under torchrun)")
+    ap.add_argument("--policy", default="least_loaded", choices=["least_loaded", "round_robin"])
+    ap.add_argument("--requests", type=int, default=512)
+    ap.add_argument("--lanes", type=int, default=16)
     args = ap.parse_args()
+    if args.config3:
+        import torch
+        counts = [n for n in (1, 2, 4, 8) if n <= torch.cuda.device_count()]
+        rows = config3_sweep("llama3.2", counts, args.policy, args.requests, args.new_tokens, args.lanes)
+        print("=" * 100)
+        print(f"Config 3: Llama-3.2-3B, {args.requests} requests, prompt lengths log-uniform 64..1024 ids (seed 3), "
+              f"{args.new_tokens} new tokens each, router policy {args.policy}, <= {args.lanes} lanes per replica")
+        for r in rows:
+            print(f"  {r['gpus']} GPU(s): {r['tok_s']:10.1f} tok/s aggregate  ({r['wall_s']:.2f} s, efficiency vs 1 GPU "
+                  f"{r['efficiency_vs_1gpu']:.3f}, p50 prefill {r['prefill_ms_p50']:.1f} ms, routed {r['routed']})")
+        print("=" * 100)
+        print(json.dumps({"config3": rows}))
+        return
     import torch
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))

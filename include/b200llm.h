@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200LLM_ABI_VERSION 1
+#define B200LLM_ABI_VERSION 2
 
 enum {
     B200LLM_OK = 0,
@@ -166,6 +166,14 @@ int b200llm_workspace_bytes(const b200llm_config *cfg, size_t *bytes);
 int b200llm_kv_page_bytes(const b200llm_config *cfg, size_t *bytes);
 int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, int32_t n);
 int b200llm_bind_kv_pool(b200llm_engine *e, void *dev, size_t bytes);
+/* A KV pool that several engines share (the reference serves two models from one process: duckdb-nsql at
+ * Flask/app.py:102-107 and llama3.2 at :160-166; BASELINE.json config 5 co-locates both on every GPU).  The pool is
+ * cut into slots of `slot_bytes`, a page of this engine is ONE slot (page id = slot index, page i at dev + i *
+ * slot_bytes), laid out page-major: [layer][K|V][kv head][page_tokens][head_dim].  slot_bytes must be a multiple of
+ * page_tokens * head_dim * 2 and at least b200llm_kv_page_bytes.  Engines with different page sizes share one pool by
+ * agreeing on a block size and taking slot_bytes = block / k each (host side: b200llm/kv_pool.py); the library never
+ * allocates or frees pages, the host's allocator decides which slots a lane's page table names. */
+int b200llm_bind_kv_pool_shared(b200llm_engine *e, void *dev, size_t bytes, size_t slot_bytes);
 int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes);
 
 /* ---- sequence ("lane") state ------------------------------------------------------ */
@@ -240,6 +248,10 @@ typedef struct b200llm_gemv_args {
     int32_t *part_idx;       /* int32 [bs, grid] */
     int32_t logits_idx_offset; /* added to the argmax ids (vocab-parallel shards) */
     int32_t grid_hint;       /* 0 = auto */
+    int32_t kv_page_heads;   /* QKV_ROPE: (kv head, 16-token) tiles from one page to the next; 0 = n_kv (pages are
+                              * [n_kv, page_tokens, head_dim] and lie back to back); larger in a shared pool, see
+                              * b200llm_bind_kv_pool_shared */
+    int32_t reserved0;
 } b200llm_gemv_args;
 int b200llm_op_gemv(const b200llm_gemv_args *a, void *stream);
 /* Number of CTAs b200llm_op_gemv will launch for (N, K, bs, epi): size of the LOGITS partials. */
@@ -265,6 +277,7 @@ typedef struct b200llm_attn_args {
     const int32_t *row_pos;  /* [bs]: attends to tokens 0..pos inclusive */
     const int32_t *page_table;
     int32_t bs, n_q, n_kv, head_dim, page_tokens, max_pages_per_lane, n_splits;
+    int32_t kv_page_heads;   /* (kv head, 16-token) tiles from one page to the next; 0 = n_kv (see b200llm_gemv_args) */
     void *scratch;
     size_t scratch_bytes;
 } b200llm_attn_args;

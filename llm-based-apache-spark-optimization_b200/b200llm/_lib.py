@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # B200LLM_LIB: another build of the same sources (the trace build of scripts/tcd_trace.py); there is no non-CUDA substitute
 LIB_PATH = os.environ.get("B200LLM_LIB") or os.path.join(_HERE, "libb200llm.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 OK, EINVAL, ENODEV, ECUDA, ESTATE, ENCCL, ENOMEM = 0, -1, -2, -3, -4, -5, -6
 
 W_EMBED, W_LM_HEAD, W_FINAL_NORM, W_INV_FREQ, W_ATTN_NORM, W_QKV, W_O, W_MLP_NORM, W_GATE_UP, W_DOWN = range(10)
@@ -53,14 +53,14 @@ class GemvArgs(C.Structure):
                 ("inv_freq", C.c_void_p), ("row_lane", C.c_void_p), ("row_pos", C.c_void_p),
                 ("page_table", C.c_void_p), ("k_pages", C.c_void_p), ("v_pages", C.c_void_p),
                 ("part_max", C.c_void_p), ("part_idx", C.c_void_p), ("logits_idx_offset", C.c_int32),
-                ("grid_hint", C.c_int32)]
+                ("grid_hint", C.c_int32), ("kv_page_heads", C.c_int32), ("reserved0", C.c_int32)]
 
 
 class AttnArgs(C.Structure):
     _fields_ = [("q", C.c_void_p), ("out", C.c_void_p), ("k_pages", C.c_void_p), ("v_pages", C.c_void_p),
                 ("row_lane", C.c_void_p), ("row_pos", C.c_void_p), ("page_table", C.c_void_p), ("bs", C.c_int32),
                 ("n_q", C.c_int32), ("n_kv", C.c_int32), ("head_dim", C.c_int32), ("page_tokens", C.c_int32),
-                ("max_pages_per_lane", C.c_int32), ("n_splits", C.c_int32), ("scratch", C.c_void_p),
+                ("max_pages_per_lane", C.c_int32), ("n_splits", C.c_int32), ("kv_page_heads", C.c_int32), ("scratch", C.c_void_p),
                 ("scratch_bytes", C.c_size_t)]
 
 
@@ -81,6 +81,7 @@ SYMBOLS = {
     "b200llm_kv_page_bytes": (C.c_int, [_P(Config), _P(C.c_size_t)]),
     "b200llm_bind_weights": (C.c_int, [C.c_void_p, _P(TensorDesc), C.c_int32]),
     "b200llm_bind_kv_pool": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "b200llm_bind_kv_pool_shared": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t]),
     "b200llm_bind_workspace": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "b200llm_set_page_table": (C.c_int, [C.c_void_p, C.c_int32, _P(C.c_int32), C.c_int32]),
     "b200llm_set_sampling": (C.c_int, [C.c_void_p, C.c_int32, _P(Sampling)]),

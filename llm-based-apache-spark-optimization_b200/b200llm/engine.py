@@ -52,7 +52,7 @@ class Engine:
     def __init__(self, geo: Geometry, weights: PackedWeights, device: int = 0, max_lanes: int = 8,
                  max_ctx: int = 4096, max_rows: int = 64, kv_pages: Optional[int] = None, tp_rank: int = 0,
                  tp_size: int = 1, nccl_id: Optional[bytes] = None, use_graphs: bool = True, use_pdl: bool = False,
-                 attn_splits: int = 0, use_megakernel: bool = True, use_tc: bool = True):
+                 attn_splits: int = 0, use_megakernel: bool = True, use_tc: bool = True, kv_pool=None, name: str = ""):
         if not torch.cuda.is_available():
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         self.geo, self.weights, self.device = geo, weights, device
@@ -81,16 +81,24 @@ class Engine:
         self.workspace = torch.empty(nbytes.value, dtype=torch.uint8, device=device)
         _lib.check(_lib.lib.b200llm_kv_page_bytes(C.byref(cfg), C.byref(nbytes)))
         self.page_bytes = nbytes.value
-        if kv_pages is None:
-            kv_pages = max_lanes * self.max_pages_per_lane
-        self.n_pages = kv_pages
-        self.kv_pool = torch.zeros(kv_pages * self.page_bytes, dtype=torch.uint8, device=device)
-        torch.cuda.synchronize(device)
         descs = weights.descs()
         _lib.check(_lib.lib.b200llm_bind_weights(self._h, descs, len(descs)))
-        _lib.check(_lib.lib.b200llm_bind_kv_pool(self._h, self.kv_pool.data_ptr(), self.kv_pool.numel()))
+        if kv_pool is not None:
+            # pages come from a pool shared with other engines on this GPU (kv_pool.SharedKVPool): a page is one slot of it
+            tile = PAGE_TOKENS * geo.head_dim * 2
+            self._free_pages = kv_pool.view(name or geo.name, self.page_bytes, tile)
+            kv_pages = self._free_pages.n_slots
+            self.kv_pool = kv_pool.buffer
+            _lib.check(_lib.lib.b200llm_bind_kv_pool_shared(self._h, kv_pool.data_ptr(), kv_pool.nbytes, self._free_pages.slot_bytes))
+        else:
+            if kv_pages is None:
+                kv_pages = max_lanes * self.max_pages_per_lane
+            self.kv_pool = torch.zeros(kv_pages * self.page_bytes, dtype=torch.uint8, device=device)
+            _lib.check(_lib.lib.b200llm_bind_kv_pool(self._h, self.kv_pool.data_ptr(), self.kv_pool.numel()))
+            self._free_pages = list(range(kv_pages - 1, -1, -1))
+        self.n_pages = kv_pages
+        torch.cuda.synchronize(device)
         _lib.check(_lib.lib.b200llm_bind_workspace(self._h, self.workspace.data_ptr(), self.workspace.numel()))
-        self._free_pages = list(range(kv_pages - 1, -1, -1))
         self._page_ref = [0] * kv_pages      # lanes and prefix-cache entries holding each page
         self.on_page_pressure = None         # callable(n_pages_short), set by the prefix cache
         self._lane_pages: List[List[int]] = [[] for _ in range(max_lanes)]
@@ -162,9 +170,14 @@ class Engine:
             self.on_page_pressure(need - len(pages) - len(self._free_pages))   # the prefix cache gives pages back
         if need - len(pages) > len(self._free_pages):
             raise _lib.B200LLMError(_lib.ENOMEM, "KV pool exhausted")
-        while len(pages) < need:
-            pages.append(self._free_pages.pop())
-            self._page_ref[pages[-1]] = 1
+        try:
+            while len(pages) < need:
+                pages.append(self._free_pages.pop())
+                self._page_ref[pages[-1]] = 1
+        except IndexError:      # a shared pool: another engine took the blocks in the meantime
+            arr = (C.c_int32 * len(pages))(*pages)
+            _lib.check(_lib.lib.b200llm_set_page_table(self._h, lane, arr, len(pages)))
+            raise _lib.B200LLMError(_lib.ENOMEM, "KV pool exhausted") from None
         arr = (C.c_int32 * len(pages))(*pages)
         _lib.check(_lib.lib.b200llm_set_page_table(self._h, lane, arr, len(pages)))
 

@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __gr
     auto issue = [&](int i) {
         const int st = i % kAttnStages;
         const int page = ptab[my_first + i * kAttnWarps];
-        const size_t off = ((size_t)page * a.n_kv + hk) * (size_t)TILE;
+        const size_t off = ((size_t)page * (a.kv_page_heads > 0 ? a.kv_page_heads : a.n_kv) + hk) * (size_t)TILE;
         mbar_expect_tx(&full[st], 2 * TILE);
         tma_load_1d(tiles + (size_t)st * 2 * TILE, kbase + off, TILE, &full[st]);
         tma_load_1d(tiles + (size_t)st * 2 * TILE + TILE, vbase + off, TILE, &full[st]);

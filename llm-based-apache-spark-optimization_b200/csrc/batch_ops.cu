@@ -93,7 +93,7 @@ struct RopeArgs {
     void *k_pages, *v_pages;
     const float *inv_freq;
     const int32_t *row_lane, *row_pos, *page_table;
-    int n_q, n_kv, hd, page_tokens, max_pages;
+    int n_q, n_kv, hd, page_tokens, max_pages, kv_page_heads;
 };
 __global__ void __launch_bounds__(256) rope_append_kernel(const __grid_constant__ RopeArgs a) {
     pdl_trigger();
@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(256) rope_append_kernel(const __grid_constant_
             const bool is_k = n < qrows + krows;
             const int kn = is_k ? n - qrows : n - qrows - krows;
             uint16_t *dst = reinterpret_cast<uint16_t *>(is_k ? a.k_pages : a.v_pages) +
-                            (((size_t)page * a.n_kv + kn / a.hd) * a.page_tokens + slot) * a.hd + kn % a.hd;
+                            (((size_t)page * a.kv_page_heads + kn / a.hd) * a.page_tokens + slot) * a.hd + kn % a.hd;
             *reinterpret_cast<uint32_t *>(dst) = (uint32_t)f32_to_bf16_bits(v0) | ((uint32_t)f32_to_bf16_bits(v1) << 16);
         }
     }
@@ -147,8 +147,9 @@ int swiglu_bf16_launch(const float *gu, void *out, int rows, int ffn, cudaStream
 }
 int rope_append_launch(const float *qkv, float *q, void *k_pages, void *v_pages, const float *inv_freq,
                        const int32_t *row_lane, const int32_t *row_pos, const int32_t *page_table, int rows, int n_q,
-                       int n_kv, int hd, int page_tokens, int max_pages, cudaStream_t s, bool pdl) {
-    RopeArgs a{qkv, q, k_pages, v_pages, inv_freq, row_lane, row_pos, page_table, n_q, n_kv, hd, page_tokens, max_pages};
+                       int n_kv, int hd, int page_tokens, int max_pages, cudaStream_t s, bool pdl, int kv_page_heads) {
+    RopeArgs a{qkv, q, k_pages, v_pages, inv_freq, row_lane, row_pos, page_table, n_q, n_kv, hd, page_tokens, max_pages,
+               kv_page_heads > 0 ? kv_page_heads : n_kv};
     const int width = (n_q + 2 * n_kv) * hd;
     LaunchCfg lc(dim3((width / 2 + 255) / 256, rows), dim3(256), 0, s, pdl);
     B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, rope_append_kernel, a));

@@ -35,7 +35,7 @@ __device__ __forceinline__ void tcd_attn_prefetch(const TcdParams &p, const TcdJ
         for (int i = tid; i < (pg_end - pg_begin) * LINES; i += kTC) {
             const int pg = pg_begin + i / LINES, line = i % LINES;
             const int page = pg < kTMaxPtab ? s.ptab[pg] : p.page_table[pg];
-            const size_t off = ((size_t)page * p.n_kv + hk) * (size_t)(kTPT * HD * 2) + (size_t)line * 128;
+            const size_t off = ((size_t)page * p.kv_page_heads + hk) * (size_t)(kTPT * HD * 2) + (size_t)line * 128;
             prefetch_l2(kbase + off);
             prefetch_l2(vbase + off);
         }
@@ -143,7 +143,7 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
             if (tg == 0) {
                 const int pgi = c.pos / kTPT;
                 const int page = pgi < kTMaxPtab ? s.ptab[pgi] : p.page_table[pgi];
-                const size_t at = (((size_t)page * p.n_kv + hk) * kTPT + (c.pos % kTPT)) * HD + p16 * EL;
+                const size_t at = (((size_t)page * p.kv_page_heads + hk) * kTPT + (c.pos % kTPT)) * HD + p16 * EL;
                 uint32_t kw[EL / 2], vw[EL / 2];
 #pragma unroll
                 for (int e = 0; e < EL / 2; ++e) kw[e] = tcd_pack_bf16(kf[2 * e], kf[2 * e + 1]), vw[e] = tcd_pack_bf16(vf[2 * e], vf[2 * e + 1]);
@@ -159,7 +159,7 @@ __device__ void tcd_attn_phase(const TcdParams &p, const TcdJob &qkv_job, const 
         for (int hp = 2 * pg_begin + warp; hp < 2 * pg_end; hp += kTW) {  // half-pages of this item, round-robin over the warps
             const int pg = hp >> 1;
             const int page = pg < kTMaxPtab ? s.ptab[pg] : p.page_table[pg];
-            const size_t tile = ((size_t)page * p.n_kv + hk) * (size_t)(kTPT * HD);
+            const size_t tile = ((size_t)page * p.kv_page_heads + hk) * (size_t)(kTPT * HD);
             const uint16_t *kp = kbase + tile + p16 * EL;
             const uint16_t *vp = vbase + tile + p16 * EL;
             // a half-page = 4 x 2 tokens: all its K and V loads in flight together, its 8 scores

@@ -113,7 +113,8 @@ struct b200llm_engine {
     // kv pool: [layer][K|V][page][kv head][token][dim] bf16
     uint8_t *kv = nullptr;
     int n_pages = 0;
-    size_t kv_half_stride = 0;  // bytes of one layer's K (or V) region
+    size_t kv_half_stride = 0;  // bytes from one layer's K region to its V region (and on to the next layer's K)
+    int kv_page_heads = 0;      // (kv head, 16-token) tiles from one page to the next: nkv_l, or a shared pool's slot size
     // workspace
     uint8_t *ws = nullptr;
     float *h, *q, *att, *act, *delta, *logits, *part_max;
@@ -525,6 +526,28 @@ int b200llm_bind_kv_pool(b200llm_engine *e, void *dev, size_t bytes) {
     B200_REQUIRE(e->n_pages >= 1, "bind_kv_pool: pool smaller than one page (%zu < %zu)", bytes, pb);
     e->kv = (uint8_t *)dev;
     e->kv_half_stride = (size_t)e->n_pages * e->nkv_l * e->cfg.page_tokens * e->cfg.head_dim * 2;
+    e->kv_page_heads = e->nkv_l;
+    for (auto &kv : e->graphs) cudaGraphExecDestroy(kv.second);   // captured steps carry the old addresses
+    e->graphs.clear();
+    e->mega_ready = e->tcd_ready = false;
+    return B200LLM_OK;
+}
+
+int b200llm_bind_kv_pool_shared(b200llm_engine *e, void *dev, size_t bytes, size_t slot_bytes) {
+    B200_REQUIRE(e && dev && ((uintptr_t)dev % 256) == 0, "bind_kv_pool_shared: NULL or unaligned pool");
+    size_t pb;
+    b200llm_kv_page_bytes(&e->cfg, &pb);
+    const size_t tile = (size_t)e->cfg.page_tokens * e->cfg.head_dim * 2;
+    B200_REQUIRE(slot_bytes >= pb && slot_bytes % tile == 0 && slot_bytes % 256 == 0,
+                 "bind_kv_pool_shared: slot of %zu bytes must hold a %zu-byte page and be a multiple of %zu", slot_bytes, pb, tile);
+    e->n_pages = (int)(bytes / slot_bytes);
+    B200_REQUIRE(e->n_pages >= 1, "bind_kv_pool_shared: pool smaller than one slot (%zu < %zu)", bytes, slot_bytes);
+    e->kv = (uint8_t *)dev;
+    e->kv_half_stride = (size_t)e->nkv_l * tile;        // page-major: layer l's K tiles, then its V tiles, inside every page
+    e->kv_page_heads = (int)(slot_bytes / tile);
+    for (auto &kv : e->graphs) cudaGraphExecDestroy(kv.second);
+    e->graphs.clear();
+    e->mega_ready = e->tcd_ready = false;
     return B200LLM_OK;
 }
 
@@ -761,13 +784,13 @@ static int forward_pass_gemv(b200llm_engine *e, const PassRows &pr, bool advance
         g.out = e->q, g.out_stride = (int64_t)qd, g.N = (e->nq_l + 2 * e->nkv_l) * c.head_dim, g.K = c.d;
         g.epi = B200LLM_EPI_QKV_ROPE, g.n_q = e->nq_l, g.n_kv = e->nkv_l, g.head_dim = c.head_dim;
         g.page_tokens = c.page_tokens, g.max_pages_per_lane = c.max_pages_per_lane, g.inv_freq = e->inv_freq;
-        g.page_table = e->page_table, g.k_pages = kl, g.v_pages = vl;
+        g.page_table = e->page_table, g.k_pages = kl, g.v_pages = vl, g.kv_page_heads = e->kv_page_heads;
         B200_TRY(gemv_rows(e, g, rows, pr, 0));
         // --- attention ---
         b200llm_attn_args at{};
         at.q = e->q, at.out = e->att, at.k_pages = kl, at.v_pages = vl, at.row_lane = pr.row_lane, at.row_pos = pr.row_pos;
         at.page_table = e->page_table, at.bs = rows, at.n_q = e->nq_l, at.n_kv = e->nkv_l, at.head_dim = c.head_dim;
-        at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane;
+        at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane, at.kv_page_heads = e->kv_page_heads;
         // enough CTAs to fill the GPU, no more splits than that needs
         int want = (kNumSMs + rows * e->nkv_l - 1) / (rows * e->nkv_l);
         if (want > 6) want = 6;  // the last-CTA merge is serial in the number of splits (profiles/launches_r1a)
@@ -833,6 +856,7 @@ static int mega_decode(b200llm_engine *e, int lane, int n_steps) {
     MegaParams p{};
     p.jobs = e->mega_jobs, p.n_layers = c.n_layers;
     p.d = c.d, p.n_q = c.n_q, p.n_kv = c.n_kv, p.head_dim = c.head_dim, p.ffn = c.ffn, p.vocab = c.vocab;
+    p.kv_page_heads = e->kv_page_heads;
     p.rms_eps = c.rms_eps;
     p.scale_log2 = (float)(1.4426950408889634 / sqrt((double)c.head_dim));
     p.h = e->h, p.q = e->q, p.att = e->att, p.act = e->act, p.logits = e->logits;
@@ -917,6 +941,7 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
     p.dataflow = e->tcd_dataflow, p.gu2 = e->tcd_gu2, p.att2 = e->tcd_att2, p.qkv2 = e->tcd_qkv2;
     p.jobs = reinterpret_cast<const TcdJob *>(e->mega_jobs), p.n_layers = c.n_layers;
     p.d = c.d, p.n_q = e->nq_l, p.n_kv = e->nkv_l, p.head_dim = c.head_dim, p.ffn = e->ffn_l, p.vocab = e->vocab_l;
+    p.kv_page_heads = e->kv_page_heads;
     p.vocab_global = c.vocab, p.tp_rank = c.tp_rank, p.tp_size = c.tp_size;
     if (c.tp_size > 1) {
         p.delta = e->delta, p.ar_seq = e->ar_seq, p.ar_slot_floats = e->ar_slot_floats, p.ar_max_slices = e->ar_max_slices;
@@ -1042,11 +1067,11 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         B200_TRY(rmsnorm_bf16_launch(e->h, w.attn_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->qkv_out, qkv_w, e->xb_lo));
         B200_TRY(tc_gemm(e, w.wqkv, qkv_w, c.d, e->qkv_out, qkv_w, rows, false, true));
         B200_TRY(rope_append_launch(e->qkv_out, e->q, kl, vl, e->inv_freq, pr.row_lane, pr.row_pos, e->page_table, rows,
-                                    n_q, n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, pdl));
+                                    n_q, n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, pdl, e->kv_page_heads));
         b200llm_attn_args at{};
         at.q = e->q, at.out = e->att, at.k_pages = kl, at.v_pages = vl, at.row_lane = pr.row_lane, at.row_pos = pr.row_pos;
         at.page_table = e->page_table, at.bs = rows, at.n_q = n_q, at.n_kv = n_kv, at.head_dim = c.head_dim;
-        at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane;
+        at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane, at.kv_page_heads = e->kv_page_heads;
         int want = (kNumSMs + rows * n_kv - 1) / (rows * n_kv);
         if (want > 6) want = 6;
         at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
@@ -1323,6 +1348,7 @@ int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, 
     TcdParams p{};
     p.jobs = reinterpret_cast<const TcdJob *>(scr), p.n_layers = 0;
     p.d = K, p.n_q = 1, p.n_kv = 1, p.head_dim = 128, p.ffn = 0, p.vocab = N;
+    p.kv_page_heads = 1;
     p.vocab_global = N, p.tp_rank = 0, p.tp_size = 1;
     p.h = const_cast<float *>(x), p.logits = out;
     p.part_max = reinterpret_cast<float *>(scr + 1024), p.part_idx = reinterpret_cast<int32_t *>(scr + 2048);

@@ -292,7 +292,7 @@ gemv_kernel(const __grid_constant__ GemvDev p) {
                     const int kn = is_k ? n - qrows : n - qrows - krows;
                     const int hk = kn / hd, dim = kn % hd;
                     uint16_t *dst = reinterpret_cast<uint16_t *>(is_k ? a.k_pages : a.v_pages) +
-                                    (((size_t)page * a.n_kv + hk) * a.page_tokens + slot_t) * hd + dim;
+                                    (((size_t)page * (a.kv_page_heads > 0 ? a.kv_page_heads : a.n_kv) + hk) * a.page_tokens + slot_t) * hd + dim;
                     const uint32_t packed = (uint32_t)f32_to_bf16_bits(v0) | ((uint32_t)f32_to_bf16_bits(v1) << 16);
                     *reinterpret_cast<uint32_t *>(dst) = packed;
                 }

@@ -69,7 +69,7 @@ int cast_bf16_launch(const float *x, int64_t in_stride, void *out, int rows, int
 int swiglu_bf16_launch(const float *gu, void *out, int rows, int ffn, cudaStream_t s, bool pdl, int64_t lo_off = 0);
 int rope_append_launch(const float *qkv, float *q, void *k_pages, void *v_pages, const float *inv_freq,
                        const int32_t *row_lane, const int32_t *row_pos, const int32_t *page_table, int rows, int n_q,
-                       int n_kv, int hd, int page_tokens, int max_pages, cudaStream_t s, bool pdl);
+                       int n_kv, int hd, int page_tokens, int max_pages, cudaStream_t s, bool pdl, int kv_page_heads = 0);
 
 int fill_weights_launch(void *dev_bf16, uint64_t n, uint64_t seed, float sigma, float mean, cudaStream_t s);
 int add_inplace_launch(float *dst, const float *src, size_t n, cudaStream_t s, bool pdl);

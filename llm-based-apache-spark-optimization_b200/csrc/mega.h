@@ -21,6 +21,7 @@ struct MegaParams {
     const MegaJob *jobs;  // device array: 4 per layer (qkv, o, gate_up, down) + lm_head
     int32_t n_layers;
     int32_t d, n_q, n_kv, head_dim, ffn, vocab;
+    int32_t kv_page_heads;   // (kv head, 16-token) tiles from one KV page to the next (n_kv, or more in a shared pool)
     float rms_eps;
     float scale_log2;     // log2(e) / sqrt(head_dim)
     // activations (fp32), all one row (batch 1)

@@ -33,7 +33,7 @@ __device__ __forceinline__ void mega_attn_prefetch(const MegaParams &p, const Me
         for (int i = tid; i < (pg_end - pg_begin) * LINES; i += kMC) {
             const int pg = pg_begin + i / LINES, line = i % LINES;
             const int page = pg < kMaxPtab ? s.ptab[pg] : p.page_table[pg];
-            const size_t off = ((size_t)page * p.n_kv + hk) * (size_t)(kMPT * HD * 2) + (size_t)line * 128;
+            const size_t off = ((size_t)page * p.kv_page_heads + hk) * (size_t)(kMPT * HD * 2) + (size_t)line * 128;
             prefetch_l2(kbase + off);
             prefetch_l2(vbase + off);
         }
@@ -74,7 +74,7 @@ __device__ void mega_attn_phase(const MegaParams &p, const MegaJob &qkv_job, con
         if (q[0][0] != 1.2345e30f) mega_trace(p, c.ti, bid, tid);  // (debug) q arrived
         for (int pg = pg_begin + warp; pg < pg_end; pg += kMW) {
             const int page = pg < kMaxPtab ? s.ptab[pg] : p.page_table[pg];
-            const size_t tile = ((size_t)page * p.n_kv + hk) * (size_t)(kMPT * HD);
+            const size_t tile = ((size_t)page * p.kv_page_heads + hk) * (size_t)(kMPT * HD);
             const uint16_t *kp = kbase + tile + p16 * EL;
             const uint16_t *vp = vbase + tile + p16 * EL;
             // two half-pages of 4 x 2 tokens: all loads of a half-page in flight together, its 8

@@ -234,7 +234,7 @@ __device__ void mega_gemv_phase(const MegaParams &p, const MegaJob &job, const M
                     const bool is_k = n < qrows + krows;
                     const int kn = is_k ? n - qrows : n - qrows - krows;
                     uint16_t *dst = reinterpret_cast<uint16_t *>(is_k ? job.k_pages : job.v_pages) +
-                                    (((size_t)page * p.n_kv + kn / hd) * kMPT + (c.pos % kMPT)) * hd + kn % hd;
+                                    (((size_t)page * p.kv_page_heads + kn / hd) * kMPT + (c.pos % kMPT)) * hd + kn % hd;
                     *reinterpret_cast<uint32_t *>(dst) = pack_bf16(v0, v1);
                 }
             }

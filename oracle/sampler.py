@@ -76,3 +76,16 @@ def sample(logits: np.ndarray, temperature: float, top_k: int, top_p: float, rep
             pick = i
             break
     return int(order[pick]), order[:keep], probs[:keep]
+
+
+def top_p_margin(logits: np.ndarray, temperature: float, top_k: int, top_p: float, cap: int = 1024) -> float:
+    """How close the top-p cut is to keeping one candidate more or fewer: min |cum_i / total - top_p| over the top-k
+    candidates (1.0 when top-p is off).  The kept SET, and with it the mass the uniform draw is scaled by, changes
+    discontinuously there, so logits that differ by rounding noise may legitimately lead to different draws."""
+    if temperature <= 0 or top_p >= 1.0:
+        return 1.0
+    lg = logits.astype(np.float32)
+    k = min(top_k if top_k > 0 else cap, cap, lg.shape[0])
+    vals = np.sort(lg)[::-1][:k].astype(np.float64)
+    probs = np.exp((vals - vals[0]) / float(temperature))
+    return float(np.abs(np.cumsum(probs) / probs.sum() - top_p).min())

@@ -175,6 +175,84 @@ def config3_sweep(model: str, device_counts, policy: str, n_requests: int, new_t
     return rows
 
 
+def config5(n_gpus: int, in_flight_per_model: int, new_tokens: int, pool_gib: float, policy: str):
+    """BASELINE.json config 5 / SURVEY.md 8(d): duckdb-nsql-7B and Llama-3.2-3B co-resident on each of `n_gpus` GPUs, their
+    KV pages drawn from ONE pool per GPU (b200llm.kv_pool.SharedKVPool, 16-token pages), `in_flight_per_model` sequences
+    per model in flight over the whole box (requests routed per model over the GPUs by b200llm.router.Router), 3B prompts
+    of 296 ids, 7B prompts log-uniform in [128, 2048] ids, `new_tokens` greedy tokens each.  The reference serves both
+    models from one process (Flask/app.py:102-107 and :160-166).  Returns aggregate tok/s per model and pool occupancy."""
+    import threading
+    import numpy as np
+    import torch
+    from b200llm import Engine, SamplingParams, geometry, weights
+    from b200llm.kv_pool import SharedKVPool
+    from b200llm.router import Router
+    from b200llm.scheduler import Scheduler
+    models = ["duckdb-nsql", "llama3.2"]
+    geos = {m: geometry.resolve(m) for m in models}
+    page = {m: geos[m].n_layers * 2 * geos[m].n_kv * 16 * geos[m].head_dim * 2 for m in models}
+    block = max(page.values())
+    lanes = max(1, (in_flight_per_model + n_gpus - 1) // n_gpus)
+    pools, engines = [], {m: [] for m in models}
+    for d in range(n_gpus):
+        torch.cuda.set_device(d)
+        pools.append(SharedKVPool(int(pool_gib * (1 << 30)) // block, block, device=d))
+        for m in models:
+            engines[m].append(Engine(geos[m], weights.random_init(geos[m], 0xB200, d), device=d, max_lanes=lanes,
+                                     max_ctx=2048 + new_tokens + 32, max_rows=256, kv_pool=pools[d], name=m))
+    routers = {m: Router([Scheduler(e, chunk=16, prefix_cache=False) for e in engines[m]], policy) for m in models}
+    rng = np.random.default_rng(5)
+    n_req = 2 * in_flight_per_model                  # two waves per model, so that lanes are refilled while others still run
+    prompts = {"llama3.2": [rng.integers(0, 128000, 296, dtype=np.int32) for _ in range(n_req)],
+               "duckdb-nsql": [rng.integers(0, geos["duckdb-nsql"].vocab, int(n), dtype=np.int32)
+                               for n in np.exp(rng.uniform(np.log(128), np.log(2048), n_req)).astype(int)]}
+    for m in models:                                 # warm-up: tensor maps, graphs
+        for r in [routers[m].submit(prompts[m][i][:128], 4, SamplingParams(temperature=0.0)) for i in range(n_gpus)]:
+            routers[m].wait(r)
+    for d in range(n_gpus):
+        torch.cuda.synchronize(d)
+    peak = [0] * n_gpus
+    stop = threading.Event()
+
+    def watch():
+        while not stop.is_set():
+            for d in range(n_gpus):
+                occ = pools[d].occupancy()
+                peak[d] = max(peak[d], occ["blocks"] - occ["free_blocks"])
+            time.sleep(0.02)
+    w = threading.Thread(target=watch, daemon=True)
+    w.start()
+    t0 = time.perf_counter()
+    reqs = {m: [routers[m].submit(p, new_tokens, SamplingParams(temperature=0.0)) for p in prompts[m]] for m in models}
+    done_at, n_tok = {}, {}
+
+    def collect(m):                                  # one waiter per model: each model's wall time ends with ITS last request
+        n_tok[m] = sum(len(routers[m].wait(r)[0]) for r in reqs[m])
+        done_at[m] = time.perf_counter() - t0
+    waiters = [threading.Thread(target=collect, args=(m,)) for m in models]
+    for t in waiters:
+        t.start()
+    for t in waiters:
+        t.join()
+    stop.set()
+    w.join()
+    out = {"gpus": n_gpus, "in_flight_per_model": in_flight_per_model, "lanes_per_engine": lanes, "new_tokens_each": new_tokens,
+           "policy": policy, "models": {}, "pool": {"block_bytes": block, "blocks_per_gpu": pools[0].n_blocks,
+                                                     "gib_per_gpu": pools[0].nbytes / (1 << 30),
+                                                     "peak_blocks_in_use_per_gpu": peak,
+                                                     "peak_occupancy": max(peak) / pools[0].n_blocks,
+                                                     "after": [p.occupancy()["free_blocks"] for p in pools]}}
+    for m in models:
+        out["models"][m] = {"requests": n_req, "prompt_ids_total": int(sum(len(p) for p in prompts[m])), "new_tokens": n_tok[m],
+                            "wall_s": done_at[m], "tok_s": n_tok[m] / done_at[m], "routed": list(routers[m].routed),
+                            "slots_per_block": engines[m][0]._free_pages.k}
+    for m in models:
+        routers[m].shutdown()
+        for e in engines[m]:
+            e.close()
+    return out
+
+
 def cpu_row(model: str):
     import bench
     v, dt, cores = bench.cpu_decode_tok_s(model, 64, 12, 1)
@@ -191,6 +269,10 @@ def main():
     ap.add_argument("--no-text", action="store_true")
     ap.add_argument("--config3", action="store_true", help="config 3: 512 mixed-length requests routed over 1/2/4/8 replicas "
                     "(single process; do not run under torchrun)")
+    ap.add_argument("--config5", action="store_true", help="config 5: the 7B and the 3B co-served on every GPU out of one KV pool "
+                    "per GPU, 128 sequences per model in flight (single process; do not run under torchrun)")
+    ap.add_argument("--in-flight", type=int, default=128)
+    ap.add_argument("--pool-gib", type=float, default=48.0)
     ap.add_argument("--policy", default="least_loaded", choices=["least_loaded", "round_robin"])
     ap.add_argument("--requests", type=int, default=512)
     ap.add_argument("--lanes", type=int, default=16)
@@ -207,6 +289,22 @@ def main():
                   f"{r['efficiency_vs_1gpu']:.3f}, p50 prefill {r['prefill_ms_p50']:.1f} ms, routed {r['routed']})")
         print("=" * 100)
         print(json.dumps({"config3": rows}))
+        return
+    if args.config5:
+        import torch
+        r = config5(torch.cuda.device_count(), args.in_flight, args.new_tokens, args.pool_gib, args.policy)
+        print("=" * 100)
+        print(f"Config 5: duckdb-nsql-7B + Llama-3.2-3B co-served on {r['gpus']} GPU(s), one KV pool of {r['pool']['gib_per_gpu']:.0f} GiB "
+              f"per GPU ({r['pool']['blocks_per_gpu']} blocks of {r['pool']['block_bytes'] >> 20} MiB), {r['in_flight_per_model']} sequences "
+              f"per model in flight ({r['lanes_per_engine']} lanes per engine), {r['new_tokens_each']} new tokens each")
+        for m, v in r["models"].items():
+            print(f"  {m:12s}: {v['tok_s']:10.1f} tok/s aggregate  ({v['requests']} requests, {v['prompt_ids_total']} prompt ids, "
+                  f"{v['wall_s']:.2f} s, {v['slots_per_block']} page(s) per block, routed {v['routed']})")
+        print(f"  pool: peak {max(r['pool']['peak_blocks_in_use_per_gpu'])} blocks in use on the fullest GPU = "
+              f"{100 * r['pool']['peak_occupancy']:.1f} % of the pool; all blocks free afterwards: "
+              f"{all(a == r['pool']['blocks_per_gpu'] for a in r['pool']['after'])}")
+        print("=" * 100)
+        print(json.dumps({"config5": r}))
         return
     import torch
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))

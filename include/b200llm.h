@@ -285,6 +285,22 @@ int b200llm_op_attn_decode(const b200llm_attn_args *a, void *stream);
 int b200llm_op_attn_scratch_bytes(int32_t bs, int32_t n_q, int32_t n_kv, int32_t head_dim,
                                   int32_t n_splits, size_t *bytes);
 
+/* Causal attention of a prefill chunk on the tensor cores (kernel K10; csrc/attn_prefill.cu): `rows` consecutive query
+ * rows of ONE lane, row r at position pos0 + r attending keys 0 .. pos0 + r, whose K/V rows are in the paged cache
+ * already (this chunk's included).  Replaces what llama.cpp's prompt processing does below the reference's
+ * ollama.generate calls (Flask/app.py:102-107,160-166) -- the TTFT path.  q is fp32 [rows, n_q * head_dim] with RoPE
+ * applied; out fp32 of the same shape.  k_pages / v_pages: bf16 tiles [page][kv_page_heads (>= n_kv)][16][head_dim] as
+ * for b200llm_op_attn_decode; n_pages bounds the page ids; page_table_row is the lane's row (n_ptab entries). */
+typedef struct b200llm_attn_prefill_args {
+    const float *q;
+    float *out;
+    const void *k_pages;
+    const void *v_pages;
+    const int32_t *page_table_row;
+    int32_t n_ptab, rows, pos0, n_q, n_kv, head_dim, n_pages, kv_page_heads;   /* kv_page_heads 0 = n_kv */
+} b200llm_attn_prefill_args;
+int b200llm_op_attn_prefill(const b200llm_attn_prefill_args *a, void *stream);
+
 /* The same attention launch for callers that cannot allocate device memory.  (This entry
  * point has no counterpart in the reference; it exists for host programs of two kinds: those
  * that handed the whole card to their own memory pool at start-up, where a later cudaMalloc

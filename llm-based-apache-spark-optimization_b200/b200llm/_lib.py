@@ -64,6 +64,13 @@ class AttnArgs(C.Structure):
                 ("scratch_bytes", C.c_size_t)]
 
 
+class AttnPrefillArgs(C.Structure):
+    _fields_ = [("q", C.c_void_p), ("out", C.c_void_p), ("k_pages", C.c_void_p), ("v_pages", C.c_void_p),
+                ("page_table_row", C.c_void_p), ("n_ptab", C.c_int32), ("rows", C.c_int32), ("pos0", C.c_int32),
+                ("n_q", C.c_int32), ("n_kv", C.c_int32), ("head_dim", C.c_int32), ("n_pages", C.c_int32),
+                ("kv_page_heads", C.c_int32)]
+
+
 class SampleArgs(C.Structure):
     _fields_ = [("logits", C.c_void_p), ("bs", C.c_int32), ("vocab", C.c_int32), ("part_max", C.c_void_p),
                 ("part_idx", C.c_void_p), ("n_part", C.c_int32), ("params", C.c_void_p), ("history", C.c_void_p),
@@ -104,6 +111,7 @@ SYMBOLS = {
     "b200llm_op_gemv_grid": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P(C.c_int32)]),
     "b200llm_op_gemv_tm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "b200llm_op_attn_decode": (C.c_int, [_P(AttnArgs), C.c_void_p]),
+    "b200llm_op_attn_prefill": (C.c_int, [_P(AttnPrefillArgs), C.c_void_p]),
     "b200llm_op_attn_scratch_bytes": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                                 _P(C.c_size_t)]),
     "b200llm_op_attn_decode_static": (C.c_int, [_P(AttnArgs), C.c_void_p]),

@@ -115,6 +115,7 @@ struct b200llm_engine {
     int n_pages = 0;
     size_t kv_half_stride = 0;  // bytes from one layer's K region to its V region (and on to the next layer's K)
     int kv_page_heads = 0;      // (kv head, 16-token) tiles from one page to the next: nkv_l, or a shared pool's slot size
+    bool kv_shared = false;     // pages are page-major slots of a pool shared with other engines
     // workspace
     uint8_t *ws = nullptr;
     float *h, *q, *att, *act, *delta, *logits, *part_max;
@@ -526,7 +527,7 @@ int b200llm_bind_kv_pool(b200llm_engine *e, void *dev, size_t bytes) {
     B200_REQUIRE(e->n_pages >= 1, "bind_kv_pool: pool smaller than one page (%zu < %zu)", bytes, pb);
     e->kv = (uint8_t *)dev;
     e->kv_half_stride = (size_t)e->n_pages * e->nkv_l * e->cfg.page_tokens * e->cfg.head_dim * 2;
-    e->kv_page_heads = e->nkv_l;
+    e->kv_page_heads = e->nkv_l, e->kv_shared = false;
     for (auto &kv : e->graphs) cudaGraphExecDestroy(kv.second);   // captured steps carry the old addresses
     e->graphs.clear();
     e->mega_ready = e->tcd_ready = false;
@@ -544,7 +545,7 @@ int b200llm_bind_kv_pool_shared(b200llm_engine *e, void *dev, size_t bytes, size
     B200_REQUIRE(e->n_pages >= 1, "bind_kv_pool_shared: pool smaller than one slot (%zu < %zu)", bytes, slot_bytes);
     e->kv = (uint8_t *)dev;
     e->kv_half_stride = (size_t)e->nkv_l * tile;        // page-major: layer l's K tiles, then its V tiles, inside every page
-    e->kv_page_heads = (int)(slot_bytes / tile);
+    e->kv_page_heads = (int)(slot_bytes / tile), e->kv_shared = true;
     for (auto &kv : e->graphs) cudaGraphExecDestroy(kv.second);
     e->graphs.clear();
     e->mega_ready = e->tcd_ready = false;
@@ -678,6 +679,8 @@ struct PassRows {
     bool from_lanes;
     int logit_row0;   // first row that needs logits
     int logit_rows;   // 0 = skip lm_head + sampler
+    int lane = -1;    // prefill chunk: its rows are consecutive positions pos0 .. of this lane
+    int pos0 = 0;
 };
 
 // GEMV over `rows` rows in groups of <= 4 (the batch > 4 tensor-core path replaces this loop)
@@ -993,12 +996,12 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
 }
 
 // ---------------------------------------------------------------- batch / prefill pass (tcgen05 GEMM)
-static int get_map(b200llm_engine *e, const void *base, int64_t rows, int64_t cols, int box, const void **out) {
-    auto key = std::make_tuple(base, rows, cols, box);
+static int get_map(b200llm_engine *e, const void *base, int64_t rows, int64_t cols, int box, const void **out, int bk = 64) {
+    auto key = std::make_tuple(base, rows, cols, box + 1000 * bk);
     auto it = e->maps.find(key);
     if (it == e->maps.end()) {
         auto *m = new b200llm_engine::MapBox();
-        int rc = tc_make_map(m->b, base, rows, cols, box);
+        int rc = tc_make_map(m->b, base, rows, cols, box, bk);
         if (rc) {
             delete m;
             return rc;
@@ -1025,9 +1028,10 @@ static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, i
     const void *mw, *mx, *mxl = nullptr;
     const uint16_t *xb = x_buf ? reinterpret_cast<const uint16_t *>(x_buf) : e->xb;
     const int64_t lo = xb == e->xb2 ? e->xb2_lo : e->xb_lo;
-    B200_TRY(get_map(e, w, N, K, 128, &mw));
-    B200_TRY(get_map(e, xb, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mx));
-    if (lo != 0) B200_TRY(get_map(e, xb + lo, e->cfg.max_rows, K, (T + 15) / 16 * 16, &mxl));
+    const int bk = tc_bk(T, lo != 0);
+    B200_TRY(get_map(e, w, N, K, 128, &mw, bk));
+    B200_TRY(get_map(e, xb, e->cfg.max_rows, K, tc_x_box(N, T), &mx, bk));
+    if (lo != 0) B200_TRY(get_map(e, xb + lo, e->cfg.max_rows, K, tc_x_box(N, T), &mxl, bk));
     int accumulate = 1;
     if (out_swiglu != nullptr) {
         accumulate = 0;
@@ -1039,7 +1043,7 @@ static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, i
         }
     }
     B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, e->tc_pdl, out_swiglu, mxl,
-                            out_swiglu != nullptr ? e->xb2_lo : 0));
+                            out_swiglu != nullptr ? e->xb2_lo : 0, bk));
     e->launches++;
     return B200LLM_OK;
 }
@@ -1076,7 +1080,24 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         if (want > 6) want = 6;
         at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
         at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
-        B200_TRY(attn_decode_launch(at, st, pdl, e->xb, e->xb_lo));  // output rounded to bf16 straight into the o_proj operand
+        // (short contexts: the decode-style kernel, one CTA group per row, still wins -- 296 ids: 8.9 vs 9.7 ms; from ~512 keys on
+        // the tiled kernel does -- 1024 ids: 27.8 vs 30.2 ms, 7B at 2072 ids: 132 vs 182 ms)
+        if (pr.lane >= 0 && pr.pos0 + rows >= 512 && getenv("B200LLM_NO_PREFILL_ATTN") == nullptr) {
+            // prefill chunk: query-tiled causal attention on the tensor cores (attn_prefill.cu) instead of one decode-style
+            // pass over the whole prefix per query row; output as bf16 hi + lo straight into the o_proj operand
+            // rows of [head_dim] bf16 from the layer's K (V) base to the end of what page ids can reach: the layer's own region in
+            // a pool of this engine's own, the rest of the whole pool when pages are page-major slots of a shared one
+            const int64_t all_rows = (int64_t)e->n_pages * e->kv_page_heads * c.page_tokens;
+            const int64_t k_rows = e->kv_shared ? all_rows - (int64_t)((kl - e->kv) / ((size_t)c.head_dim * 2)) : all_rows;
+            const int64_t v_rows = e->kv_shared ? all_rows - (int64_t)((vl - e->kv) / ((size_t)c.head_dim * 2)) : all_rows;
+            const void *mk, *mv;
+            B200_TRY(get_map(e, kl, k_rows, c.head_dim, c.page_tokens, &mk));
+            B200_TRY(get_map(e, vl, v_rows, c.head_dim, c.page_tokens, &mv));
+            B200_TRY(attn_prefill_launch(mk, mv, e->q, nullptr, e->xb, e->xb_lo, e->page_table + (size_t)pr.lane * c.max_pages_per_lane,
+                                         c.max_pages_per_lane, rows, pr.pos0, n_q, n_kv, c.head_dim, e->kv_page_heads, st, pdl));
+        } else {
+            B200_TRY(attn_decode_launch(at, st, pdl, e->xb, e->xb_lo));  // output rounded to bf16 straight into the o_proj operand
+        }
         if (tp) {
             B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->delta, c.d, rows, false));
             B200_TRY(tp_allreduce_add(e, rows));
@@ -1160,6 +1181,7 @@ int b200llm_prefill(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t
         pr.rows = n - c0 < c.max_rows ? n - c0 : c.max_rows;
         pr.row_lane = e->pf_lane + c0, pr.row_pos = e->pf_pos + c0, pr.row_token = e->pf_token + c0;
         pr.from_lanes = false;
+        pr.lane = lane, pr.pos0 = pos0 + c0;
         const bool is_last = c0 + pr.rows == n;
         pr.logit_row0 = pr.rows - 1;
         pr.logit_rows = is_last ? 1 : 0;
@@ -1379,6 +1401,18 @@ int b200llm_op_attn_decode(const b200llm_attn_args *a, void *stream) {
     return attn_decode_launch(*a, (cudaStream_t)stream, false);
 }
 
+int b200llm_op_attn_prefill(const b200llm_attn_prefill_args *a, void *stream) {
+    B200_REQUIRE(a && a->q && a->out && a->k_pages && a->v_pages && a->page_table_row, "op_attn_prefill: NULL argument");
+    int rc = require_device_any();
+    if (rc) return rc;
+    const int kvph = a->kv_page_heads > 0 ? a->kv_page_heads : a->n_kv;
+    alignas(128) unsigned char mk[128], mv[128];
+    B200_TRY(tc_make_map(mk, a->k_pages, (int64_t)a->n_pages * kvph * 16, a->head_dim, 16));
+    B200_TRY(tc_make_map(mv, a->v_pages, (int64_t)a->n_pages * kvph * 16, a->head_dim, 16));
+    return attn_prefill_launch(mk, mv, a->q, a->out, nullptr, 0, a->page_table_row, a->n_ptab, a->rows, a->pos0, a->n_q, a->n_kv,
+                               a->head_dim, kvph, (cudaStream_t)stream, false);
+}
+
 int b200llm_op_attn_scratch_bytes(int32_t bs, int32_t n_q, int32_t n_kv, int32_t head_dim, int32_t n_splits,
                                   size_t *bytes) {
     B200_REQUIRE(bytes && bs >= 1 && n_q >= 1 && n_kv >= 1 && n_splits >= 1, "op_attn_scratch_bytes: bad arguments");
@@ -1392,9 +1426,10 @@ int b200llm_op_gemm_tc(const void *w, const void *x, float *out, int64_t out_str
     int rc = require_device_any();
     if (rc) return rc;
     alignas(128) unsigned char mw[128], mx[128];
-    B200_TRY(tc_make_map(mw, w, N, K, 128));
-    B200_TRY(tc_make_map(mx, x, T, K, (T + 15) / 16 * 16));
-    return tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, (cudaStream_t)stream, false);
+    const int bk = tc_bk(T, false);
+    B200_TRY(tc_make_map(mw, w, N, K, 128, bk));
+    B200_TRY(tc_make_map(mx, x, T, K, tc_x_box(N, T), bk));
+    return tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, (cudaStream_t)stream, false, nullptr, nullptr, 0, bk);
 }
 
 int b200llm_op_sample(const b200llm_sample_args *a, void *stream) {

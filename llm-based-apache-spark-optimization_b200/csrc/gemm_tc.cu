@@ -37,6 +37,8 @@ struct TcParams {
     int32_t tmem_cols;   // power of two >= max(32, bn)
     int32_t has_lo;       // 1: a second X map holds the bf16 lo parts (x - hi); both are multiplied, ~fp32-accurate activations
     int64_t swiglu_lo_off; // != 0: lo parts of the fused SwiGLU output go to out_swiglu + swiglu_lo_off
+    int32_t bk;           // k per stage: 64 (128-byte swizzle rows) or 32 (64-byte swizzle rows: half the stage, twice the stages)
+    int32_t cs;           // CTAs per cluster (1, 2 or 4): neighbouring weight tiles that share every activation tile
     uint16_t *out_swiglu; // when set (needs one k split): rows (2i, 2i+1) = (gate_i, up_i) -> bf16 silu(gate) * up at
                           // out_swiglu[t, i], row stride N / 2, instead of the fp32 output
 };
@@ -49,14 +51,35 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m
         : "memory");
 }
 
+// The same box, delivered to the same shared-memory offset of every CTA of the cluster in `mask` (and counted on each one's
+// barrier at the same offset).  The source is always THIS GPU's memory: the activation buffers of the engine's own
+// workspace (TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
+// GPU's memory hung the GPU).
+__device__ __forceinline__ void tma_load_2d_mc(void *smem_dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar, uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // K-major operand tile in shared memory, 128-byte swizzle, rows of 128 bytes, 8-row groups 1024 B apart
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr, int bk = 64) {
     uint64_t d = 0;
     d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);          // start address
     d |= (uint64_t)1 << 16;                               // leading byte offset (unused for swizzled K-major)
-    d |= (uint64_t)(1024 >> 4) << 32;                     // stride byte offset between 8-row groups
+    d |= (uint64_t)((bk == 64 ? 1024 : 512) >> 4) << 32;  // stride byte offset between 8-row groups (rows of 2 bk bytes)
     d |= (uint64_t)1 << 46;                               // descriptor version (sm_100)
-    d |= (uint64_t)2 << 61;                               // SWIZZLE_128B
+    d |= (uint64_t)(bk == 64 ? 2 : 4) << 61;              // SWIZZLE_128B / SWIZZLE_64B
     return d;
 }
 
@@ -72,8 +95,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                const __grid_constant__ CUtensorMap map_xl, const __grid_constant__ TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int a_bytes = kTcBM * kTcBK * 2;          // 16 KB
-    const int b_bytes = p.bn * kTcBK * 2;           // multiple of 2 KB (bn % 16 == 0)
+    const int a_bytes = kTcBM * p.bk * 2;           // 16 KB (8 KB at bk 32)
+    const int b_bytes = p.bn * p.bk * 2;            // multiple of 1 KB (bn % 16 == 0)
     const int b_pad = (b_bytes + 1023) & ~1023;
     const int stage_bytes = a_bytes + (p.has_lo ? 2 : 1) * b_pad;
     uint8_t *tiles = smem;
@@ -84,12 +107,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
 
     const int row0 = blockIdx.x * kTcBM;
     const int k0 = blockIdx.y * p.k_per_split;
-    const int n_k = min(p.k_per_split, p.K - k0) / kTcBK;
+    const int n_k = min(p.k_per_split, p.K - k0) / p.bk;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], 1);
+            mbar_init(&empty[s], (uint32_t)p.cs);   // every CTA of the cluster writes a slice of the stage's activation tile
         }
         mbar_init(tmem_full, 1);
         mbar_fence_init();
@@ -105,8 +128,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (p.cs > 1) cluster_sync_all();   // the peers' barriers exist before anything is sent to them
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = *tmem_slot;
+    const uint32_t crank = p.cs > 1 ? cluster_ctarank() : 0u;
+    const uint16_t cmask = (uint16_t)((1u << p.cs) - 1u);
     pdl_trigger();
     pdl_wait();  // X (and the residual in `out`) come from the previous kernel
 
@@ -117,9 +143,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                 if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
                 uint8_t *a_dst = tiles + (size_t)s * stage_bytes;
                 mbar_expect_tx(&full[s], (uint32_t)(a_bytes + (p.has_lo ? 2 : 1) * b_bytes));
-                tma_load_2d(a_dst, &map_w, k0 + i * kTcBK, row0, &full[s]);
-                tma_load_2d(a_dst + a_bytes, &map_x, k0 + i * kTcBK, 0, &full[s]);
-                if (p.has_lo) tma_load_2d(a_dst + a_bytes + b_pad, &map_xl, k0 + i * kTcBK, 0, &full[s]);
+                tma_load_2d(a_dst, &map_w, k0 + i * p.bk, row0, &full[s]);
+                if (p.cs == 1) {
+                    tma_load_2d(a_dst + a_bytes, &map_x, k0 + i * p.bk, 0, &full[s]);
+                    if (p.has_lo) tma_load_2d(a_dst + a_bytes + b_pad, &map_xl, k0 + i * p.bk, 0, &full[s]);
+                } else {
+                    // this CTA fetches rows [rank * bn / cs, +bn / cs) of the activation tile (the maps' box) for the whole cluster
+                    const int r0 = (int)crank * (p.bn / p.cs);
+                    const int soff = r0 * p.bk * 2;
+                    tma_load_2d_mc(a_dst + a_bytes + soff, &map_x, k0 + i * p.bk, r0, &full[s], cmask);
+                    if (p.has_lo) tma_load_2d_mc(a_dst + a_bytes + b_pad + soff, &map_xl, k0 + i * p.bk, r0, &full[s], cmask);
+                }
             }
         }
     } else if (warp == 1) {
@@ -133,11 +167,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                 mbar_wait(&full[s], use & 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t a_addr = smem_u32(tiles + (size_t)s * stage_bytes);
-                const uint64_t adesc = umma_desc_sw128(a_addr);
-                const uint64_t bdesc = umma_desc_sw128(a_addr + a_bytes);
-                const uint64_t bdesc_lo = umma_desc_sw128(a_addr + a_bytes + b_pad);
+                const uint64_t adesc = umma_desc_sw128(a_addr, p.bk);
+                const uint64_t bdesc = umma_desc_sw128(a_addr + a_bytes, p.bk);
+                const uint64_t bdesc_lo = umma_desc_sw128(a_addr + a_bytes + b_pad, p.bk);
 #pragma unroll
-                for (int k = 0; k < kTcBK / 16; ++k) {
+                for (int k = 0; k < p.bk / 16; ++k) {
                     const uint32_t accum = (i > 0 || k > 0) ? 1u : 0u;
                     // advancing 16 k = 32 bytes inside the 128-byte swizzle row: +2 in the address field
                     asm volatile(
@@ -152,10 +186,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                             "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc_lo + (uint64_t)(2 * k)), "r"(idesc), "r"(1u)
                             : "memory");
                 }
-                // frees the stage once the MMAs above have read it
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                                 smem_u32(&empty[s]))
-                             : "memory");
+                // frees the stage once the MMAs above have read it -- in every CTA of the cluster, whose producers write into it
+                if (p.cs == 1)
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                     smem_u32(&empty[s]))
+                                 : "memory");
+                else
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                                     smem_u32(&empty[s])),
+                                 "h"(cmask)
+                                 : "memory");
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                              smem_u32(tmem_full))
@@ -222,6 +262,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
     __syncthreads();
+    if (p.cs > 1) cluster_sync_all();   // nobody leaves while a peer may still signal its barriers
     if (warp == 2) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)p.tmem_cols)
                      : "memory");
@@ -248,18 +289,19 @@ static int load_encode() {
 }
 
 // bf16 row-major [rows, cols] -> 2-D map with a [box_rows x 64] box, 128-byte swizzle, zero fill out of bounds
-int tc_make_map(void *map_out, const void *base, int64_t rows, int64_t cols, int box_rows) {
+int tc_make_map(void *map_out, const void *base, int64_t rows, int64_t cols, int box_rows, int bk) {
     int rc = load_encode();
     if (rc) return rc;
     B200_REQUIRE(cols % 8 == 0 && ((uintptr_t)base % 16) == 0 && box_rows >= 1 && box_rows <= 256,
                  "tensor map: bad shape/alignment");
     cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
     cuuint64_t gstr[1] = {(cuuint64_t)cols * 2};
-    cuuint32_t box[2] = {(cuuint32_t)kTcBK, (cuuint32_t)box_rows};
+    B200_REQUIRE(bk == 64 || bk == 32, "tensor map: k per box must be 64 or 32");
+    cuuint32_t box[2] = {(cuuint32_t)bk, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode(reinterpret_cast<CUtensorMap *>(map_out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
                           const_cast<void *>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed with %d (rows %lld cols %lld box %d)", (int)r, (long long)rows,
@@ -269,16 +311,40 @@ int tc_make_map(void *map_out, const void *base, int64_t rows, int64_t cols, int
     return B200LLM_OK;
 }
 
+// CTAs per cluster for an [N, K] x [T, K] GEMM: neighbouring weight tiles share the activation tile, which each CTA fetches a
+// slice of and multicasts (the activation tile is re-read per weight tile: at 256 rows with hi + lo operands it is 4x the
+// weight bytes of a stage).  The activation maps' box must be tc_x_box(N, T) rows.  OFF by default (B200LLM_TC_CLUSTER=2|4
+// turns it on): measured on the prefill of 296 / 2072 ids and on batch-64 decode, clusters of 2 are level and clusters of
+// 4 are 10-15 % slower -- L2 reads of the activation tile are not what bounds this kernel (profiles/prefill_r2.txt).
+int tc_cluster_size(int N, int T) {
+    static const int forced = getenv("B200LLM_TC_CLUSTER") ? atoi(getenv("B200LLM_TC_CLUSTER")) : 1;
+    const int tiles = N / kTcBM, bn = (T + 15) / 16 * 16;
+    for (int cs = forced; cs > 1; cs >>= 1)
+        if (tiles % cs == 0 && (bn / cs) % 8 == 0 && bn % cs == 0) return cs;
+    return 1;
+}
+int tc_x_box(int N, int T) { return (T + 15) / 16 * 16 / tc_cluster_size(N, T); }
+// k per stage: 64; B200LLM_TC_BK=32 halves the stage (64-byte swizzle rows) for twice the stages -- 256 rows with hi + lo
+// operands are 80 KB per 64-wide stage, i.e. two stages.  Measured level to 8 % slower, so the pipeline depth is not
+// the limit either: ncu shows the tensor pipe active throughout at ~36 % of the cuBLAS rate (profiles/prefill_r2.txt).
+int tc_bk(int T, bool has_lo) {
+    static const int forced = getenv("B200LLM_TC_BK") ? atoi(getenv("B200LLM_TC_BK")) : 64;
+    (void)T, (void)has_lo;
+    return forced == 32 ? 32 : 64;
+}
+
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
                    int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu, const void *map_x_lo,
-                   int64_t swiglu_lo_off) {
+                   int64_t swiglu_lo_off, int bk) {
+    B200_REQUIRE(bk == 64 || bk == 32, "gemm_tc: bk must be 64 or 32");
     B200_REQUIRE(T >= 1 && T <= 256 && N % kTcBM == 0 && K % kTcBK == 0, "gemm_tc: need 1 <= T <= 256, N %% 128 == 0, K %% 64 == 0 (T %d N %d K %d)", T, N, K);
     TcParams p{};
     p.out = out, p.out_stride = out_stride, p.T = T, p.N = N, p.K = K;
     p.bn = (T + 15) / 16 * 16;
     const int tiles = N / kTcBM;
     int ks = kNumSMs / tiles;
-    const int k_iters = K / kTcBK;
+    const int k_iters = K / kTcBK;   // (k splits stay multiples of 64)
+    p.bk = bk;
     if (ks < 1) ks = 1;
     if (ks > k_iters) ks = k_iters;
     if (!accumulate || out_swiglu != nullptr) ks = 1;  // a plain store / the fused SwiGLU needs the whole K in one CTA
@@ -292,13 +358,23 @@ int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out
     int cols = 32;
     while (cols < ((p.has_lo && p.bn <= 128) ? 2 * p.bn : p.bn)) cols <<= 1;
     p.tmem_cols = cols;
-    const int stage_bytes = kTcBM * kTcBK * 2 + (p.has_lo ? 2 : 1) * ((p.bn * kTcBK * 2 + 1023) & ~1023);
+    const int stage_bytes = kTcBM * bk * 2 + (p.has_lo ? 2 : 1) * ((p.bn * bk * 2 + 1023) & ~1023);
     int stages = (200 * 1024) / stage_bytes;
     p.stages = stages > 8 ? 8 : (stages < 2 ? 2 : stages);
     const size_t smem = (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16 + 1024;
     // per launch: the attribute belongs to the (function, device) pair, and callers may use several devices and threads
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    p.cs = tc_cluster_size(N, T);
     LaunchCfg lc(dim3(tiles, ks), dim3(kTcThreads), smem, stream, pdl);
+    cudaLaunchAttribute attrs[2];
+    int n_attr = 0;
+    if (pdl) attrs[n_attr++] = lc.attr[0];
+    if (p.cs > 1) {
+        attrs[n_attr].id = cudaLaunchAttributeClusterDimension;
+        attrs[n_attr].val.clusterDim.x = (unsigned)p.cs, attrs[n_attr].val.clusterDim.y = 1, attrs[n_attr].val.clusterDim.z = 1;
+        ++n_attr;
+    }
+    lc.cfg.attrs = n_attr ? attrs : nullptr, lc.cfg.numAttrs = n_attr;
     B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, gemm_tc_kernel, *reinterpret_cast<const CUtensorMap *>(map_w),
                                     *reinterpret_cast<const CUtensorMap *>(map_x),
                                     *reinterpret_cast<const CUtensorMap *>(map_x_lo ? map_x_lo : map_x), p));

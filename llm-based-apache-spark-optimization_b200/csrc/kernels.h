@@ -20,6 +20,12 @@ size_t attn_scratch_bytes(int bs, int n_q, int n_kv, int head_dim, int n_splits)
 // launch keeps tickets (tickets must stay zero between launches).
 constexpr size_t kAttnTicketBytes = 256 * 1024;  // 65536 (row, kv head) tickets
 
+// attn_prefill.cu: causal attention of `rows` consecutive positions of one lane (prefill chunk) on tcgen05; map_k / map_v are
+// tc_make_map(base of the layer's K / V region, rows of 16-token page tiles, head_dim, box 16)
+int attn_prefill_launch(const void *map_k, const void *map_v, const float *q, float *out, void *out_bf16, int64_t out_lo_off,
+                        const int32_t *page_table_row, int n_ptab, int rows, int pos0, int n_q, int n_kv, int head_dim,
+                        int kv_page_heads, cudaStream_t stream, bool pdl);
+
 // misc.cu
 struct EmbedArgs {
     const void *embed;        // bf16 [vocab, d]
@@ -54,10 +60,13 @@ struct SampleDev {
 int sample_launch(const SampleDev &a, cudaStream_t stream, bool pdl);
 
 // gemm_tc.cu: tcgen05 GEMM  out[t, n] (+)= sum_k X[t, k] W[n, k]  (bf16 in, fp32 out), T <= 256
-int tc_make_map(void *map_out_128B, const void *base, int64_t rows, int64_t cols, int box_rows);
+int tc_make_map(void *map_out_128B, const void *base, int64_t rows, int64_t cols, int box_rows, int bk = 64);
+int tc_bk(int T, bool has_lo);       // k per stage (64 or 32) tc_gemm_launch should be given for T rows: the maps' box is [box_rows x bk]
+int tc_cluster_size(int N, int T);   // CTAs per cluster tc_gemm_launch will use
+int tc_x_box(int N, int T);          // rows of the activation maps' box for that launch: ceil16(T) / cluster size
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
                    int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu = nullptr,
-                   const void *map_x_lo = nullptr, int64_t swiglu_lo_off = 0);
+                   const void *map_x_lo = nullptr, int64_t swiglu_lo_off = 0, int bk = 64);
 // tp_ar.cu: one-shot all-reduce + residual add over NVLink peer memory (h += sum over ranks of delta)
 constexpr int kTpMaxRanks = 8;
 int tp_allreduce_add_launch(float *h, const float *delta, int n, float *const *inbox, unsigned *const *flags,

@@ -286,3 +286,48 @@ def test_gemv_tile_major_tcgen05_phase(N, K, k_split):
     _lib.check(_lib.lib.b200llm_op_gemv_tm(wt.data_ptr(), xd.data_ptr(), out.data_ptr(), N, K, k_split,
                                            torch.cuda.current_stream().cuda_stream))
     _close(out.cpu(), ref, 2e-5)
+
+
+@pytest.mark.parametrize("nq,nkv,hd,pos0,rows,kvph", [(4, 2, 128, 0, 128, 0), (8, 2, 64, 0, 200, 0), (6, 2, 128, 300, 77, 0),
+                                                        (4, 4, 128, 1000, 256, 0), (4, 2, 128, 37, 150, 7)])
+def test_attn_prefill_matches_fp32_attention(nq, nkv, hd, pos0, rows, kvph):
+    """Causal prefill attention on tcgen05 (csrc/attn_prefill.cu) against plain fp32 softmax(q k^T / sqrt(hd)) v in torch on
+    the same bf16 K/V: chunks that start at position 0 and in the middle of a sequence, ragged row counts, GQA groups 1..3,
+    both head sizes, scattered pages, and a page stride larger than n_kv (the shared-pool layout)."""
+    import ctypes as C
+    from b200llm import _lib
+    gen = torch.Generator().manual_seed(1000 + rows + pos0)
+    n_tok = pos0 + rows
+    n_lane_pages = (n_tok + 15) // 16
+    n_pages = n_lane_pages + 5
+    stride = kvph or nkv
+    order = torch.randperm(n_pages, generator=gen)[:n_lane_pages]
+    max_pages = n_lane_pages + 3
+    ptab = torch.zeros(max_pages, dtype=torch.int32)
+    ptab[:n_lane_pages] = order.to(torch.int32)
+    kp = torch.zeros(n_pages, stride, 16, hd, dtype=torch.bfloat16)
+    vp = torch.zeros_like(kp)
+    K = torch.randn(n_tok, nkv, hd, generator=gen).to(torch.bfloat16)
+    V = torch.randn(n_tok, nkv, hd, generator=gen).to(torch.bfloat16)
+    for t in range(n_tok):
+        kp[order[t // 16], :nkv, t % 16] = K[t]
+        vp[order[t // 16], :nkv, t % 16] = V[t]
+    q = torch.randn(rows, nq * hd, generator=gen)
+    qd, kpd, vpd, ptd = q.cuda(), kp.cuda(), vp.cuda(), ptab.cuda()
+    out = torch.full_like(qd, float("nan"))
+    a = _lib.AttnPrefillArgs(qd.data_ptr(), out.data_ptr(), kpd.data_ptr(), vpd.data_ptr(), ptd.data_ptr(), max_pages, rows, pos0,
+                             nq, nkv, hd, n_pages, kvph)
+    _lib.check(_lib.lib.b200llm_op_attn_prefill(C.byref(a), torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    # reference
+    rep = nq // nkv
+    Kf, Vf = K.float(), V.float()
+    ref = torch.empty(rows, nq, hd)
+    for h in range(nq):
+        s = (q.view(rows, nq, hd)[:, h] @ Kf[:, h // rep].t()) / hd ** 0.5                     # [rows, n_tok]
+        mask = torch.arange(n_tok)[None, :] > (pos0 + torch.arange(rows))[:, None]
+        ref[:, h] = torch.softmax(s.masked_fill(mask, float("-inf")), dim=-1) @ Vf[:, h // rep]
+    got = out.cpu().view(rows, nq, hd)
+    assert torch.isfinite(got).all()
+    err = float((got - ref).abs().max() / ref.abs().max())
+    assert err <= 2e-4, f"rel err {err:.3e}"

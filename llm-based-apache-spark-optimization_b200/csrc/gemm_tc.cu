@@ -130,7 +130,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
     __syncthreads();
     if (p.cs > 1) cluster_sync_all();   // the peers' barriers exist before anything is sent to them
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_d = *tmem_slot;
+    const uint32_t tmem_d = __shfl_sync(0xffffffffu, *tmem_slot, 0);
     const uint32_t crank = p.cs > 1 ? cluster_ctarank() : 0u;
     const uint16_t cmask = (uint16_t)((1u << p.cs) - 1u);
     pdl_trigger();
@@ -157,49 +157,59 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // hi and lo tiles of a stage are contiguous (bn * 128 B is a multiple of 1 KB), so up to bn = 128 they are ONE
+        // MMA issue: the whole warp walks the loop, converged, one elected lane issues -- descriptors and addresses are then
+        // warp-uniform and stay in uniform registers (issued from lane 0 of a diverged warp, every tcgen05.mma sat in an
+        // ELECT / R2UR.BROADCAST / BRA.U.ANY loop of ~145 clk, more than a 128 x 64..128 MMA takes to execute)
+        {
+            // hi and lo tiles of a stage are contiguous (bn * 2 bk bytes is a multiple of 1 KB), so up to bn = 128 they are ONE
             // B operand of N = 2 bn: columns [0, bn) = W x hi, [bn, 2 bn) = W x lo, added in the epilogue
             const bool stacked = p.has_lo && p.bn <= 128;
             const uint32_t idesc = umma_idesc_bf16(kTcBM, stacked ? 2 * p.bn : p.bn);
+            const uint32_t tiles_a = smem_u32(tiles);
             for (int i = 0; i < n_k; ++i) {
                 const int s = i % p.stages, use = i / p.stages;
                 mbar_wait(&full[s], use & 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t a_addr = smem_u32(tiles + (size_t)s * stage_bytes);
+                const uint32_t a_addr = tiles_a + (uint32_t)s * (uint32_t)stage_bytes;
                 const uint64_t adesc = umma_desc_sw128(a_addr, p.bk);
                 const uint64_t bdesc = umma_desc_sw128(a_addr + a_bytes, p.bk);
                 const uint64_t bdesc_lo = umma_desc_sw128(a_addr + a_bytes + b_pad, p.bk);
-#pragma unroll
-                for (int k = 0; k < p.bk / 16; ++k) {
-                    const uint32_t accum = (i > 0 || k > 0) ? 1u : 0u;
-                    // advancing 16 k = 32 bytes inside the 128-byte swizzle row: +2 in the address field
-                    asm volatile(
-                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-                        "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc + (uint64_t)(2 * k)), "r"(idesc), "r"(accum)
-                        : "memory");
-                    if (p.has_lo && !stacked)  // W x lo(X) into the same accumulator
+                uint32_t el;
+                asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.b32 %0, 1, 0, P;\n\t}" : "=r"(el));
+                if (el) {
+                    for (int k = 0; k < p.bk / 16; ++k) {
+                        const uint32_t accum = (i > 0 || k > 0) ? 1u : 0u;
+                        // advancing 16 k = 32 bytes inside the swizzle row: +2 in the address field
                         asm volatile(
                             "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                             "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-                            "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc_lo + (uint64_t)(2 * k)), "r"(idesc), "r"(1u)
+                            "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc + (uint64_t)(2 * k)), "r"(idesc), "r"(accum)
                             : "memory");
+                        if (p.has_lo && !stacked)  // W x lo(X) into the same accumulator
+                            asm volatile(
+                                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+                                "l"(adesc + (uint64_t)(2 * k)), "l"(bdesc_lo + (uint64_t)(2 * k)), "r"(idesc), "r"(1u)
+                                : "memory");
+                    }
+                    // frees the stage once the MMAs above have read it -- in every CTA of the cluster, whose producers write into it
+                    if (p.cs == 1)
+                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                         smem_u32(&empty[s]))
+                                     : "memory");
+                    else
+                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                                         smem_u32(&empty[s])),
+                                     "h"(cmask)
+                                     : "memory");
                 }
-                // frees the stage once the MMAs above have read it -- in every CTA of the cluster, whose producers write into it
-                if (p.cs == 1)
-                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                                     smem_u32(&empty[s]))
-                                 : "memory");
-                else
-                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-                                     smem_u32(&empty[s])),
-                                 "h"(cmask)
-                                 : "memory");
+                __syncwarp();
             }
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                             smem_u32(tmem_full))
-                         : "memory");
+            if (lane == 0)
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                 smem_u32(tmem_full))
+                             : "memory");
+            __syncwarp();
         }
     } else if (warp >= 4) {
         // ===== epilogue: this warp owns accumulator lanes 32*(warp%4) .. +31 = 32 weight rows =====

@@ -544,3 +544,36 @@ def test_scheduler_fails_only_the_offending_request():
     assert res["greedy_budget"][:10] == want[0]
     sched.shutdown()
     eng.close()
+
+
+def test_c_abi_refuses_rows_outside_the_lanes_pages():
+    """The C ABI itself (below the Python wrapper, which would grow the page table first) refuses a prefill or a
+    decode whose K/V rows would land outside the pages the caller put in the lane's table, a lane or step count out
+    of range, and a prompt beyond the lane context -- before any launch, and the engine keeps working afterwards."""
+    import ctypes as C
+    from b200llm import _lib
+    geo = lo.GEOMETRIES["tiny"]
+    sd = lo.make_weights(geo, 0xB200, sigma=0.08)
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    eng = _engine("tiny", sd, max_lanes=2, max_ctx=64, max_rows=4)
+    lib, h = _lib.lib, eng._h
+    lane = eng.open_lane()
+    ids = np.ascontiguousarray(wg.gen_tokens(20, 5, geo.vocab), dtype=np.int32)
+    p_ids = ids.ctypes.data_as(C.POINTER(C.c_int32))
+    # no pages in the lane's table yet: 20 rows have nowhere to go
+    assert lib.b200llm_prefill(h, lane, p_ids, 20, 0) == _lib.EINVAL
+    assert b"pages" in lib.b200llm_last_error()
+    assert lib.b200llm_prefill(h, 7, p_ids, 20, 0) == _lib.EINVAL               # lane out of range
+    assert lib.b200llm_prefill(h, lane, p_ids, 20, 60) == _lib.EINVAL           # 60 + 20 > 64-token context
+    assert lib.b200llm_prefill(h, lane, p_ids, 0, 0) == _lib.EINVAL
+    eng.prefill(lane, ids)                                                       # the wrapper sets 2 pages (32 rows), pos = 20
+    one = (C.c_int32 * 1)(lane)
+    assert lib.b200llm_decode(h, one, 1, 13) == _lib.EINVAL                      # 20 + 13 > 32 rows of its 2 pages
+    assert b"pages" in lib.b200llm_last_error()
+    bad = (C.c_int32 * 1)(5)
+    assert lib.b200llm_decode(h, bad, 1, 1) == _lib.EINVAL
+    assert lib.b200llm_decode(h, one, 1, 0) == _lib.EINVAL
+    assert lib.b200llm_decode(h, one, 9, 1) == _lib.EINVAL                       # more lanes than max_rows
+    got = eng.decode([lane], 12)[:, 0].tolist()                                  # refused calls left the lane untouched
+    assert got == orc.greedy(ids.tolist(), 12)[0]
+    eng.close()

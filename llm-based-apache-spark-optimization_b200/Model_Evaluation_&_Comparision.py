@@ -90,7 +90,7 @@ def engine_bench(model: str, batch_sizes, prompt_len: int, new_tokens: int, n_tt
     geo = geometry.resolve(model)
     w = weights.random_init(geo, 0xB200, local)
     max_bs = max(batch_sizes)
-    eng = Engine(geo, w, device=local, max_lanes=max_bs, max_ctx=prompt_len + new_tokens + 32, max_rows=max(64, max_bs))
+    eng = Engine(geo, w, device=local, max_lanes=max_bs, max_ctx=prompt_len + new_tokens + 32, max_rows=256)   # prefill in 256-row chunks, decode batches up to 256 lanes
     rng = np.random.default_rng(7 + local)
     out = {"model": model, "ttft_ms_p50": None, "decode": []}
     ttfts = []

@@ -1017,14 +1017,18 @@ static bool tc_usable(const b200llm_engine *e, int rows) {
     auto okn = [](int n) { return n % 128 == 0; };
     auto okk = [](int k) { return k % 64 == 0; };
     const bool lm_ok = c.tp_size > 1 || okn(c.vocab);   // tensor parallel keeps the GEMV lm_head (partials are gathered)
-    return c.use_tc && rows > 4 && rows <= 256 && okn((e->nq_l + 2 * e->nkv_l) * c.head_dim) && okn(c.d) &&
+    // from 3 rows on the GEMM path is faster per step than the per-phase GEMV kernels (3B: 2.4 ms at any batch <= 16 against
+    // 2.3 / 3.3 ms at 2 / 4 rows; profiles/harness_r2.txt)
+    static const int min_rows = getenv("B200LLM_TC_MIN_ROWS") ? atoi(getenv("B200LLM_TC_MIN_ROWS")) : 3;
+    return c.use_tc && rows >= min_rows && rows <= 256 && okn((e->nq_l + 2 * e->nkv_l) * c.head_dim) && okn(c.d) &&
            okn(2 * e->ffn_l) && lm_ok && okk(c.d) && okk(e->nq_l * c.head_dim) && okk(e->ffn_l) &&
            getenv("B200LLM_NO_TC") == nullptr;
 }
 
 // out (+)= X W^T through the tcgen05 kernel; X = e->xb viewed as [max_rows, K]
 static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, int64_t out_stride, int T,
-                   bool add_to_existing, bool prezeroed = false, const void *x_buf = nullptr, void *out_swiglu = nullptr) {
+                   bool add_to_existing, bool prezeroed = false, const void *x_buf = nullptr, void *out_swiglu = nullptr,
+                   const void *w_tm = nullptr) {
     const void *mw, *mx, *mxl = nullptr;
     const uint16_t *xb = x_buf ? reinterpret_cast<const uint16_t *>(x_buf) : e->xb;
     const int64_t lo = xb == e->xb2 ? e->xb2_lo : e->xb_lo;
@@ -1042,8 +1046,11 @@ static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, i
             B200_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)T * out_stride * 4, e->stream));
         }
     }
+    // the tile-major copy (bound for the persistent decode kernel) serves this kernel too: one 16 KB bulk copy per weight tile
+    static const bool use_tm = !(getenv("B200LLM_TC_TM") && atoi(getenv("B200LLM_TC_TM")) == 0);
+    if (!use_tm || bk != 64 || tc_cluster_size(N, T) != 1) w_tm = nullptr;
     B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, e->tc_pdl, out_swiglu, mxl,
-                            out_swiglu != nullptr ? e->xb2_lo : 0, bk));
+                            out_swiglu != nullptr ? e->xb2_lo : 0, bk, w_tm));
     e->launches++;
     return B200LLM_OK;
 }
@@ -1069,7 +1076,7 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
         uint8_t *vl = kl + e->kv_half_stride;
         B200_TRY(rmsnorm_bf16_launch(e->h, w.attn_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->qkv_out, qkv_w, e->xb_lo));
-        B200_TRY(tc_gemm(e, w.wqkv, qkv_w, c.d, e->qkv_out, qkv_w, rows, false, true));
+        B200_TRY(tc_gemm(e, w.wqkv, qkv_w, c.d, e->qkv_out, qkv_w, rows, false, true, nullptr, nullptr, w.wqkv_tm));
         B200_TRY(rope_append_launch(e->qkv_out, e->q, kl, vl, e->inv_freq, pr.row_lane, pr.row_pos, e->page_table, rows,
                                     n_q, n_kv, c.head_dim, c.page_tokens, c.max_pages_per_lane, st, pdl, e->kv_page_heads));
         b200llm_attn_args at{};
@@ -1078,6 +1085,8 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         at.page_tokens = c.page_tokens, at.max_pages_per_lane = c.max_pages_per_lane, at.kv_page_heads = e->kv_page_heads;
         int want = (kNumSMs + rows * n_kv - 1) / (rows * n_kv);
         if (want > 6) want = 6;
+        static const int forced_splits = getenv("B200LLM_BATCH_SPLITS") ? atoi(getenv("B200LLM_BATCH_SPLITS")) : 0;
+        if (forced_splits > 0 && pr.lane < 0) want = forced_splits;
         at.n_splits = want < 1 ? 1 : (want > e->attn_splits ? e->attn_splits : want);
         at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
         // (short contexts: the decode-style kernel, one CTA group per row, still wins -- 296 ids: 8.9 vs 9.7 ms; from ~512 keys on
@@ -1099,32 +1108,32 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
             B200_TRY(attn_decode_launch(at, st, pdl, e->xb, e->xb_lo));  // output rounded to bf16 straight into the o_proj operand
         }
         if (tp) {
-            B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->delta, c.d, rows, false));
+            B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->delta, c.d, rows, false, false, nullptr, nullptr, w.wo_tm));
             B200_TRY(tp_allreduce_add(e, rows));
         } else {
-            B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->h, c.d, rows, true));
+            B200_TRY(tc_gemm(e, w.wo, c.d, qd, e->h, c.d, rows, true, false, nullptr, nullptr, w.wo_tm));
         }
         // gate/up: with >= 74 row tiles the GEMM runs without a k split and applies SwiGLU in its epilogue
         const bool fuse_swiglu = 2 * ffn / 128 > kNumSMs / 2;
         if (fuse_swiglu) {
             B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, nullptr, 0, e->xb_lo));
-            B200_TRY(tc_gemm(e, w.wgu, 2 * ffn, c.d, e->gu_out, 2 * ffn, rows, false, true, nullptr, e->xb2));
+            B200_TRY(tc_gemm(e, w.wgu, 2 * ffn, c.d, e->gu_out, 2 * ffn, rows, false, true, nullptr, e->xb2, w.wgu_tm));
             if (tp) {
-                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->delta, c.d, rows, false, false, e->xb2));
+                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->delta, c.d, rows, false, false, e->xb2, nullptr, w.wdown_tm));
                 B200_TRY(tp_allreduce_add(e, rows));
             } else {
-                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->h, c.d, rows, true, false, e->xb2));
+                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->h, c.d, rows, true, false, e->xb2, nullptr, w.wdown_tm));
             }
             e->launches += 4;
         } else {
             B200_TRY(rmsnorm_bf16_launch(e->h, w.mlp_norm, e->xb, rows, c.d, c.rms_eps, st, pdl, e->gu_out, 2 * ffn, e->xb_lo));
-            B200_TRY(tc_gemm(e, w.wgu, 2 * ffn, c.d, e->gu_out, 2 * ffn, rows, false, true));
+            B200_TRY(tc_gemm(e, w.wgu, 2 * ffn, c.d, e->gu_out, 2 * ffn, rows, false, true, nullptr, nullptr, w.wgu_tm));
             B200_TRY(swiglu_bf16_launch(e->gu_out, e->xb, rows, ffn, st, pdl, e->xb_lo));
             if (tp) {
-                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->delta, c.d, rows, false));
+                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->delta, c.d, rows, false, false, nullptr, nullptr, w.wdown_tm));
                 B200_TRY(tp_allreduce_add(e, rows));
             } else {
-                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->h, c.d, rows, true));
+                B200_TRY(tc_gemm(e, w.wdown, c.d, ffn, e->h, c.d, rows, true, false, nullptr, nullptr, w.wdown_tm));
             }
             e->launches += 5;
         }
@@ -1135,7 +1144,7 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
     if (tp) return lm_head_and_sample(e, pr, advance);
     B200_TRY(rmsnorm_bf16_launch(e->h + (size_t)pr.logit_row0 * c.d, e->final_norm, e->xb, pr.logit_rows, c.d, c.rms_eps,
                                  st, pdl, nullptr, 0, e->xb_lo));
-    B200_TRY(tc_gemm(e, e->lm_head, c.vocab, c.d, e->logits, c.vocab, pr.logit_rows, false));
+    B200_TRY(tc_gemm(e, e->lm_head, c.vocab, c.d, e->logits, c.vocab, pr.logit_rows, false, false, nullptr, nullptr, e->lm_head_tm));
     SampleDev sd{};
     sd.a.logits = e->logits, sd.a.bs = pr.logit_rows, sd.a.vocab = c.vocab;
     sd.a.part_max = nullptr, sd.a.part_idx = nullptr, sd.a.n_part = 0;  // full-vocabulary argmax over the logits

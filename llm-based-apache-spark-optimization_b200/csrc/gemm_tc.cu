@@ -39,6 +39,9 @@ struct TcParams {
     int64_t swiglu_lo_off; // != 0: lo parts of the fused SwiGLU output go to out_swiglu + swiglu_lo_off
     int32_t bk;           // k per stage: 64 (128-byte swizzle rows) or 32 (64-byte swizzle rows: half the stage, twice the stages)
     int32_t cs;           // CTAs per cluster (1, 2 or 4): neighbouring weight tiles that share every activation tile
+    int32_t w_early;      // 1: the first ring of weight tiles is requested before griddepcontrol.wait
+    const uint8_t *w_tm;  // != NULL (bk 64): the TILE-MAJOR copy of W ([N/128][K/64] tiles of 16 KB, stored as the swizzled operand,
+                          // tcd.h): a weight tile is then ONE contiguous 16 KB bulk copy instead of a 2-D box of 128 rows of 128 bytes
     uint16_t *out_swiglu; // when set (needs one k split): rows (2i, 2i+1) = (gate_i, up_i) -> bf16 silu(gate) * up at
                           // out_swiglu[t, i], row stride N / 2, instead of the fp32 output
 };
@@ -134,6 +137,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
     const uint32_t crank = p.cs > 1 ? cluster_ctarank() : 0u;
     const uint16_t cmask = (uint16_t)((1u << p.cs) - 1u);
     pdl_trigger();
+    // The weights do not depend on the previous kernel: the first ring of weight tiles is requested BEFORE the wait, so a
+    // CTA that became resident while its predecessor still runs (programmatic dependent launch) has its HBM stream under
+    // way when the activations arrive.  The stage barrier expects the whole stage; the activation tiles follow the wait.
+    const int n_pre = p.w_early ? min(n_k, p.stages) : 0;
+    // tile-major weights: this CTA's tiles (row tile blockIdx.x, k blocks k0 / 64 ...) are consecutive 16 KB pieces
+    const uint8_t *w_tile0 = p.w_tm ? p.w_tm + ((size_t)blockIdx.x * (size_t)(p.K / kTcBK) + (size_t)(k0 / kTcBK)) * (size_t)a_bytes : nullptr;
+    const uint64_t w_policy = l2_policy_evict_first();
+    if (warp == 0 && lane == 0) {
+        for (int i = 0; i < n_pre; ++i) {
+            mbar_expect_tx(&full[i], (uint32_t)(a_bytes + (p.has_lo ? 2 : 1) * b_bytes));
+            if (p.w_tm)
+                tma_load_1d_hint(tiles + (size_t)i * stage_bytes, w_tile0 + (size_t)i * a_bytes, (uint32_t)a_bytes, &full[i], w_policy);
+            else
+                tma_load_2d(tiles + (size_t)i * stage_bytes, &map_w, k0 + i * p.bk, row0, &full[i]);
+        }
+    }
     pdl_wait();  // X (and the residual in `out`) come from the previous kernel
 
     if (warp == 0) {
@@ -142,8 +161,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                 const int s = i % p.stages, use = i / p.stages;
                 if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
                 uint8_t *a_dst = tiles + (size_t)s * stage_bytes;
-                mbar_expect_tx(&full[s], (uint32_t)(a_bytes + (p.has_lo ? 2 : 1) * b_bytes));
-                tma_load_2d(a_dst, &map_w, k0 + i * p.bk, row0, &full[s]);
+                if (i >= n_pre) {
+                    mbar_expect_tx(&full[s], (uint32_t)(a_bytes + (p.has_lo ? 2 : 1) * b_bytes));
+                    if (p.w_tm)
+                        tma_load_1d_hint(a_dst, w_tile0 + (size_t)i * a_bytes, (uint32_t)a_bytes, &full[s], w_policy);
+                    else
+                        tma_load_2d(a_dst, &map_w, k0 + i * p.bk, row0, &full[s]);
+                }
                 if (p.cs == 1) {
                     tma_load_2d(a_dst + a_bytes, &map_x, k0 + i * p.bk, 0, &full[s]);
                     if (p.has_lo) tma_load_2d(a_dst + a_bytes + b_pad, &map_xl, k0 + i * p.bk, 0, &full[s]);
@@ -345,8 +369,9 @@ int tc_bk(int T, bool has_lo) {
 
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
                    int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu, const void *map_x_lo,
-                   int64_t swiglu_lo_off, int bk) {
+                   int64_t swiglu_lo_off, int bk, const void *w_tile_major) {
     B200_REQUIRE(bk == 64 || bk == 32, "gemm_tc: bk must be 64 or 32");
+    B200_REQUIRE(w_tile_major == nullptr || (bk == 64 && ((uintptr_t)w_tile_major % 16) == 0), "gemm_tc: tile-major weights need bk 64 and 16-byte alignment");
     B200_REQUIRE(T >= 1 && T <= 256 && N % kTcBM == 0 && K % kTcBK == 0, "gemm_tc: need 1 <= T <= 256, N %% 128 == 0, K %% 64 == 0 (T %d N %d K %d)", T, N, K);
     TcParams p{};
     p.out = out, p.out_stride = out_stride, p.T = T, p.N = N, p.K = K;
@@ -375,6 +400,9 @@ int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out
     // per launch: the attribute belongs to the (function, device) pair, and callers may use several devices and threads
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     p.cs = tc_cluster_size(N, T);
+    static const int w_early = getenv("B200LLM_TC_W_EARLY") ? atoi(getenv("B200LLM_TC_W_EARLY")) : 1;
+    p.w_early = w_early;
+    p.w_tm = reinterpret_cast<const uint8_t *>(w_tile_major);
     LaunchCfg lc(dim3(tiles, ks), dim3(kTcThreads), smem, stream, pdl);
     cudaLaunchAttribute attrs[2];
     int n_attr = 0;

@@ -66,7 +66,8 @@ int tc_cluster_size(int N, int T);   // CTAs per cluster tc_gemm_launch will use
 int tc_x_box(int N, int T);          // rows of the activation maps' box for that launch: ceil16(T) / cluster size
 int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out_stride, int T, int N, int K,
                    int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu = nullptr,
-                   const void *map_x_lo = nullptr, int64_t swiglu_lo_off = 0, int bk = 64);
+                   const void *map_x_lo = nullptr, int64_t swiglu_lo_off = 0, int bk = 64,
+                   const void *w_tile_major = nullptr);   // tile-major copy of W (tcd.h): weight tiles as 16 KB bulk copies; map_w unused
 // tp_ar.cu: one-shot all-reduce + residual add over NVLink peer memory (h += sum over ranks of delta)
 constexpr int kTpMaxRanks = 8;
 int tp_allreduce_add_launch(float *h, const float *delta, int n, float *const *inbox, unsigned *const *flags,

@@ -256,7 +256,8 @@ def config5(n_gpus: int, in_flight_per_model: int, new_tokens: int, pool_gib: fl
 def cpu_row(model: str):
     import bench
     v, dt, cores = bench.cpu_decode_tok_s(model, 64, 12, 1)
-    return {"tok_s": v, "cores": cores, "sample": "12 decode steps at bs1 after a 64-id prompt, oracle port, torch CPU bf16"}
+    return {"tok_s": v, "cores": cores, "sample": "12 decode steps at bs1 after a 64-id prompt, oracle port, torch CPU bf16",
+            "quantised": bench.cpu_quantised_tok_s(model)}
 
 
 def main():
@@ -356,6 +357,10 @@ def main():
                 print(f"  text metrics: {t['error']}")
             if "cpu" in e:
                 print(f"  CPU ({e['cpu']['cores']} cores, oracle port): {e['cpu']['tok_s']:.2f} tok/s")
+                q = e["cpu"].get("quantised")
+                if q and "value" in q:
+                    print(f"  CPU ({q['cores']} threads, {q['format']} restatement of llama.cpp math, {q['simd']}): {q['value']:.2f} tok/s "
+                          f"({q['weight_gb_per_step']:.2f} GB of quantised weights per step)")
             print(f"  p50 TTFT ({args.prompt_len} ids): {e['gpu']['ttft_ms_p50']:.2f} ms")
             for r in e["gpu"]["decode"]:
                 print(f"  bs {r['bs']:3d}: {r['tok_s_total']:10.1f} tok/s  {r['ms_per_step']:.3f} ms/step  "

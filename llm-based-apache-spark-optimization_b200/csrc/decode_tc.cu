@@ -34,6 +34,13 @@
 #include "kernels.h"
 #include "tcd.h"
 
+// The file is compiled eight times (Makefile): part 0 holds the host-side planning functions and the dispatcher, parts
+// 1..7 each instantiate the kernel for one (head_dim, q heads per kv head) pair -- the instantiations take minutes
+// each, in parallel they take as long as one.
+#ifndef B200_TCD_PART
+#define B200_TCD_PART 0
+#endif
+
 namespace b200 {
 
 constexpr int kTC = 384;              // compute threads
@@ -90,7 +97,7 @@ __host__ __device__ __forceinline__ size_t tcd_qst_bytes(int hd, int gq) { retur
 // Layout: everything the compute warps address sits at COMPILE-TIME offsets from the base (merge buffer,
 // barriers, scratch, page table, phase descriptors), so those pointers cost no registers; the operand blocks
 // and the ring (1024-byte aligned, sizes known at launch) follow.
-__device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int n_jobs, int n_bslots) {
+__device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int n_jobs, int n_bslots, int lb) {   // lb: lanes the kernel instance can hold (1 or kTcdMaxLanes)
     TcdSmem s;
     s.mrg = reinterpret_cast<float *>(base);
     s.qst = reinterpret_cast<float *>(base + ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15));
@@ -103,22 +110,22 @@ __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int 
     s.xrdy = s.tempty + kTSlots;
     s.tmem_slot = reinterpret_cast<uint32_t *>(s.xrdy + 2);
     s.red = reinterpret_cast<float *>(s.tmem_slot + 4);
-    s.misc = reinterpret_cast<int *>(s.red + 64);
+    s.misc = reinterpret_cast<int *>(s.red + 128);
     s.rope = reinterpret_cast<float *>(s.misc + 64);
-    s.ptab = reinterpret_cast<int32_t *>(s.rope + 128);
-    s.jobs = reinterpret_cast<TcdJob *>(s.ptab + kTMaxPtab);
+    s.ptab = reinterpret_cast<int32_t *>(s.rope + 128 * lb);           // per lane: [head_dim/2][cos, sin]
+    s.jobs = reinterpret_cast<TcdJob *>(s.ptab + kTMaxPtab * lb);      // per lane: the first kTMaxPtab page-table entries
     const size_t head = (size_t)(reinterpret_cast<uint8_t *>(s.jobs) - base) + (size_t)n_jobs * sizeof(TcdJob);
     s.bop = base + ((head + 1023) & ~(size_t)1023);
     s.ring = s.bop + (size_t)n_bslots * 1024;
     return s;
 }
 
-static size_t tcd_fixed_smem_bytes(int hd, int gq, int n_jobs) {  // everything but the ring and the operand blocks
-    return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + tcd_qst_bytes(hd, gq) + (2 * kTMaxStages + 2 * kTAcc + kTSlots + 2) * 8 + 16 + 64 * 4 + 64 * 4 + 128 * 4 +
-           kTMaxPtab * 4 + (size_t)n_jobs * sizeof(TcdJob) + 2 * 1024;  // slack: 1024-byte alignment of the base and of the operand blocks
+static size_t tcd_fixed_smem_bytes(int hd, int gq, int n_jobs, int lb = 1) {  // everything but the ring and the operand blocks
+    return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + tcd_qst_bytes(hd, gq) + (2 * kTMaxStages + 2 * kTAcc + kTSlots + 2) * 8 + 16 + 128 * 4 + 64 * 4 + 128 * 4 * lb +
+           kTMaxPtab * 4 * lb + (size_t)n_jobs * sizeof(TcdJob) + 2 * 1024;  // slack: 1024-byte alignment of the base and of the operand blocks
 }
-static size_t tcd_smem_bytes(int hd, int gq, int n_jobs, int n_stages, int n_bslots) {
-    return (size_t)n_stages * kTStageBytes + (size_t)n_bslots * 1024 + tcd_fixed_smem_bytes(hd, gq, n_jobs);
+static size_t tcd_smem_bytes(int hd, int gq, int n_jobs, int n_stages, int n_bslots, int lb = 1) {
+    return (size_t)n_stages * kTStageBytes + (size_t)n_bslots * 1024 + tcd_fixed_smem_bytes(hd, gq, n_jobs, lb);
 }
 constexpr size_t kTSmemLimit = 232448;  // 227 KB per CTA on sm_100
 
@@ -138,6 +145,7 @@ __host__ __device__ __forceinline__ TRange tcd_range(int N, int K, bool whole_ti
     return r;
 }
 
+#if B200_TCD_PART == 0
 // operand blocks the CTA with the largest share needs for one matrix (0: the shape cannot be tiled)
 int tcd_job_slots(int N, int K, bool whole_tiles) {
     if (N % 128 != 0 || K % 64 != 0 || N < 128 || K < 64) return 0;
@@ -157,7 +165,7 @@ int tcd_stages_for(int head_dim, int gq, int n_jobs, int n_bslots) {
 
 // ring stages and operand blocks of a model: the operand buffer is sized for the neediest matrix,
 // the ring takes what is left of the 227 KB (false: not even 4 stages fit)
-bool tcd_plan(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers, int *n_stages, int *n_bslots) {
+bool tcd_plan(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers, int *n_stages, int *n_bslots, int lanes) {
     const int qd = n_q * head_dim, qkv = (n_q + 2 * n_kv) * head_dim;
     const int shapes[5][2] = {{qkv, d}, {d, qd}, {2 * ffn, d}, {d, ffn}, {vocab, d}};
     int slots = 0;
@@ -166,7 +174,7 @@ bool tcd_plan(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_
         if (need < 1 || need > kTBSlots) return false;
         slots = need > slots ? need : slots;
     }
-    const size_t fixed = tcd_fixed_smem_bytes(head_dim, n_kv > 0 ? n_q / n_kv : 1, 4 * n_layers + 1) + (size_t)slots * 1024;
+    const size_t fixed = tcd_fixed_smem_bytes(head_dim, n_kv > 0 ? n_q / n_kv : 1, 4 * n_layers + 1, lanes > 1 ? kTcdMaxLanes : 1) + (size_t)slots * 1024;
     if (fixed + 4 * (size_t)kTStageBytes > kTSmemLimit) return false;
     int st = (int)((kTSmemLimit - fixed) / kTStageBytes);
     *n_stages = (st > kTMaxStages ? kTMaxStages : st) & ~(kTIssuers - 1);
@@ -179,7 +187,7 @@ bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, i
     if (!(head_dim == 64 || head_dim == 128) || G < 1 || G > 4 || (G == 3 && head_dim == 64)) return false;
     if (4 * n_layers + 1 > kTMaxJobs) return false;
     int st, sl;
-    return tcd_plan(d, ffn, n_q, n_kv, head_dim, vocab, n_layers, &st, &sl);
+    return tcd_plan(d, ffn, n_q, n_kv, head_dim, vocab, n_layers, &st, &sl, 1);
 }
 
 // The in-kernel sampler keeps kTSampPerThread logit rows per compute thread and its scratch in the attention
@@ -191,6 +199,8 @@ bool tcd_sampler_supported(int vocab_rows, int head_dim, int gq, float temperatu
     if (tcd_mrg_bytes(head_dim, gq) < 64 * 4 + 2 * kTW * 8 + kTcdSampK * 8 + kTcdSampK * 4) return false;
     return temperature <= 0.f || (top_k >= 1 && top_k <= kTcdSampK);
 }
+
+#endif  // part 0
 
 __device__ __forceinline__ bool tcd_whole(const TcdParams &p, int j, int n_jobs) {
     return j == n_jobs - 1 && !p.split_all;
@@ -231,7 +241,7 @@ __device__ __forceinline__ void tcd_grid_sync(unsigned *ctr, unsigned target, in
 }
 
 // ---------------------------------------------------------------- producer: the weight stream
-__device__ void tcd_producer(const TcdParams &p, const TcdSmem &s, int G, int bid) {
+static __device__ void tcd_producer(const TcdParams &p, const TcdSmem &s, int G, int bid) {
     const uint64_t pol = l2_policy_evict_first();
     const int n_jobs = 4 * p.n_layers + 1;
     // ring position: slot and the parity of its current use (no modulo of a run-time ring size in the loop)
@@ -399,7 +409,7 @@ __device__ __forceinline__ bool tcd_try_move(const TcdParams &p, const TcdSmem &
 #define TCD_IACC(i_, v_) do { } while (0)
 #endif
 
-__device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem_in, int me) {
+static __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bid, int lane, uint32_t tmem_in, int me) {
     (void)lane;
 #ifdef B200LLM_TCD_TRACE
     bool tr_on = false;
@@ -526,13 +536,32 @@ __device__ void tcd_mma_warp(const TcdParams &p, const TcdSmem &s, int G, int bi
 // Kept small: what lives across the whole step competes with the attention phase for the 128 registers, and a
 // spilled value is reloaded behind a grid barrier at L2 latency.  (The tensor-parallel sequence numbers live in
 // shared memory: s.misc[62] reductions, s.misc[63] token exchanges.)
-struct TcdCtx {
-    int tok, pos;
+// NB = lanes the kernel instance decodes together (1, or kTcdMaxLanes for 2..4).  With one lane the token and position
+// live in registers; with several they live in shared memory (misc[16 + b], misc[20 + b]): tcd_pos / tcd_tok.
+template <int NB>
+struct TcdCtxT {
+    int tok, pos;         // (NB == 1)
     int ti;               // trace cursor (-1: tracing off for this step)
     uint32_t as;          // accumulator counter, in lock-step with the MMA issuer
-    float best;           // lm_head: running (max, argmax) of this thread
-    int best_i;
+    float best[NB];       // lm_head: running (max, argmax) of this thread, per lane
+    int best_i[NB];
 };
+template <int NB>
+__device__ __forceinline__ int tcd_pos(const TcdCtxT<NB> &c, const TcdSmem &s, int b) {
+    if constexpr (NB == 1) return c.pos;
+    else return reinterpret_cast<volatile int *>(s.misc)[16 + b];
+}
+template <int NB>
+__device__ __forceinline__ int tcd_tok(const TcdCtxT<NB> &c, const TcdSmem &s, int b) {
+    if constexpr (NB == 1) return c.tok;
+    else return reinterpret_cast<volatile int *>(s.misc)[20 + b];
+}
+// lane b's first page-table entries (shared memory) and its whole table (global)
+template <int NB>
+__device__ __forceinline__ int tcd_page(const TcdParams &p, const TcdSmem &s, int b, int pg) {
+    if constexpr (NB == 1) return pg < kTMaxPtab ? s.ptab[pg] : p.page_table[pg];
+    else return pg < kTMaxPtab ? s.ptab[b * kTMaxPtab + pg] : p.page_tables[b][pg];
+}
 
 // (debug) tagged globaltimer stamps of thread 0: tag in bits 48.., nanoseconds below
 enum { TT_STEP = 1, TT_XCONV = 2, TT_XREADY = 3, TT_EPI = 4, TT_BAR = 5, TT_ATT_Q = 6, TT_ATT_KV = 7, TT_ATT_WARPS = 8,

@@ -74,16 +74,19 @@ __device__ __forceinline__ unsigned long long tcd_block_max64(const TcdSampScrat
 }
 
 // Steps 2 and 3: repeat penalty on the rows this CTA owns, then its k best rows -> p.cand[bid][0..k).
-__device__ void tcd_sample_local(const TcdParams &p, const TcdJob &job, const TcdSmem &s, int k, int G, int bid, int tid) {
+// (b: the lane of a multi-lane launch; its logits, candidate lists and sampler settings are lane b's)
+static __device__ void tcd_sample_local(const TcdParams &p, const TcdJob &job, const TcdSmem &s, int k, int G, int bid, int tid, int b) {
     const int warp = tid >> 5, lane = tid & 31;
     const TcdSampScratch t = tcd_samp_scratch(s);
+    float *logits = p.logits + (size_t)b * p.vocab;
+    const float repeat_penalty = p.repeat_penalty_l[b];
     const TRange r = tcd_range(job.N, job.K, true, G, bid);
     const int row0 = (r.g0 / r.nkb) * 128;
     const int row1 = min((r.g1 / r.nkb) * 128, p.vocab);
     const int id0 = p.tp_rank * p.vocab;     // global id of this rank's row 0 (vocab-parallel lm_head)
     bar_sync(1, kTC);                        // the epilogue warps have stored this CTA's logit rows
-    if (p.repeat_penalty != 1.f) {
-        if (tid < 64) t.hist[tid] = __ldcg(p.lane_hist + (size_t)p.lane * 64 + tid);
+    if (repeat_penalty != 1.f) {
+        if (tid < 64) t.hist[tid] = __ldcg(p.lane_hist + (size_t)p.lanes[b] * 64 + tid);
         bar_sync(1, kTC);
         if (tid < 64) {   // each distinct recent token once: logit > 0 ? logit / penalty : logit * penalty
             const int tk = t.hist[tid];
@@ -91,8 +94,8 @@ __device__ void tcd_sample_local(const TcdParams &p, const TcdJob &job, const Tc
             bool skip = tk < 0 || tk >= p.vocab_global || row < row0 || row >= row1;
             for (int j = 0; j < tid && !skip; ++j) skip = t.hist[j] == tk;
             if (!skip) {
-                const float v = __ldcg(p.logits + row);
-                p.logits[row] = v > 0.f ? v / p.repeat_penalty : v * p.repeat_penalty;
+                const float v = __ldcg(logits + row);
+                logits[row] = v > 0.f ? v / repeat_penalty : v * repeat_penalty;
             }
         }
         bar_sync(1, kTC);
@@ -101,9 +104,9 @@ __device__ void tcd_sample_local(const TcdParams &p, const TcdJob &job, const Tc
 #pragma unroll
     for (int m = 0; m < kTSampPerThread; ++m) {
         const int n = row0 + tid + m * kTC;
-        key[m] = n < row1 ? tcd_cand_key(__ldcg(p.logits + n), id0 + n) : 0ull;
+        key[m] = n < row1 ? tcd_cand_key(__ldcg(logits + n), id0 + n) : 0ull;
     }
-    unsigned long long *out = p.cand + (size_t)bid * kTSampK;
+    unsigned long long *out = p.cand + ((size_t)b * G + bid) * kTSampK;
     for (int round = 0; round < k; ++round) {
         unsigned long long mx = key[0];
 #pragma unroll
@@ -116,10 +119,11 @@ __device__ void tcd_sample_local(const TcdParams &p, const TcdJob &job, const Tc
 }
 
 // Step 4, after the grid barrier: merge the G lists, then the serial tail.  Returns the token (the same in every CTA).
-__device__ int tcd_sample_merge(const TcdParams &p, const TcdSmem &s, const TcdCtx &c, int k, int G, int tid) {
+static __device__ int tcd_sample_merge(const TcdParams &p, const TcdSmem &s, int pos, int k, int G, int tid, int b) {
     const int warp = tid >> 5, lane = tid & 31;
     const TcdSampScratch t = tcd_samp_scratch(s);
-    const unsigned long long *list = p.cand + (size_t)tid * kTSampK;
+    const unsigned long long *list = p.cand + ((size_t)b * G + tid) * kTSampK;
+    const float temperature = p.temperature_l[b], top_p = p.top_p_l[b];
     unsigned long long h0 = 0, h1 = 0, h2 = 0, h3 = 0;
     int nxt = 0, used = 0;
     auto refill = [&]() {   // the next four entries of this thread's list (entries past k are stale)
@@ -143,19 +147,19 @@ __device__ int tcd_sample_merge(const TcdParams &p, const TcdSmem &s, const TcdC
     for (int i = 0; i < k; ++i) kk += t.top[i] != 0ull ? 1 : 0;
     const float v0 = tcd_unfkey((uint32_t)(t.top[0] >> 32));
     int tok = (int)(0x7fffffffu - (uint32_t)t.top[0]);
-    if (p.temperature > 0.f) {
-        const float inv_t = 1.f / p.temperature;
+    if (temperature > 0.f) {
+        const float inv_t = 1.f / temperature;
         if (tid < kk) t.ev[tid] = expf((tcd_unfkey((uint32_t)(t.top[tid] >> 32)) - v0) * inv_t);
         bar_sync(1, kTC);
         if (tid == 0) {   // sequential fp32 sums, the order of sample_kernel / oracle/sampler.py
             float total = 0.f;
             for (int i = 0; i < kk; ++i) total += t.ev[i];
             int keep = kk;
-            if (p.top_p < 1.f) {
+            if (top_p < 1.f) {
                 float cum = 0.f;
                 for (int i = 0; i < kk; ++i) {
                     cum += t.ev[i];
-                    if (cum / total >= p.top_p) {
+                    if (cum / total >= top_p) {
                         keep = i + 1;
                         break;
                     }
@@ -163,7 +167,7 @@ __device__ int tcd_sample_merge(const TcdParams &p, const TcdSmem &s, const TcdC
             }
             float mass = 0.f;
             for (int i = 0; i < keep; ++i) mass += t.ev[i];
-            const uint64_t z = tcd_mix64(p.seed + ((uint64_t)c.pos + 1ULL) * 0x9E3779B97F4A7C15ULL);
+            const uint64_t z = tcd_mix64(p.seed_l[b] + ((uint64_t)pos + 1ULL) * 0x9E3779B97F4A7C15ULL);
             const float u = (float)(z >> 40) * (1.f / 16777216.f);
             const float rr = u * mass;
             float cum = 0.f;

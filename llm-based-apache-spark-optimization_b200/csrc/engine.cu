@@ -129,7 +129,7 @@ struct b200llm_engine {
     unsigned long long *trace = nullptr;
     unsigned long long *samp_cand = nullptr;
     float2 *tcd_gu2 = nullptr, *tcd_att2 = nullptr, *tcd_qkv2 = nullptr;
-    size_t tcd_att2_bytes = 0;
+    size_t tcd_att2_bytes = 0, tcd_att2_lane_bytes = 0;
     // batch / prefill path
     uint16_t *xb = nullptr, *xb2 = nullptr;
     int64_t xb_lo = 0, xb2_lo = 0;   // element offsets of the lo parts inside xb / xb2 (0: single-bf16 activations)
@@ -192,7 +192,7 @@ struct WsLayout {
     size_t h, q, att, act, delta, logits, part_max, part_idx, row_lane, row_pos, row_token, pf_lane, pf_pos,
         pf_token, lane_token, lane_pos, lane_hist, page_table, gen_out, step_ctr, lane_samp, gath_max, gath_idx,
         attn_scratch, mega_jobs, bar_ctr, trace, samp_cand, tcd_gu2, tcd_att2, tcd_qkv2, xb, xb2, qkv_out, gu_out, total;
-    size_t attn_scratch_bytes, tcd_att2_bytes;
+    size_t attn_scratch_bytes, tcd_att2_bytes, tcd_att2_lane_bytes;
     size_t xb_lo_off, xb2_lo_off;
     int lm_grid, attn_splits;
 };
@@ -229,8 +229,9 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->act = take(R * ffn_l * 4);
     w->delta = take(R * c->d * 4);
     w->logits = take(R * vocab_l * 4);
-    w->part_max = take(R * w->lm_grid * 4);
-    w->part_idx = take(R * w->lm_grid * 4);
+    const size_t part_n = R * w->lm_grid > (size_t)kTcdMaxLanes * kNumSMs ? R * w->lm_grid : (size_t)kTcdMaxLanes * kNumSMs;
+    w->part_max = take(part_n * 4);   // (the persistent kernel keeps [lanes][148] partials here)
+    w->part_idx = take(part_n * 4);
     w->row_lane = take(R * 4);
     w->row_pos = take(R * 4);
     w->row_token = take(R * 4);
@@ -250,12 +251,15 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * (sizeof(MegaJob) > sizeof(TcdJob) ? sizeof(MegaJob) : sizeof(TcdJob)));
     w->bar_ctr = take(256);
     w->trace = take(4096 * 8);
-    w->samp_cand = take((size_t)kNumSMs * kTcdSampK * 8);   // per-CTA candidate keys of the in-kernel sampler
-    w->tcd_gu2 = take((size_t)2 * ffn_l * 8);                  // (sum, count) pairs of the persistent kernel's gate/up phase
-    w->tcd_qkv2 = take((size_t)(nq_l + 2 * nkv_l) * c->head_dim * 8);   // ... and of its qkv phase
+    // the persistent kernel decodes up to kTcdMaxLanes lanes per launch: one block of each of these per lane
+    const size_t TL = R < (size_t)kTcdMaxLanes ? R : (size_t)kTcdMaxLanes;
+    w->samp_cand = take(TL * kNumSMs * kTcdSampK * 8);        // per-CTA candidate keys of the in-kernel sampler
+    w->tcd_gu2 = take(TL * 2 * ffn_l * 8);                    // (sum, count) pairs of the persistent kernel's gate/up phase
+    w->tcd_qkv2 = take(TL * (nq_l + 2 * nkv_l) * c->head_dim * 8);   // ... and of its qkv phase
     {   // (value, tag) pairs of its attention phase: outputs, split-T partials, their (max, sum, tag, -)
         const size_t ns = (size_t)(kNumSMs / (nkv_l > 0 ? nkv_l : 1) < 1 ? 1 : kNumSMs / (nkv_l > 0 ? nkv_l : 1));
-        w->tcd_att2_bytes = nq_l * c->head_dim * 8 + nq_l * ns * c->head_dim * 8 + nq_l * ns * 16;
+        w->tcd_att2_lane_bytes = nq_l * c->head_dim * 8 + nq_l * ns * c->head_dim * 8 + nq_l * ns * 16;
+        w->tcd_att2_bytes = TL * w->tcd_att2_lane_bytes;
         w->tcd_att2 = take(w->tcd_att2_bytes);
     }
     {   // batch / prefill path (tcgen05 GEMM): bf16 activations and fp32 GEMM outputs
@@ -584,7 +588,7 @@ int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     e->samp_cand = (unsigned long long *)(b + w.samp_cand);
     e->tcd_gu2 = (float2 *)(b + w.tcd_gu2);
     e->tcd_qkv2 = (float2 *)(b + w.tcd_qkv2);
-    e->tcd_att2 = (float2 *)(b + w.tcd_att2), e->tcd_att2_bytes = w.tcd_att2_bytes;
+    e->tcd_att2 = (float2 *)(b + w.tcd_att2), e->tcd_att2_bytes = w.tcd_att2_bytes, e->tcd_att2_lane_bytes = w.tcd_att2_lane_bytes;
     const bool hilo = getenv("B200LLM_TC_BF16ACT") == nullptr;  // default: hi + lo operand pairs, ~fp32-accurate activations
     e->xb_lo = hilo ? (int64_t)w.xb_lo_off : 0, e->xb2_lo = hilo ? (int64_t)w.xb2_lo_off : 0;
     e->xb = (uint16_t *)(b + w.xb), e->xb2 = (uint16_t *)(b + w.xb2), e->qkv_out = (float *)(b + w.qkv_out), e->gu_out = (float *)(b + w.gu_out);
@@ -937,8 +941,13 @@ static int tcd_prepare(b200llm_engine *e) {
     return B200LLM_OK;
 }
 
-static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sampling &sp, bool in_kernel_sampler) {
+// One launch of the persistent kernel: n_steps decode steps of `nb` lanes (1..kTcdMaxLanes; several lanes only at tp_size 1).
+// in_kernel_sampler: the sampler chain runs as the kernel's last phase with every lane's own settings (a greedy lane is
+// temperature 0 there); otherwise all lanes are greedy.
+static int tcd_decode(b200llm_engine *e, const int32_t *lanes, int nb, int n_steps, bool in_kernel_sampler) {
     const b200llm_config &c = e->cfg;
+    const int lane = lanes[0];
+    const b200llm_sampling &sp = e->samp_host[lane];
     if (!e->tcd_ready || e->tcd_dataflow != tcd_dataflow_bits(e)) B200_TRY(tcd_prepare(e));
     TcdParams p{};
     p.dataflow = e->tcd_dataflow, p.gu2 = e->tcd_gu2, p.att2 = e->tcd_att2, p.qkv2 = e->tcd_qkv2;
@@ -960,13 +969,28 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
     p.page_table = e->page_table + (size_t)lane * c.max_pages_per_lane;
     p.n_ptab = c.max_pages_per_lane;
     p.gen_out = e->gen_out, p.n_steps = n_steps;
-    int ns = kNumSMs / e->nkv_l;
+    // attention items = lanes x kv heads x splits, at most one per CTA
+    int ns = kNumSMs / (e->nkv_l * nb);
     ns = ns < 1 ? 1 : (ns > e->attn_splits ? e->attn_splits : ns);
+    {   // (the att2 block of a lane is sized for the single-lane split count)
+        const int ns1 = kNumSMs / e->nkv_l < 1 ? 1 : kNumSMs / e->nkv_l;
+        ns = ns > ns1 ? ns1 : ns;
+    }
     p.n_splits = ns;
     uint8_t *sc = reinterpret_cast<uint8_t *>(e->attn_scratch);
     p.tickets = reinterpret_cast<unsigned *>(sc);
     p.part_o = reinterpret_cast<float *>(sc + kAttnTicketBytes);
     p.part_ml = p.part_o + (size_t)e->nq_l * ns * c.head_dim;
+    p.part_stride = e->nq_l * ns * (c.head_dim + 2);
+    p.att2_stride = (int32_t)(e->tcd_att2_lane_bytes / 8);
+    p.nb = nb;
+    for (int b = 0; b < nb; ++b) {
+        const b200llm_sampling &sb = e->samp_host[lanes[b]];
+        p.lanes[b] = lanes[b];
+        p.page_tables[b] = e->page_table + (size_t)lanes[b] * c.max_pages_per_lane;
+        p.temperature_l[b] = sb.temperature > 0.f ? sb.temperature : 0.f, p.top_k_l[b] = sb.top_k, p.top_p_l[b] = sb.top_p;
+        p.repeat_penalty_l[b] = sb.repeat_penalty, p.seed_l[b] = sb.seed;
+    }
     p.bar_ctr = e->bar_ctr;
     p.sample = 1;
     if (in_kernel_sampler) {   // penalty -> top-k -> top-p -> temperature -> draw as the kernel's last phase
@@ -974,7 +998,8 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
         p.temperature = sp.temperature, p.top_k = sp.top_k, p.top_p = sp.top_p, p.repeat_penalty = sp.repeat_penalty;
         p.seed = sp.seed;
     }
-    B200_REQUIRE(tcd_plan(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, (e->vocab_l + 127) / 128 * 128, c.n_layers, &p.n_stages, &p.n_bslots),
+    B200_REQUIRE(nb == 1 || (size_t)nb * p.part_stride * 4 + kAttnTicketBytes <= e->attn_scratch_bytes, "tcd: attention scratch too small for %d lanes", nb);
+    B200_REQUIRE(tcd_plan(c.d, e->ffn_l, e->nq_l, e->nkv_l, c.head_dim, (e->vocab_l + 127) / 128 * 128, c.n_layers, &p.n_stages, &p.n_bslots, nb),
                  "tcd: geometry does not fit");
     if (const char *ns = getenv("B200LLM_TCD_STAGES")) p.n_stages = (atoi(ns) < p.n_stages ? atoi(ns) : p.n_stages) & ~1;
     if (const char *nf = getenv("B200LLM_TCD_INFLIGHT")) p.n_inflight = atoi(nf);
@@ -986,12 +1011,12 @@ static int tcd_decode(b200llm_engine *e, int lane, int n_steps, const b200llm_sa
     if (const char *np = getenv("B200LLM_TCD_POLL")) p.n_poll = atoi(np) < 1 ? 1 : (atoi(np) > 12 ? 12 : atoi(np));
     if (getenv("B200LLM_MEGA_TRACE")) p.trace = e->trace, p.trace_step = n_steps > 1 ? 1 : 0;
     // the qkv and gate/up phases ADD into these rows; later layers find them cleared by the o_proj phase
-    B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim * 4, e->stream));
-    B200_CUDA_OK(cudaMemsetAsync(e->gu_out, 0, (size_t)2 * e->ffn_l * 4, e->stream));
-    if (p.dataflow & 1) B200_CUDA_OK(cudaMemsetAsync(e->tcd_gu2, 0, (size_t)2 * e->ffn_l * 8, e->stream));
-    if (p.dataflow & 2) B200_CUDA_OK(cudaMemsetAsync(e->tcd_att2, 0, e->tcd_att2_bytes, e->stream));
-    if (p.dataflow & 4) B200_CUDA_OK(cudaMemsetAsync(e->tcd_qkv2, 0, (size_t)(e->nq_l + 2 * e->nkv_l) * c.head_dim * 8, e->stream));   // no tag of an earlier launch survives
-    e->last_rows = 1, e->last_logit_rows = 1;
+    B200_CUDA_OK(cudaMemsetAsync(e->qkv_out, 0, (size_t)nb * (e->nq_l + 2 * e->nkv_l) * c.head_dim * 4, e->stream));
+    B200_CUDA_OK(cudaMemsetAsync(e->gu_out, 0, (size_t)nb * 2 * e->ffn_l * 4, e->stream));
+    if (p.dataflow & 1) B200_CUDA_OK(cudaMemsetAsync(e->tcd_gu2, 0, (size_t)nb * 2 * e->ffn_l * 8, e->stream));
+    if (p.dataflow & 2) B200_CUDA_OK(cudaMemsetAsync(e->tcd_att2, 0, (size_t)nb * e->tcd_att2_lane_bytes, e->stream));
+    if (p.dataflow & 4) B200_CUDA_OK(cudaMemsetAsync(e->tcd_qkv2, 0, (size_t)nb * (e->nq_l + 2 * e->nkv_l) * c.head_dim * 8, e->stream));   // no tag of an earlier launch survives
+    e->last_rows = nb, e->last_logit_rows = nb;
     return tcd_decode_launch(p, e->stream);
 }
 
@@ -1230,8 +1255,25 @@ int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int
     const bool in_kernel = !greedy && c.tp_size == 1 && getenv("B200LLM_NO_TCD_SAMPLER") == nullptr &&
                            tcd_sampler_supported((e->vocab_l + 127) / 128 * 128, c.head_dim, e->nq_l / e->nkv_l,
                                                  sp0.temperature, sp0.top_k);
-    if (c.use_megakernel && n_lanes == 1 && (greedy || in_kernel) && tcd_usable(e)) {
-        B200_TRY(tcd_decode(e, lanes[0], n_steps, sp0, in_kernel));
+    // 2..4 lanes ride the same kernel (the operand block has room for four lanes' hi / lo rows): every lane greedy, or
+    // every non-greedy lane within what the in-kernel sampler takes
+    static const int tcd_max_lanes = getenv("B200LLM_TCD_LANES") ? atoi(getenv("B200LLM_TCD_LANES")) : kTcdMaxLanes;
+    bool multi = n_lanes >= 2 && n_lanes <= kTcdMaxLanes && n_lanes <= tcd_max_lanes && c.tp_size == 1, multi_sampled = false;
+    for (int i = 0; multi && i < n_lanes; ++i) {
+        const b200llm_sampling &si = e->samp_host[lanes[i]];
+        const bool g = si.temperature <= 0.f && si.repeat_penalty == 1.f;
+        if (!g) {
+            multi_sampled = true;
+            multi = getenv("B200LLM_NO_TCD_SAMPLER") == nullptr && si.repeat_penalty > 0.f &&
+                    tcd_sampler_supported((e->vocab_l + 127) / 128 * 128, c.head_dim, e->nq_l / e->nkv_l, si.temperature, si.top_k);
+        }
+        for (int j = 0; j < i; ++j) multi = multi && lanes[j] != lanes[i];
+    }
+    if (c.use_megakernel && multi && tcd_usable(e)) {
+        B200_TRY(tcd_decode(e, lanes, n_lanes, n_steps, multi_sampled));
+        e->timing.kernel_launches = 1;
+    } else if (c.use_megakernel && n_lanes == 1 && (greedy || in_kernel) && tcd_usable(e)) {
+        B200_TRY(tcd_decode(e, lanes, 1, n_steps, in_kernel));
         e->timing.kernel_launches = 1;
     } else if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy &&
                mega_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim)) {
@@ -1391,6 +1433,7 @@ int b200llm_op_gemv_tm(const void *w_tm, const float *x, float *out, int32_t N, 
     p.gen_out = reinterpret_cast<int32_t *>(scr + 3712), p.n_steps = 1, p.n_splits = 1;
     p.bar_ctr = reinterpret_cast<unsigned *>(scr + 3776);
     p.sample = 0, p.split_all = k_split ? 1 : 0;
+    p.nb = 1, p.lanes[0] = 0, p.page_tables[0] = p.page_table, p.repeat_penalty_l[0] = 1.f;
     p.n_poll = 1, p.tmem_slots = 0;
     p.n_bslots = tcd_job_slots(N, K, !k_split);
     p.n_stages = tcd_stages_for(128, 1, 1, p.n_bslots);

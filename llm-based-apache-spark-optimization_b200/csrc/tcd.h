@@ -79,6 +79,18 @@ struct TcdParams {
     int32_t poll_ns;      // pause of the issuer between two probes while it waits for a phase's operand
     int32_t n_inflight;   // bulk copies a CTA keeps in flight (0: the whole ring)
     int32_t split_all;    // (test hook) k-split the last job too instead of giving whole tiles
+    // ---- several lanes in one launch (nb = 2..4, tp_size 1): the N = 8 operand block has room for four (hi, lo) row pairs, so
+    // the weights stream ONCE for up to four sequences.  Lane b's activations, sums, partials, logits and candidates live at
+    // base + b * (the buffer's size for one lane); `lane`, `page_table` and the sampler settings above describe lane 0 and the
+    // arrays below all lanes.  gen_out is [n_steps][nb].
+    int32_t nb;
+    int32_t lanes[4];
+    const int32_t *page_tables[4];
+    float temperature_l[4], top_p_l[4], repeat_penalty_l[4];
+    int32_t top_k_l[4];
+    uint64_t seed_l[4];
+    int32_t part_stride;   // floats from one lane's (part_o | part_ml) block to the next
+    int32_t att2_stride;   // float2 from one lane's att2 block to the next
     // ---- tensor parallel (tp_size > 1): row-parallel phases (bit 10 of x_src) add into `delta`, then an
     // all-reduce phase pushes delta to the peers' inboxes and adds all ranks' partials to h (see tp_ar.cu)
     int32_t tp_rank, tp_size;
@@ -96,13 +108,14 @@ struct TcdParams {
 
 int tcd_decode_launch(const TcdParams &p, cudaStream_t stream);
 bool tcd_supported(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers);
-bool tcd_plan(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers, int *n_stages, int *n_bslots);
+bool tcd_plan(int d, int ffn, int n_q, int n_kv, int head_dim, int vocab, int n_layers, int *n_stages, int *n_bslots, int lanes = 1);
 int tcd_job_slots(int N, int K, bool whole_tiles);
 int tcd_stages_for(int head_dim, int gq, int n_jobs, int n_bslots);
 // per-phase check that the activation operand of one CTA fits its 64 k-block buffer
 bool tcd_job_fits(int N, int K, bool whole_tiles);
 // can the in-kernel sampler (sample == 2) take these settings for a lm_head of `vocab_rows` (padded) rows?
 bool tcd_sampler_supported(int vocab_rows, int head_dim, int gq, float temperature, int top_k);
+constexpr int kTcdMaxLanes = 4; // lanes one launch of the persistent kernel can decode together
 constexpr int kTcdSampK = 64;   // largest top-k of the in-kernel sampler = candidate keys per CTA in TcdParams::cand
 
 }  // namespace b200

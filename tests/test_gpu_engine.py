@@ -607,3 +607,79 @@ def test_batch64_decode_of_the_1b_matches_golden(golden_dir):
     print(f"batch-64 decode of the 1B: {exact}/64 lanes identical over 16 steps (worst oracle margin {margins.min():.1e})")
     assert exact >= 60
     eng.close()
+
+
+@pytest.mark.parametrize("name,n_lanes", [("tiny", 2), ("tiny", 4), ("small", 3), ("small", 4)])
+def test_several_lanes_in_one_persistent_kernel_launch(name, n_lanes, golden_dir):
+    """2..4 lanes decoded by ONE launch of the tcgen05 persistent kernel (operand rows 2b / 2b + 1 = lane b): lanes at
+    different positions, 12 greedy steps, every lane's tokens equal to the oracle's and its last-step logits within the
+    tolerance of the single-lane path; then the same lanes continue one by one (single-lane launches) on the KV the
+    multi-lane launch appended."""
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    geo = lo.GEOMETRIES[name]
+    sd = lo.make_weights(geo, int(g["seed"]), sigma=float(g["sigma"]), embed_sigma=float(g["embed_sigma"]))
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    prompts = [wg.gen_tokens(9 + 14 * i, 900 + i, geo.vocab) for i in range(n_lanes)]       # 9, 23, 37, 51 ids: different pages
+    eng = _engine(name, sd, max_lanes=4, max_ctx=128, max_rows=8)
+    lanes = [eng.open_lane() for _ in prompts]
+    want, states = [], []
+    for p in prompts:
+        st = orc.new_state()
+        toks = [int(torch.argmax(orc.forward(torch.as_tensor(p, dtype=torch.int64), st)))]
+        lg = None
+        for _ in range(12):
+            lg = orc.forward(torch.tensor([toks[-1]]), st)
+            toks.append(int(torch.argmax(lg)))
+        want.append(toks)
+        states.append((st, lg))
+    first = []
+    for ln, p in zip(lanes, prompts):
+        eng.prefill(ln, p)
+        first.append(eng.read_lane(ln)[0])
+    got = eng.decode(lanes, 12)                                  # [12, n_lanes]
+    assert eng.timing().kernel_launches == 1, "the lanes did not ride one persistent-kernel launch"
+    for i in range(n_lanes):
+        assert [first[i]] + got[:, i].tolist() == want[i], f"lane {i}"
+        assert _rel(eng.logits(i), states[i][1].numpy()) <= TIGHT_TOL
+    # one lane at a time on what the joint launch left (positions, KV pages, token feedback)
+    for i in range(n_lanes):
+        st = states[i][0]
+        nxt = [int(torch.argmax(orc.forward(torch.tensor([want[i][-1]]), st)))]
+        for _ in range(3):
+            nxt.append(int(torch.argmax(orc.forward(torch.tensor([nxt[-1]]), st))))
+        assert eng.decode([lanes[i]], 4)[:, 0].tolist() == nxt, f"lane {i} alone after the joint launch"
+    eng.close()
+
+
+def test_several_lanes_with_their_own_sampling_settings():
+    """Lanes of one launch keep their own sampler settings (greedy, Ollama's defaults, a hot top-k 8) and seeds: the joint
+    launch draws what every lane draws when it is decoded alone from the same state."""
+    from b200llm import SamplingParams
+    geo = lo.GEOMETRIES["small"]
+    sd = lo.make_weights(geo, 0xB200, sigma=0.06)
+    settings = [SamplingParams(temperature=0.0), SamplingParams(temperature=0.8, top_k=40, top_p=0.9, repeat_penalty=1.1, seed=11),
+                SamplingParams(temperature=1.3, top_k=8, top_p=1.0, repeat_penalty=1.0, seed=5),
+                SamplingParams(temperature=0.0, repeat_penalty=1.3)]
+    prompts = [wg.gen_tokens(12 + 7 * i, 40 + i, geo.vocab) for i in range(4)]
+
+    def run(joint):
+        eng = _engine("small", sd, max_lanes=4, max_ctx=128, max_rows=8)
+        lanes = [eng.open_lane() for _ in prompts]
+        for ln, p, sp in zip(lanes, prompts, settings):
+            eng.set_sampling(ln, sp)
+            eng.prefill(ln, p)
+        if joint:
+            out = eng.decode(lanes, 10)
+            assert eng.timing().kernel_launches == 1
+            res = [out[:, i].tolist() for i in range(4)]
+        else:
+            res = []
+            for ln in lanes:
+                res.append(eng.decode([ln], 10)[:, 0].tolist())
+                assert eng.timing().kernel_launches == 1
+        eng.close()
+        return res
+    alone, joint = run(False), run(True)
+    assert joint[0] == alone[0] and joint[3] == alone[3]            # the greedy / penalised-argmax lanes
+    assert joint[1] == alone[1] and joint[2] == alone[2]            # the sampled lanes (same seeds, same positions)
+    assert len({tuple(t) for t in joint}) == 4

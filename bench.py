@@ -488,6 +488,33 @@ def run_b200(args):
                                   "repeat_penalty 1.1, random seed)",
                        "decode_tok_s": stats["sampled"]["eval_count"] / (stats["sampled"]["eval_ns"] * 1e-9), "what": what}
 
+    # four callers at once, as the reference's threaded Flask server produces them (app.run, Flask/app.py:239, on the error
+    # path :151-166): the scheduler batches their lanes and one persistent-kernel launch decodes all four
+    e2e_4 = None
+    if model_rt is not None and rank == 0 and world == 1:
+        import threading
+        texts4 = reference_style_prompts(8, PROMPT_LEN)
+        counts = [0] * 4
+
+        def caller(j, base):
+            r = ollama.generate(model=args.model, system=texts4[base + j][0], prompt=texts4[base + j][1], options=None)
+            counts[j] = r.eval_count
+
+        def round4(base):
+            ts = [threading.Thread(target=caller, args=(j, base)) for j in range(4)]
+            for t in ts:
+                t.start()
+            for t in ts:
+                t.join()
+            return sum(counts)
+        round4(0)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        n4 = round4(4)
+        dt4 = time.perf_counter() - t0
+        e2e_4 = {"value": n4 / dt4, "unit": UNIT, "callers": 4, "options": "none (Ollama's default sampling)",
+                 "what": "4 threads call ollama.generate at once with different error texts; generated tokens of all four / wall time"}
+
     tp_7b = None
     if world > 1 and not tp_mode and args.model == "llama3.2" and bs == 1 and not args.no_tp_leg:
         if model_rt is not None:
@@ -499,13 +526,15 @@ def run_b200(args):
         torch.cuda.empty_cache()
         tp_7b = bench_tp_7b(rank, world, local)
 
-    bs64 = None
+    bs64 = bs4 = None
     if rank == 0 and world == 1 and bs == 1 and args.model == "llama3.2" and not args.no_batch:
         if model_rt is not None:
             from b200llm import runtime
             runtime.unload_all()
             model_rt = None
         bs64 = bench_batch("llama3.2:1b", 64, max(8, min(args.steps, 64)), local)
+        # 4 concurrent callers of the headline model: one launch of the persistent kernel decodes all four lanes
+        bs4 = bench_batch("llama3.2", 4, max(8, min(args.steps, 64)), local)
 
     if rank == 0:
         mean_ctx = PROMPT_LEN + (args.steps - 1) / 2.0
@@ -547,8 +576,12 @@ def run_b200(args):
         }
         if e2e_sampled is not None:
             line["e2e_sampled"] = e2e_sampled
+        if e2e_4 is not None:
+            line["e2e_4callers"] = e2e_4
         if bs64 is not None:
             line["bs64"] = bs64
+        if bs4 is not None:
+            line["bs4"] = bs4
         if tp_7b is not None:
             line["tp_7b"] = tp_7b
         if not args.no_cpu_baseline and world == 1:

@@ -196,8 +196,12 @@ bool tcd_sampler_supported(int vocab_rows, int head_dim, int gq, float temperatu
     const int tiles = (vocab_rows + 127) / 128;
     const int rows_per_cta = (tiles + kNumSMs - 1) / kNumSMs * 128;
     if (rows_per_cta > 4 * kTC) return false;
-    if (tcd_mrg_bytes(head_dim, gq) < 64 * 4 + 2 * kTW * 8 + kTcdSampK * 8 + kTcdSampK * 4) return false;
-    return temperature <= 0.f || (top_k >= 1 && top_k <= kTcdSampK);
+    if (temperature > 0.f && (top_k < 1 || top_k > kTcdSampK)) return false;
+    // scratch in the attention merge buffer (s.mrg, s.qst): recent tokens, top-k keys and weights, one list of k keys per warp (decode_tc_sample.cuh)
+    const int k = temperature > 0.f ? top_k : 1;
+    // (the staging buffer of the attention items follows the merge buffer and is idle as well)
+    const size_t room = ((tcd_mrg_bytes(head_dim, gq) + 15) & ~(size_t)15) + tcd_qst_bytes(head_dim, gq);
+    return room >= 64 * 4 + (size_t)kTcdSampK * 8 + (size_t)kTcdSampK * 4 + (size_t)kTW * k * 8;
 }
 
 #endif  // part 0

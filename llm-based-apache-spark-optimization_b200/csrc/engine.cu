@@ -248,7 +248,8 @@ static void ws_layout(const b200llm_config *c, WsLayout *w) {
     w->gath_max = take(R * tp * w->lm_grid * 4);
     w->gath_idx = take(R * tp * w->lm_grid * 4);
     w->attn_scratch = take(w->attn_scratch_bytes);
-    w->mega_jobs = take((size_t)(4 * c->n_layers + 1) * (sizeof(MegaJob) > sizeof(TcdJob) ? sizeof(MegaJob) : sizeof(TcdJob)));
+    // (two sets of phase descriptors: the persistent kernel's second set is for 3-4 lanes, see tcd_prepare)
+    w->mega_jobs = take(2 * (size_t)(4 * c->n_layers + 1) * (sizeof(MegaJob) > sizeof(TcdJob) ? sizeof(MegaJob) : sizeof(TcdJob)));
     w->bar_ctr = take(256);
     w->trace = take(4096 * 8);
     // the persistent kernel decodes up to kTcdMaxLanes lanes per launch: one block of each of these per lane
@@ -911,29 +912,39 @@ static int tcd_dataflow_bits(const b200llm_engine *e) {
     return df ? atoi(df) : 7;
 }
 
+// data-flow bits of a launch with `nb` lanes: with 3-4 lanes the gate/up -> down edge goes back to a grid barrier -- the
+// (sum, count) pairs are twice the bytes of the sums, every CTA polls its slice of them for every lane, and at 3+
+// lanes that costs more than the barrier it saves (3B, 4 lanes: 1.716 against 1.757 ms per step)
+static int tcd_dataflow_for(const b200llm_engine *e, int nb) { return nb >= 3 ? (e->tcd_dataflow & ~1) : e->tcd_dataflow; }
+
 static int tcd_prepare(b200llm_engine *e) {
     const b200llm_config &c = e->cfg;
     e->tcd_dataflow = tcd_dataflow_bits(e);
-    std::vector<TcdJob> jobs(4 * c.n_layers + 1);
+    const size_t n_jobs = 4 * (size_t)c.n_layers + 1;
+    std::vector<TcdJob> jobs(2 * n_jobs);   // set 0: 1-2 lanes, set 1: 3-4 lanes
     const int nq = e->nq_l, nkv = e->nkv_l, ffn = e->ffn_l;   // this rank's share (= the model's at tp 1)
     const int qd = nq * c.head_dim;
     const bool tp = c.tp_size > 1;
     // tensor parallel: o_proj and down_proj are row-parallel, their partial sums go to `delta` (cleared by the
     // phase two before, bit 10) and an all-reduce phase adds every rank's delta to h
     float *row_out = tp ? e->delta : e->h;
-    for (int l = 0; l < c.n_layers; ++l) {
-        const LayerW &w = e->layers[l];
-        uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
-        jobs[4 * l + 0] = TcdJob{w.wqkv_tm, w.attn_norm, kl, kl + e->kv_half_stride,
-                                 (e->tcd_dataflow & 4) ? reinterpret_cast<float *>(e->tcd_qkv2) : e->qkv_out, (nq + 2 * nkv) * c.head_dim, c.d,
-                                 (e->tcd_dataflow & 4) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD, (l == 0 ? TCD_X_EMBED : TCD_X_H) | 0x400};
-        jobs[4 * l + 1] = TcdJob{w.wo_tm, nullptr, nullptr, nullptr, row_out, c.d, qd, TCD_EPI_ADD, TCD_X_ATT | 0x100};   // 0x100: clears the gate/up sums
-        jobs[4 * l + 2] = TcdJob{w.wgu_tm, w.mlp_norm, nullptr, nullptr, (e->tcd_dataflow & 1) ? reinterpret_cast<float *>(e->tcd_gu2) : e->gu_out,
-                                 2 * ffn, c.d, (e->tcd_dataflow & 1) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD, TCD_X_H | 0x400 | 0x200};   // 0x200: clears the qkv sums
-        jobs[4 * l + 3] = TcdJob{w.wdown_tm, nullptr, nullptr, nullptr, row_out, c.d, ffn, TCD_EPI_ADD, TCD_X_SWIGLU};
+    for (int set = 0; set < 2; ++set) {
+        const int df = tcd_dataflow_for(e, set == 0 ? 1 : 4);
+        TcdJob *jb = jobs.data() + set * n_jobs;
+        for (int l = 0; l < c.n_layers; ++l) {
+            const LayerW &w = e->layers[l];
+            uint8_t *kl = e->kv + (size_t)l * 2 * e->kv_half_stride;
+            jb[4 * l + 0] = TcdJob{w.wqkv_tm, w.attn_norm, kl, kl + e->kv_half_stride,
+                                   (df & 4) ? reinterpret_cast<float *>(e->tcd_qkv2) : e->qkv_out, (nq + 2 * nkv) * c.head_dim, c.d,
+                                   (df & 4) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD, (l == 0 ? TCD_X_EMBED : TCD_X_H) | 0x400};
+            jb[4 * l + 1] = TcdJob{w.wo_tm, nullptr, nullptr, nullptr, row_out, c.d, qd, TCD_EPI_ADD, TCD_X_ATT | 0x100};   // 0x100: clears the gate/up sums
+            jb[4 * l + 2] = TcdJob{w.wgu_tm, w.mlp_norm, nullptr, nullptr, (df & 1) ? reinterpret_cast<float *>(e->tcd_gu2) : e->gu_out,
+                                   2 * ffn, c.d, (df & 1) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD, TCD_X_H | 0x400 | 0x200};   // 0x200: clears the qkv sums
+            jb[4 * l + 3] = TcdJob{w.wdown_tm, nullptr, nullptr, nullptr, row_out, c.d, ffn, TCD_EPI_ADD, TCD_X_SWIGLU};
+        }
+        // the lm_head streams whole tiles: N counts the zero rows that pad the last one, p.vocab bounds what is stored
+        jb[4 * c.n_layers] = TcdJob{e->lm_head_tm, e->final_norm, nullptr, nullptr, e->logits, (e->vocab_l + 127) / 128 * 128, c.d, TCD_EPI_LOGITS, TCD_X_H};
     }
-    // the lm_head streams whole tiles: N counts the zero rows that pad the last one, p.vocab bounds what is stored
-    jobs[4 * c.n_layers] = TcdJob{e->lm_head_tm, e->final_norm, nullptr, nullptr, e->logits, (e->vocab_l + 127) / 128 * 128, c.d, TCD_EPI_LOGITS, TCD_X_H};
     B200_CUDA_OK(cudaMemcpyAsync(e->mega_jobs, jobs.data(), jobs.size() * sizeof(TcdJob), cudaMemcpyHostToDevice, e->stream));
     B200_CUDA_OK(cudaStreamSynchronize(e->stream));  // `jobs` is a pageable temporary
     e->tcd_ready = true;
@@ -950,8 +961,8 @@ static int tcd_decode(b200llm_engine *e, const int32_t *lanes, int nb, int n_ste
     const b200llm_sampling &sp = e->samp_host[lane];
     if (!e->tcd_ready || e->tcd_dataflow != tcd_dataflow_bits(e)) B200_TRY(tcd_prepare(e));
     TcdParams p{};
-    p.dataflow = e->tcd_dataflow, p.gu2 = e->tcd_gu2, p.att2 = e->tcd_att2, p.qkv2 = e->tcd_qkv2;
-    p.jobs = reinterpret_cast<const TcdJob *>(e->mega_jobs), p.n_layers = c.n_layers;
+    p.dataflow = tcd_dataflow_for(e, nb), p.gu2 = e->tcd_gu2, p.att2 = e->tcd_att2, p.qkv2 = e->tcd_qkv2;
+    p.jobs = reinterpret_cast<const TcdJob *>(e->mega_jobs) + (nb >= 3 ? 4 * (size_t)c.n_layers + 1 : 0), p.n_layers = c.n_layers;
     p.d = c.d, p.n_q = e->nq_l, p.n_kv = e->nkv_l, p.head_dim = c.head_dim, p.ffn = e->ffn_l, p.vocab = e->vocab_l;
     p.kv_page_heads = e->kv_page_heads;
     p.vocab_global = c.vocab, p.tp_rank = c.tp_rank, p.tp_size = c.tp_size;

@@ -351,6 +351,14 @@ int b200llm_op_sample(const b200llm_sample_args *a, void *stream);
 int b200llm_op_fill_weights(void *dev_bf16, uint64_t n, uint64_t seed, float sigma, float mean,
                             void *stream);
 
+/* A GGUF tensor as it lies in the file -> bf16, on the device (the checkpoints the reference's models ship as:
+ * `ollama.generate(model="duckdb-nsql" | "llama3.2")`, Flask/app.py:102-107,160-166, pulls Q4_0 / Q4_K_M blobs).
+ * `blocks`: DEVICE copy of the raw tensor bytes; ggml_type: 0 F32, 1 F16, 2 Q4_0, 8 Q8_0, 12 Q4_K, 14 Q6_K, 30 BF16;
+ * n_elements: whole blocks (32 for Q4_0 / Q8_0, 256 for Q4_K / Q6_K, even otherwise); out_bf16: DEVICE, n_elements
+ * bf16.  ggml's reference arithmetic in ggml's order, so the result is bit-equal to rounding the fp32 values
+ * gguf-py's de-quantiser produces. */
+int b200llm_op_dequant_bf16(const void *blocks, int32_t ggml_type, int64_t n_elements, void *out_bf16, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -119,6 +119,7 @@ SYMBOLS = {
                                      C.c_int32, C.c_void_p]),
     "b200llm_op_sample": (C.c_int, [_P(SampleArgs), C.c_void_p]),
     "b200llm_op_fill_weights": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_float, C.c_float, C.c_void_p]),
+    "b200llm_op_dequant_bf16": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
 }
 
 

@@ -233,15 +233,49 @@ def geometry_from_metadata(md: Dict[str, Any], tensors: Dict[str, TensorInfo], n
                     rms_eps=float(g("attention.layer_norm_rms_epsilon", 1e-5)))
 
 
+def dequantize_on_device(raw: np.ndarray, ggml_type: int, shape, device):
+    """bf16 tensor of `shape` on the CUDA `device`: the raw blocks are uploaded as they lie in the file and expanded by
+    the library's kernel (csrc/dequant.cu), bit-equal to rounding `dequantize` to bf16."""
+    import torch
+    from . import _lib
+    n = int(np.prod(shape))
+    import warnings
+    with warnings.catch_warnings():   # the blocks come straight out of the read-only file mapping and are only read
+        warnings.simplefilter("ignore", UserWarning)
+        blocks = torch.from_numpy(np.ascontiguousarray(np.asarray(raw, dtype=np.uint8))).to(device)
+    out = torch.empty(n, dtype=torch.bfloat16, device=device)
+    with torch.cuda.device(out.device):
+        _lib.check(_lib.lib.b200llm_op_dequant_bf16(blocks.data_ptr(), int(ggml_type), n, out.data_ptr(),
+                                                    torch.cuda.current_stream(out.device).cuda_stream))
+    return out.view(*shape)
+
+
+def unpermute_qk_t(w, n_head: int):
+    """unpermute_qk for a torch tensor (the device path of `load`)."""
+    out, cols = w.shape
+    return w.view(n_head, out // n_head // 2, 2, cols).transpose(1, 2).reshape(out, cols)
+
+
 def load(path: str, device, name: str = "") -> Tuple[Any, Dict[str, Any]]:
-    """(Geometry, {HF name: bf16 tensor on `device`}) of a Llama-family GGUF file."""
+    """(Geometry, {HF name: bf16 tensor on `device`}) of a Llama-family GGUF file.  On a CUDA device the tensors are
+    expanded there (B200LLM_GGUF_HOST_DEQUANT=1: in numpy on the host, the checker's path)."""
+    import os
     import torch
     gf = GGUFFile(path)
     geo = geometry_from_metadata(gf.metadata, gf.tensors, name or gf.metadata.get("general.name", "gguf-model"))
     sd: Dict[str, Any] = {}
+    on_device = torch.device(device).type == "cuda" and not os.environ.get("B200LLM_GGUF_HOST_DEQUANT")
     for tname, info in gf.tensors.items():
         hf = hf_name(tname)
         if hf is None:
+            continue
+        if on_device:
+            w = dequantize_on_device(gf.raw(tname), info.ggml_type, info.shape, device)
+            if tname.endswith("attn_q.weight"):
+                w = unpermute_qk_t(w, geo.n_q).contiguous()
+            elif tname.endswith("attn_k.weight"):
+                w = unpermute_qk_t(w, geo.n_kv).contiguous()
+            sd[hf] = w
             continue
         w = gf.dequantize(tname)
         if tname.endswith("attn_q.weight"):

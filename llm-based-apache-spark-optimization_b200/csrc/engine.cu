@@ -1511,4 +1511,10 @@ int b200llm_op_fill_weights(void *dev_bf16, uint64_t n, uint64_t seed, float sig
     return fill_weights_launch(dev_bf16, n, seed, sigma, mean, (cudaStream_t)stream);
 }
 
+int b200llm_op_dequant_bf16(const void *blocks, int32_t ggml_type, int64_t n_elements, void *out_bf16, void *stream) {
+    int rc = require_device_any();
+    if (rc) return rc;
+    return dequant_bf16_launch(blocks, ggml_type, n_elements, out_bf16, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -68,6 +68,8 @@ int tc_gemm_launch(const void *map_w, const void *map_x, float *out, int64_t out
                    int accumulate, cudaStream_t stream, bool pdl, void *out_swiglu = nullptr,
                    const void *map_x_lo = nullptr, int64_t swiglu_lo_off = 0, int bk = 64,
                    const void *w_tile_major = nullptr);   // tile-major copy of W (tcd.h): weight tiles as 16 KB bulk copies; map_w unused
+// dequant.cu: GGUF blocks (ggml type id) -> bf16, bit-equal to rounding ggml's reference de-quantiser
+int dequant_bf16_launch(const void *blocks, int ggml_type, int64_t n_elements, void *out_bf16, cudaStream_t stream);
 // tp_ar.cu: one-shot all-reduce + residual add over NVLink peer memory (h += sum over ranks of delta)
 constexpr int kTpMaxRanks = 8;
 int tp_allreduce_add_launch(float *h, const float *delta, int n, float *const *inbox, unsigned *const *flags,

@@ -215,3 +215,41 @@ def test_text_in_text_out_with_the_checkpoints_tokenizer_and_template(tmp_path):
     assert r.response == tk.decode(want[:cut], skip_special_tokens=True)
     assert r.done_reason == ("stop" if cut < len(want) else "length")
     assert list(r.context) == ids + want[:cut]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("qt,block_bytes,per,f16_at", [(QT.Q4_K, 144, 256, (0, 2)), (QT.Q6_K, 210, 256, (208,)), (QT.Q4_0, 18, 32, (0,)),
+                                                      (QT.Q8_0, 34, 32, (0,)), (QT.F16, 2, 1, ()), (QT.BF16, 2, 1, ()), (QT.F32, 4, 1, ())])
+def test_device_dequantiser_is_bit_equal_to_the_host_one(qt, block_bytes, per, f16_at):
+    """csrc/dequant.cu (what `load` uses on a CUDA device) against the numpy de-quantiser above, which the CPU tests pin to
+    ggml's reference: random bit patterns in every field, finite fp16 scales; the bf16 results must be the same bits."""
+    rng = np.random.default_rng(100 + int(qt))
+    nb = 4096 if per > 1 else 8192
+    raw = rng.integers(0, 256, (nb, block_bytes), dtype=np.uint8)
+    for off in f16_at:
+        raw[:, off:off + 2] = (rng.standard_normal(nb) * 0.01).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    if qt == QT.F16:
+        raw = (rng.standard_normal(nb) * 3).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    if qt == QT.F32:
+        raw = (rng.standard_normal(nb) * 3).astype(np.float32).view(np.uint8).reshape(nb, 4)
+    if qt == QT.BF16:
+        raw[:, 1] &= 0x7E          # keep the exponent away from inf / nan
+    want = torch.from_numpy(gguf_loader.dequantize(raw.reshape(-1), int(qt))).to(torch.bfloat16)
+    got = gguf_loader.dequantize_on_device(raw.reshape(-1), int(qt), (nb * per,), "cuda")
+    torch.cuda.synchronize()
+    assert got.dtype == torch.bfloat16 and got.shape == want.shape
+    assert torch.equal(got.cpu().view(torch.int16), want.view(torch.int16))
+
+
+@pytest.mark.gpu
+def test_quantised_file_expanded_on_the_device_equals_the_host_path(tmp_path, monkeypatch):
+    geo = geometry.resolve("small")
+    sd = _hf_state_dict(geo, 5)
+    path = str(tmp_path / "small-q4_0.gguf")
+    write_gguf(path, geo, sd, QT.Q4_0)
+    _, on_dev = gguf_loader.load(path, "cuda")
+    monkeypatch.setenv("B200LLM_GGUF_HOST_DEQUANT", "1")
+    _, on_host = gguf_loader.load(path, "cuda")
+    assert set(on_dev) == set(on_host)
+    for k in on_dev:                                  # q / k un-permutation included
+        assert torch.equal(on_dev[k].view(torch.int16), on_host[k].view(torch.int16)), k

@@ -355,9 +355,10 @@ int tcd_decode_launch(const TcdParams &p, cudaStream_t stream) {
     }
     B200_REQUIRE(4 * p.n_layers + 1 <= kTMaxJobs, "tcd: more than 32 layers");
     const int GQ = p.n_kv > 0 ? p.n_q / p.n_kv : 1;
+    static const bool force_multi = getenv("B200LLM_TCD_FORCE_MULTI") != nullptr;   // (measurement) one lane on the multi-lane instance
 #define B200_TCD_CASE(HD_, G_)                                                  \
     if (p.head_dim == HD_ && GQ == G_)                                          \
-        return p.nb == 1 ? tcd_launch_t<HD_, G_, 1>(p, stream) : tcd_launch_t<HD_, G_, kTcdMaxLanes>(p, stream);
+        return (p.nb == 1 && !force_multi) ? tcd_launch_t<HD_, G_, 1>(p, stream) : tcd_launch_t<HD_, G_, kTcdMaxLanes>(p, stream);
     B200_TCD_CASE(128, 1) B200_TCD_CASE(128, 2) B200_TCD_CASE(128, 3) B200_TCD_CASE(128, 4)
     B200_TCD_CASE(64, 1) B200_TCD_CASE(64, 2) B200_TCD_CASE(64, 4)
 #undef B200_TCD_CASE

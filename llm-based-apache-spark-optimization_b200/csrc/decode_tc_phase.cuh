@@ -265,7 +265,7 @@ __device__ TcdScale<NB> tcd_prologue(const TcdParams &p, const TcdJob &job, cons
             if (gain != nullptr) gn = *reinterpret_cast<const uint4 *>(gain + chunk * 8);
             float4 xa[NB], xb[NB];
 #pragma unroll
-            for (int b = 0; b < NB; ++b) {
+            for (int b = 0; b < NB; ++b) {   // (a lane that is not there re-reads lane 0: predicating the loads made ptxas spill 600 bytes)
                 const float *src = p.h + (size_t)(b < nb ? b : 0) * p.d + chunk * 8;
                 xa[b] = __ldcg(reinterpret_cast<const float4 *>(src)), xb[b] = __ldcg(reinterpret_cast<const float4 *>(src + 4));
             }

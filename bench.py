@@ -33,8 +33,8 @@ METRIC = "decode_tok_s_llama3.2-3b_bs1"
 UNIT = "tok/s"
 PROMPT_LEN = 296          # 20 system + 25 wrapper + ~250 Spark-error tokens
 E2E_NEW_TOKENS = 128
-NCU_DRAM_BYTES_PER_STEP = (19.335132e9 + 6.63936e6) / 3   # 3-step launch under ncu --set full
-NCU_SOURCE = "profiles/tcd_full_r2c_summary.txt: 19.34 GB for a 3-step launch"
+NCU_DRAM_BYTES_PER_STEP = (19.349388e9 + 7.412224e6) / 3   # 3-step launch under ncu --set full
+NCU_SOURCE = "profiles/tcd_full_r2e_summary.txt: 19.35 GB for a 3-step launch"
 
 
 def parse_args():

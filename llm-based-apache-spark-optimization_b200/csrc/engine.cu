@@ -475,12 +475,39 @@ int b200llm_destroy(b200llm_engine *e) {
     return B200LLM_OK;
 }
 
+#define B200_TRY(expr)        \
+    do {                      \
+        int _rc = (expr);     \
+        if (_rc) return _rc;  \
+    } while (0)
+
+// A bound buffer must be device memory of the engine's GPU (a tensor made on another GPU of the process would fault in the
+// first kernel that touches it, far from the cause)
+static int check_on_device(const b200llm_engine *e, const void *ptr, const char *what, int index) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) {
+        cudaGetLastError();
+        set_error("%s %d: not a CUDA pointer", what, index);
+        return B200LLM_EINVAL;
+    }
+    if (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged) {
+        set_error("%s %d: not device memory", what, index);
+        return B200LLM_EINVAL;
+    }
+    if (at.type == cudaMemoryTypeDevice && at.device != e->cfg.device) {
+        set_error("%s %d lives on GPU %d, the engine on GPU %d", what, index, at.device, e->cfg.device);
+        return B200LLM_EINVAL;
+    }
+    return B200LLM_OK;
+}
+
 int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, int32_t n) {
     B200_REQUIRE(e && descs && n > 0, "bind_weights: bad arguments");
     const b200llm_config &c = e->cfg;
     for (int i = 0; i < n; ++i) {
         const b200llm_tensor_desc &t = descs[i];
         B200_REQUIRE(t.dev != nullptr && ((uintptr_t)t.dev % 16) == 0, "tensor %d: NULL or unaligned device pointer", i);
+        B200_TRY(check_on_device(e, t.dev, "tensor", i));
         auto shape = [&](int64_t r, int64_t cc) {
             if (t.rows != r || t.cols != cc) {
                 set_error("tensor kind %d layer %d: shape [%lld, %lld], expected [%lld, %lld]", t.kind, t.layer,
@@ -526,6 +553,7 @@ int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, in
 
 int b200llm_bind_kv_pool(b200llm_engine *e, void *dev, size_t bytes) {
     B200_REQUIRE(e && dev && ((uintptr_t)dev % 256) == 0, "bind_kv_pool: NULL or unaligned pool");
+    B200_TRY(check_on_device(e, dev, "KV pool", 0));
     size_t pb;
     b200llm_kv_page_bytes(&e->cfg, &pb);
     e->n_pages = (int)(bytes / pb);
@@ -541,6 +569,7 @@ int b200llm_bind_kv_pool(b200llm_engine *e, void *dev, size_t bytes) {
 
 int b200llm_bind_kv_pool_shared(b200llm_engine *e, void *dev, size_t bytes, size_t slot_bytes) {
     B200_REQUIRE(e && dev && ((uintptr_t)dev % 256) == 0, "bind_kv_pool_shared: NULL or unaligned pool");
+    B200_TRY(check_on_device(e, dev, "KV pool", 0));
     size_t pb;
     b200llm_kv_page_bytes(&e->cfg, &pb);
     const size_t tile = (size_t)e->cfg.page_tokens * e->cfg.head_dim * 2;
@@ -559,6 +588,7 @@ int b200llm_bind_kv_pool_shared(b200llm_engine *e, void *dev, size_t bytes, size
 
 int b200llm_bind_workspace(b200llm_engine *e, void *dev, size_t bytes) {
     B200_REQUIRE(e && dev && ((uintptr_t)dev % 256) == 0, "bind_workspace: NULL or unaligned workspace");
+    B200_TRY(check_on_device(e, dev, "workspace", 0));
     WsLayout w;
     ws_layout(&e->cfg, &w);
     if (bytes < w.total) {
@@ -672,12 +702,6 @@ int b200llm_set_history(b200llm_engine *e, int32_t lane, const int32_t *ids, int
 }  // extern "C"
 
 // ---------------------------------------------------------------- one forward pass
-#define B200_TRY(expr)        \
-    do {                      \
-        int _rc = (expr);     \
-        if (_rc) return _rc;  \
-    } while (0)
-
 struct PassRows {
     int rows;
     int32_t *row_lane, *row_pos, *row_token;

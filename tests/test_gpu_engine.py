@@ -683,3 +683,18 @@ def test_several_lanes_with_their_own_sampling_settings():
     assert joint[0] == alone[0] and joint[3] == alone[3]            # the greedy / penalised-argmax lanes
     assert joint[1] == alone[1] and joint[2] == alone[2]            # the sampled lanes (same seeds, same positions)
     assert len({tuple(t) for t in joint}) == 4
+
+
+def test_binding_a_buffer_of_another_gpu_is_refused():
+    """Weights (or a pool, or a workspace) that live on another GPU of the process are refused at bind time with a message
+    that names both GPUs, instead of faulting in the first kernel that touches them."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from b200llm import Engine, _lib, geometry, weights
+    geo = geometry.resolve("tiny")
+    with torch.cuda.device(1):
+        w_other = weights.random_init(geo, 0xB200, 1, sigma=0.08)
+    with pytest.raises(_lib.B200LLMError) as ei:
+        Engine(geo, w_other, device=0, max_lanes=1, max_ctx=64, max_rows=8)
+    assert ei.value.code == _lib.EINVAL and "GPU 1" in str(ei.value) and "GPU 0" in str(ei.value)
+    torch.cuda.set_device(0)

@@ -54,6 +54,7 @@ def test_two_models_decode_out_of_one_pool():
     from b200llm.scheduler import Scheduler
     from oracle import llama_oracle as lo
     from oracle import weightgen as wg
+    torch.cuda.set_device(0)
     names = ["small", "tiny"]                       # different layer counts, head_dim and kv heads: different page sizes
     ogeo = {n: lo.GEOMETRIES[n] for n in names}
     sd = {n: lo.make_weights(ogeo[n], 0xB200 + i, sigma=0.07) for i, n in enumerate(names)}

@@ -102,3 +102,4 @@ def test_sixteen_mixed_requests_over_two_replicas_match_the_oracle(policy):
     router.shutdown()
     for e in engines:
         e.close()
+    torch.cuda.set_device(0)        # (later tests of the session allocate on the current device)

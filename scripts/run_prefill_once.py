@@ -8,7 +8,7 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "llm-based-apache-spark-optimization_b2
 from b200llm import Engine, geometry, weights
 geo = geometry.resolve(sys.argv[1] if len(sys.argv) > 1 else "llama3.2")
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 296
-eng = Engine(geo, weights.random_init(geo, 0xB200, 0), max_lanes=2, max_ctx=n + 64, max_rows=256, use_megakernel=False)
+eng = Engine(geo, weights.random_init(geo, 0xB200, 0), max_lanes=2, max_ctx=n + 64, max_rows=256, use_megakernel=bool(os.environ.get("B200LLM_PREFILL_TM")))   # B200LLM_PREFILL_TM=1: with the tile-major copies (gemm_tc then takes its weight tiles from them)
 ids = (np.arange(5, 5 + n, dtype=np.int32) * 7919) % min(geo.vocab, 128000)
 lane = eng.open_lane()
 eng.prefill(lane, ids)          # warm (tensor maps, attributes)

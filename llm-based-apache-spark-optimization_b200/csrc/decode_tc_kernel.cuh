@@ -155,12 +155,14 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 }
                 phase(4 * l + 1);  // o_proj + residual
                 arrive_stamp();
-                tcd_grid_arrive(p.bar_ctr, tid);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
-                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                if (!(p.tp_size > 1 && (p.dataflow & 8))) {   // (tensor parallel, data-flow mode: the slice owners poll the sums' counts)
+                    tcd_grid_arrive(p.bar_ctr, tid);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                    tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                }
                 if (p.tp_size > 1) {   // o_proj is row-parallel: h += sum over ranks of the partial sums
-                    tcd_allreduce_phase(p, s, G, bid, tid);
+                    tcd_allreduce_phase(p, s, G, bid, tid, s.jobs[4 * l + 1].N, s.jobs[4 * l + 1].K);
                     tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 }
                 phase(4 * l + 2);  // rmsnorm + gate/up (raw sums)
@@ -173,12 +175,14 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 }
                 phase(4 * l + 3);  // swiglu + down + residual
                 arrive_stamp();
-                tcd_grid_arrive(p.bar_ctr, tid);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
-                tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
-                tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                if (!(p.tp_size > 1 && (p.dataflow & 8))) {
+                    tcd_grid_arrive(p.bar_ctr, tid);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR_ARRIVED);
+                    tcd_grid_wait(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
+                    tcd_trace(p, c.ti, bid, tid, TT_BAR);
+                }
                 if (p.tp_size > 1) {   // down_proj is row-parallel too
-                    tcd_allreduce_phase(p, s, G, bid, tid);
+                    tcd_allreduce_phase(p, s, G, bid, tid, s.jobs[4 * l + 3].N, s.jobs[4 * l + 3].K);
                     tcd_grid_sync(p.bar_ctr, ++bar_no * G, tid, bar_done, p.n_poll);
                 }
             }

@@ -191,7 +191,8 @@ __device__ TcdScale<NB> tcd_prologue(const TcdParams &p, const TcdJob &job, cons
         }
     }
     if ((job.x_src & 0x400) && p.tp_size > 1) {  // tensor parallel: clear the partial-sum vector of the next row-parallel phase
-        for (int i = bid * kTC + tid; i < p.d / 4; i += G * kTC) reinterpret_cast<float4 *>(p.delta)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int nd4 = (p.dataflow & 8) ? p.d / 2 : p.d / 4;   // (sum, count) pairs when the reduction is triggered by the data
+        for (int i = bid * kTC + tid; i < nd4; i += G * kTC) reinterpret_cast<float4 *>(p.delta)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     // Clear the sum buffers the next qkv / gate-up phases add into, each while nobody can be reading it and a grid barrier
     // before it is added to again: gate/up's in the o_proj phase (bit 8; its readers were the previous layer's down_proj
@@ -403,7 +404,10 @@ __device__ __forceinline__ bool tcd_wait_flag(const unsigned *f, unsigned want, 
     return true;
 }
 
-static __device__ void tcd_allreduce_phase(const TcdParams &p, const TcdSmem &s, int G, int bid, int tid) {
+// With TcdParams::dataflow bit 3 there is no grid barrier in front of this phase: the row-parallel phase added (partial sum, 1)
+// pairs into `delta`, and the CTA that owns slice j polls the pairs of its rows until every count equals the number of CTAs
+// that contribute to the row's tile (`red_N`, `red_K`: the shape of the phase that produced the sums).
+static __device__ void tcd_allreduce_phase(const TcdParams &p, const TcdSmem &s, int G, int bid, int tid, int red_N, int red_K) {
     const unsigned sq = (unsigned)s.misc[62] + 1u;
     const int phase = (int)(sq & 1u);
     const int n_slices = (p.d + 1023) / 1024;
@@ -411,7 +415,20 @@ static __device__ void tcd_allreduce_phase(const TcdParams &p, const TcdSmem &s,
         const int i = j * 1024 + tid * 4;
         const bool live = tid < 256 && i < p.d;
         float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (live) mine = __ldcg(reinterpret_cast<const float4 *>(p.delta + i));
+        if (live && (p.dataflow & 8)) {
+            const float want = tcd_tile_contributors(red_N, red_K, i / 128, G);   // 4 consecutive rows lie in one tile
+            const float2 *dp = reinterpret_cast<const float2 *>(p.delta) + i;
+            float4 a, b;
+            for (;;) {
+                asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "l"(dp) : "memory");
+                asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(dp + 2) : "memory");
+                if (a.y == want && a.w == want && b.y == want && b.w == want) break;
+                __nanosleep(32);
+            }
+            mine = make_float4(a.x, a.z, b.x, b.z);
+        } else if (live) {
+            mine = __ldcg(reinterpret_cast<const float4 *>(p.delta + i));
+        }
         if (live)
             for (int r = 0; r < p.tp_size; ++r)
                 if (r != p.tp_rank)

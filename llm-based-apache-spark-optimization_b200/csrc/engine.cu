@@ -932,8 +932,12 @@ static bool tcd_usable(const b200llm_engine *e) {
 
 static int tcd_dataflow_bits(const b200llm_engine *e) {
     // (tensor parallel: the three edges below are local to a rank; the all-reduce phases keep their grid barriers)
+    // bit 3 (tensor parallel only): the row-parallel sums are (sum, count) pairs in `delta` and the all-reduce phase's slice
+    // owners poll them -- no grid barrier between o_proj / down_proj and their reduction (needs room for d pairs in `delta`)
     const char *df = getenv("B200LLM_TCD_DATAFLOW");
-    return df ? atoi(df) : 7;
+    int bits = df ? atoi(df) : 15;
+    if (e->cfg.tp_size == 1 || e->cfg.max_rows < 2) bits &= ~8;
+    return bits;
 }
 
 // data-flow bits of a launch with `nb` lanes: with 3-4 lanes the gate/up -> down edge goes back to a grid barrier -- the
@@ -952,6 +956,7 @@ static int tcd_prepare(b200llm_engine *e) {
     // tensor parallel: o_proj and down_proj are row-parallel, their partial sums go to `delta` (cleared by the
     // phase two before, bit 10) and an all-reduce phase adds every rank's delta to h
     float *row_out = tp ? e->delta : e->h;
+    const int row_epi = (tp && (e->tcd_dataflow & 8)) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD;
     for (int set = 0; set < 2; ++set) {
         const int df = tcd_dataflow_for(e, set == 0 ? 1 : 4);
         TcdJob *jb = jobs.data() + set * n_jobs;
@@ -961,10 +966,10 @@ static int tcd_prepare(b200llm_engine *e) {
             jb[4 * l + 0] = TcdJob{w.wqkv_tm, w.attn_norm, kl, kl + e->kv_half_stride,
                                    (df & 4) ? reinterpret_cast<float *>(e->tcd_qkv2) : e->qkv_out, (nq + 2 * nkv) * c.head_dim, c.d,
                                    (df & 4) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD, (l == 0 ? TCD_X_EMBED : TCD_X_H) | 0x400};
-            jb[4 * l + 1] = TcdJob{w.wo_tm, nullptr, nullptr, nullptr, row_out, c.d, qd, TCD_EPI_ADD, TCD_X_ATT | 0x100};   // 0x100: clears the gate/up sums
+            jb[4 * l + 1] = TcdJob{w.wo_tm, nullptr, nullptr, nullptr, row_out, c.d, qd, row_epi, TCD_X_ATT | 0x100};   // 0x100: clears the gate/up sums
             jb[4 * l + 2] = TcdJob{w.wgu_tm, w.mlp_norm, nullptr, nullptr, (df & 1) ? reinterpret_cast<float *>(e->tcd_gu2) : e->gu_out,
                                    2 * ffn, c.d, (df & 1) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD, TCD_X_H | 0x400 | 0x200};   // 0x200: clears the qkv sums
-            jb[4 * l + 3] = TcdJob{w.wdown_tm, nullptr, nullptr, nullptr, row_out, c.d, ffn, TCD_EPI_ADD, TCD_X_SWIGLU};
+            jb[4 * l + 3] = TcdJob{w.wdown_tm, nullptr, nullptr, nullptr, row_out, c.d, ffn, row_epi, TCD_X_SWIGLU};
         }
         // the lm_head streams whole tiles: N counts the zero rows that pad the last one, p.vocab bounds what is stored
         jb[4 * c.n_layers] = TcdJob{e->lm_head_tm, e->final_norm, nullptr, nullptr, e->logits, (e->vocab_l + 127) / 128 * 128, c.d, TCD_EPI_LOGITS, TCD_X_H};
@@ -1151,7 +1156,9 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
         at.scratch = e->attn_scratch, at.scratch_bytes = e->attn_scratch_bytes;
         // (short contexts: the decode-style kernel, one CTA group per row, still wins -- 296 ids: 8.9 vs 9.7 ms; from ~512 keys on
         // the tiled kernel does -- 1024 ids: 27.8 vs 30.2 ms, 7B at 2072 ids: 132 vs 182 ms)
-        if (pr.lane >= 0 && pr.pos0 + rows >= 512 && getenv("B200LLM_NO_PREFILL_ATTN") == nullptr) {
+        // (it runs one CTA per (128-query tile, q head): with few heads per rank -- tensor parallel 4 / 8 of the 7B: 16 / 8 CTAs per
+        // 256-row chunk -- the decode-style kernel's rows x kv heads x splits CTAs are faster: TTFT at TP 8 134 against 118 ms)
+        if (pr.lane >= 0 && pr.pos0 + rows >= 512 && n_q * ((rows + 127) / 128) >= 32 && getenv("B200LLM_NO_PREFILL_ATTN") == nullptr) {
             // prefill chunk: query-tiled causal attention on the tensor cores (attn_prefill.cu) instead of one decode-style
             // pass over the whole prefix per query row; output as bf16 hi + lo straight into the o_proj operand
             // rows of [head_dim] bf16 from the layer's K (V) base to the end of what page ids can reach: the layer's own region in

@@ -272,6 +272,8 @@ def main():
                     "(single process; do not run under torchrun)")
     ap.add_argument("--config5", action="store_true", help="config 5: the 7B and the 3B co-served on every GPU out of one KV pool "
                     "per GPU, 128 sequences per model in flight (single process; do not run under torchrun)")
+    ap.add_argument("--tp7b", action="store_true", help="config 4: duckdb-nsql-7B tensor parallel over all ranks (run under torchrun "
+                    "with 2, 4 or 8 ranks): 2048 + 24 prompt ids, 64 new tokens; ms per step, tok/s, TTFT, all-reduce share")
     ap.add_argument("--in-flight", type=int, default=128)
     ap.add_argument("--pool-gib", type=float, default=48.0)
     ap.add_argument("--policy", default="least_loaded", choices=["least_loaded", "round_robin"])
@@ -313,8 +315,23 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("gloo")
+        dist.init_process_group("nccl" if args.tp7b else "gloo")   # (the tensor-parallel leg synchronises through device tensors)
     import bench
+    if args.tp7b:
+        if world < 2:
+            raise SystemExit("--tp7b needs torchrun with 2, 4 or 8 ranks")
+        r = bench.bench_tp_7b(rank, world, local)
+        if rank == 0:
+            print("=" * 100)
+            print(f"Config 4: duckdb-nsql-7B, tensor parallel {world}, {r['prompt_ids']} prompt ids, {r['new_tokens']} new tokens (one sequence)")
+            print(f"  {r['ms_per_step']:.3f} ms/step = {r['tok_s']:.1f} tok/s  TTFT {r['ttft_ms']:.1f} ms  "
+                  f"{r['achieved_gbs_per_gpu']:.0f} GB/s per GPU = {100 * r['frac_per_gpu']:.1f}% of the HBM roofline  "
+                  f"one [1, d] all-reduce {r['allreduce_us']:.1f} us (share of the step {r['allreduce_share']:.2f})  "
+                  f"{r['gpu_launches']} launch per decode call")
+            print("=" * 100)
+            print(json.dumps({"config4": r}))
+        dist.destroy_process_group()
+        return
     peak, peak_src = bench.peaks()
     report = {"n_gpus": world, "hbm_peak_gbs": peak, "peak_source": peak_src, "models": []}
     for model in args.models:

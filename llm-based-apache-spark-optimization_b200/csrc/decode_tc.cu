@@ -114,7 +114,10 @@ __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int 
     s.rope = reinterpret_cast<float *>(s.misc + 64);
     s.ptab = reinterpret_cast<int32_t *>(s.rope + 128 * lb);           // per lane: [head_dim/2][cos, sin]
     s.jobs = reinterpret_cast<TcdJob *>(s.ptab + kTMaxPtab * lb);      // per lane: the first kTMaxPtab page-table entries
-    const size_t head = (size_t)(reinterpret_cast<uint8_t *>(s.jobs) - base) + (size_t)n_jobs * sizeof(TcdJob);
+    // (room for the most phase descriptors a launch may have, so that the operand blocks too sit at a compile-time offset:
+    // with the offset depending on n_jobs, ptxas spilled the pointer and every compute thread reloaded it once per phase)
+    (void)n_jobs;
+    const size_t head = (size_t)(reinterpret_cast<uint8_t *>(s.jobs) - base) + (size_t)kTMaxJobs * sizeof(TcdJob);
     s.bop = base + ((head + 1023) & ~(size_t)1023);
     s.ring = s.bop + (size_t)n_bslots * 1024;
     return s;
@@ -122,7 +125,7 @@ __device__ __forceinline__ TcdSmem tcd_carve(uint8_t *base, int hd, int gq, int 
 
 static size_t tcd_fixed_smem_bytes(int hd, int gq, int n_jobs, int lb = 1) {  // everything but the ring and the operand blocks
     return ((tcd_mrg_bytes(hd, gq) + 15) & ~(size_t)15) + tcd_qst_bytes(hd, gq) + (2 * kTMaxStages + 2 * kTAcc + kTSlots + 2) * 8 + 16 + 128 * 4 + 64 * 4 + 128 * 4 * lb +
-           kTMaxPtab * 4 * lb + (size_t)n_jobs * sizeof(TcdJob) + 2 * 1024;  // slack: 1024-byte alignment of the base and of the operand blocks
+           kTMaxPtab * 4 * lb + (size_t)kTMaxJobs * sizeof(TcdJob) + 2 * 1024 + 0 * (size_t)n_jobs;  // slack: 1024-byte alignment of the base and of the operand blocks
 }
 static size_t tcd_smem_bytes(int hd, int gq, int n_jobs, int n_stages, int n_bslots, int lb = 1) {
     return (size_t)n_stages * kTStageBytes + (size_t)n_bslots * 1024 + tcd_fixed_smem_bytes(hd, gq, n_jobs, lb);

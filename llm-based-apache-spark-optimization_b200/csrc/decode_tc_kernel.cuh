@@ -5,9 +5,10 @@
 // operand rows 2b / 2b + 1 and accumulator columns 2b / 2b + 1 belong to lane b, so the weights stream once for all of them)
 template <int HD, int GQ, int NB>
 __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_constant__ TcdParams p) {
-    extern __shared__ uint8_t smem_dyn[];
-    // the swizzled operand tiles need 1024-byte alignment
-    uint8_t *smem_raw = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
+    // the swizzled operand tiles need 1024-byte alignment; declared, not computed: with the base a compile-time shared-memory
+    // address the regions below cost no register at all (a base aligned at run time was spilled and reloaded once per phase)
+    extern __shared__ __align__(1024) uint8_t smem_dyn[];
+    uint8_t *smem_raw = smem_dyn;
     const int n_jobs = 4 * p.n_layers + 1;
     const TcdSmem s = tcd_carve(smem_raw, HD, GQ, n_jobs, p.n_bslots, NB);
     const int nb = NB == 1 ? 1 : p.nb;

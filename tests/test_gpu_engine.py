@@ -609,6 +609,29 @@ def test_batch64_decode_of_the_1b_matches_golden(golden_dir):
     eng.close()
 
 
+def test_several_lanes_at_very_different_positions(golden_dir):
+    """Lanes of one launch at 40, 150, 300 and 470 tokens: their attention runs with 1, 2, 4 and 5 splits per kv head in
+    the same phase (split-T partials merged per lane by the o_proj prologue), pages beyond the first of the table; 8 greedy
+    steps, every lane's tokens equal to the oracle's."""
+    g = np.load(os.path.join(golden_dir, "small.npz"))
+    geo = lo.GEOMETRIES["small"]
+    sd = lo.make_weights(geo, int(g["seed"]), sigma=float(g["sigma"]), embed_sigma=float(g["embed_sigma"]))
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    prompts = [wg.gen_tokens(n, 2000 + n, geo.vocab) for n in (40, 150, 300, 470)]
+    eng = _engine("small", sd, max_lanes=4, max_ctx=512, max_rows=64)
+    lanes = [eng.open_lane() for _ in prompts]
+    want = [orc.greedy(p, 9)[0] for p in prompts]
+    first = []
+    for ln, p in zip(lanes, prompts):
+        eng.prefill(ln, p)
+        first.append(eng.read_lane(ln)[0])
+    got = eng.decode(lanes, 8)
+    assert eng.timing().kernel_launches == 1
+    for i in range(4):
+        assert [first[i]] + got[:, i].tolist() == want[i], f"lane {i} ({len(prompts[i])} ids)"
+    eng.close()
+
+
 @pytest.mark.parametrize("name,n_lanes", [("tiny", 2), ("tiny", 4), ("small", 3), ("small", 4)])
 def test_several_lanes_in_one_persistent_kernel_launch(name, n_lanes, golden_dir):
     """2..4 lanes decoded by ONE launch of the tcgen05 persistent kernel (operand rows 2b / 2b + 1 = lane b): lanes at

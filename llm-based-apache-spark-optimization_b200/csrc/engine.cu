@@ -1252,9 +1252,18 @@ int b200llm_prefill(b200llm_engine *e, int32_t lane, const int32_t *ids, int32_t
     B200_CUDA_OK(cudaMemcpyAsync(e->lane_pos + lane, &last, 4, cudaMemcpyHostToDevice, e->stream));
     if (pos0 == 0) B200_CUDA_OK(cudaMemsetAsync(e->lane_hist + (size_t)lane * 64, 0xFF, 64 * 4, e->stream));
     // pageable sources above are staged by the runtime before the call returns
-    for (int c0 = 0; c0 < n; c0 += c.max_rows) {
+    // chunks of equal size (a multiple of 16 rows) rather than full ones and a remainder: on the GEMM path a pass costs its
+    // weight stream plus an activation re-read that grows with the rows, so 296 ids as 160 + 136 beat 256 + 40
+    int chunk = c.max_rows;
+    static const bool balanced = !(getenv("B200LLM_PREFILL_BALANCED") && atoi(getenv("B200LLM_PREFILL_BALANCED")) == 0);
+    if (balanced && n > c.max_rows) {
+        const int n_chunks = (n + c.max_rows - 1) / c.max_rows;
+        chunk = ((n + n_chunks - 1) / n_chunks + 15) / 16 * 16;
+        if (chunk > c.max_rows) chunk = c.max_rows;
+    }
+    for (int c0 = 0; c0 < n; c0 += chunk) {
         PassRows pr{};
-        pr.rows = n - c0 < c.max_rows ? n - c0 : c.max_rows;
+        pr.rows = n - c0 < chunk ? n - c0 : chunk;
         pr.row_lane = e->pf_lane + c0, pr.row_pos = e->pf_pos + c0, pr.row_token = e->pf_token + c0;
         pr.from_lanes = false;
         pr.lane = lane, pr.pos0 = pos0 + c0;

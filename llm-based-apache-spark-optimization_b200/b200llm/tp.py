@@ -30,11 +30,31 @@ def shard_bounds(n: int, rank: int, size: int):
     return rank * per, (rank + 1) * per
 
 
+# environment switches that decide which kernels a rank launches: ranks that disagree on one of them would leave the
+# lock-step of the reductions (one rank in the persistent kernel, its peer in the per-phase kernels) and wait for each other
+PATH_SWITCHES = ("B200LLM_NO_TCD", "B200LLM_NO_TC", "B200LLM_PERSISTENT", "B200LLM_TCD_STAGES", "B200LLM_TCD_DATAFLOW",
+                 "B200LLM_TC_MIN_ROWS", "B200LLM_NO_PREFILL_ATTN", "B200LLM_PREFILL_BALANCED", "B200LLM_TC_BF16ACT")
+
+
+def check_same_path(group=None, extra=()) -> None:
+    """Collective: raise on every rank unless all ranks of `group` see the same path-selecting settings (and `extra`,
+    e.g. the engine's use_megakernel / use_tc / max_rows)."""
+    import os
+    mine = tuple(os.environ.get(k) for k in PATH_SWITCHES) + tuple(extra)
+    box = [None] * dist.get_world_size(group)
+    dist.all_gather_object(box, mine, group=group)
+    if any(b != box[0] for b in box):
+        bad = [k for i, k in enumerate(PATH_SWITCHES + tuple(f"extra[{j}]" for j in range(len(extra))))
+               if any(b[i] != box[0][i] for b in box)]
+        raise RuntimeError(f"tensor-parallel ranks disagree on {bad}: {box}")
+
+
 def connect_peers(engine, group=None) -> None:
     """Collective: switch `engine` (one per rank of `group`, all on one node) from ncclAllReduce to the
     one-shot all-reduce over NVLink peer memory (csrc/tp_ar.cu).  Every rank exports the CUDA IPC handle
     of its inbox region, the handles travel over torch.distributed, every rank opens its peers'."""
     size = dist.get_world_size(group)
+    check_same_path(group, (bool(engine.cfg.use_megakernel), bool(engine.cfg.use_tc), int(engine.cfg.max_rows), int(engine.cfg.use_graphs)))
     buf = C.create_string_buffer(64)
     _lib.check(_lib.lib.b200llm_tp_export(engine._h, buf))
     box = [None] * size

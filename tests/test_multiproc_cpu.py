@@ -47,6 +47,22 @@ def _worker(rank, world, port, out_dir):
         v = np.concatenate([b[(_lib.W_LM_HEAD, -1)] for b in box], 0)
         assert np.array_equal(v, sd["model.embed_tokens.weight"].view(torch.int16).numpy())
     assert tp.shard_bounds(geo.ffn, rank, world) == (rank * geo.ffn // world, (rank + 1) * geo.ffn // world)
+    # 2b. ranks must agree on the switches that select the kernels (a rank alone in the persistent kernel would wait for
+    # its peers for ever): same settings pass, a switch set on one rank only is named in the error on EVERY rank
+    tp.check_same_path(extra=(True, 256))
+    if rank == 1:
+        os.environ["B200LLM_NO_TCD"] = "1"
+    try:
+        tp.check_same_path(extra=(True, 256))
+        raise AssertionError("a disagreement went unnoticed")
+    except RuntimeError as e:
+        assert "B200LLM_NO_TCD" in str(e)
+    os.environ.pop("B200LLM_NO_TCD", None)
+    try:
+        tp.check_same_path(extra=(True, 256 + rank))
+        raise AssertionError("a disagreement went unnoticed")
+    except RuntimeError as e:
+        assert "extra[1]" in str(e)
     # 3. the timing reduction bench.py does: max over ranks
     t = torch.tensor([1.0 + rank], dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)

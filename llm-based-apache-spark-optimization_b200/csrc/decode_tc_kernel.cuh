@@ -223,8 +223,12 @@ __global__ void __launch_bounds__(kTThreads, 1) tcd_decode_kernel(const __grid_c
                 continue;
             }
             for (int b = 0; b < nb; ++b) {
-                float m = c.best[NB == 1 ? 0 : b];
-                int mi = c.best_i[NB == 1 ? 0 : b];
+                // (static indices only: an array indexed by b would live in local memory and every epilogue would load and store it)
+                float m = c.best[0];
+                int mi = c.best_i[0];
+#pragma unroll
+                for (int l = 1; l < NB; ++l)
+                    if (l == b) m = c.best[l], mi = c.best_i[l];
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) {
                     const float om = __shfl_xor_sync(0xffffffffu, m, o);

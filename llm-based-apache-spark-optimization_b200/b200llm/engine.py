@@ -52,7 +52,8 @@ class Engine:
     def __init__(self, geo: Geometry, weights: PackedWeights, device: int = 0, max_lanes: int = 8,
                  max_ctx: int = 4096, max_rows: int = 64, kv_pages: Optional[int] = None, tp_rank: int = 0,
                  tp_size: int = 1, nccl_id: Optional[bytes] = None, use_graphs: bool = True, use_pdl: bool = False,
-                 attn_splits: int = 0, use_megakernel: bool = True, use_tc: bool = True, kv_pool=None, name: str = ""):
+                 attn_splits: int = 0, use_megakernel: bool = True, use_tc: bool = True, kv_pool=None, name: str = "",
+                 lean_weights: bool = False):
         if not torch.cuda.is_available():
             raise _lib.B200LLMError(_lib.ENODEV, "no CUDA device: b200llm has no CPU fallback")
         self.geo, self.weights, self.device = geo, weights, device
@@ -64,6 +65,11 @@ class Engine:
                 add_tile_major(weights)     # (tensor parallel: of this rank's shards; used once tp.connect_peers ran)
             elif tp_size == 1:
                 add_stage_major(weights)
+        if lean_weights:
+            # keep the tile-major matrices only: the persistent kernel (1-4 lanes) and the tcgen05 GEMM path (everything else)
+            # both stream them; the row-major ones, which only the GEMV kernels read, are dropped -- half the weight footprint
+            from .weights import drop_row_major
+            drop_row_major(weights)
         self.max_lanes, self.max_rows = max_lanes, max_rows
         self.max_pages_per_lane = (max_ctx + PAGE_TOKENS - 1) // PAGE_TOKENS
         torch.cuda.set_device(device)

@@ -74,7 +74,9 @@ def get_model(name: str) -> LoadedModel:
                 w = weights.random_init(geo, SEED, dev)
             engines.append(Engine(geo, w, device=dev, max_lanes=int(os.environ.get("B200LLM_MAX_LANES", "8")),
                                   max_ctx=int(os.environ.get("B200LLM_NUM_CTX", "4096")),
-                                  max_rows=int(os.environ.get("B200LLM_MAX_ROWS", "256"))))   # prefill chunk = tcgen05 GEMM N limit
+                                  max_rows=int(os.environ.get("B200LLM_MAX_ROWS", "256")),   # prefill chunk = tcgen05 GEMM N limit
+                                  # B200LLM_LEAN_WEIGHTS=1: tile-major matrices only (half the weight bytes; no GEMV fallback)
+                                  lean_weights=os.environ.get("B200LLM_LEAN_WEIGHTS", "0") not in ("", "0")))
         # a checkpoint with tokenizer tables is prompted through its model's template (by the registered name, else
         # by the base name before ':'); without tables text goes through the byte stand-in, untemplated
         template = (TEMPLATES.get(name) or TEMPLATES.get(name.split(":")[0], "")) if tok is not None else ""

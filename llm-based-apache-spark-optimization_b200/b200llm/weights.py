@@ -147,6 +147,22 @@ def add_tile_major(pw: "PackedWeights", start: int = 0) -> None:
             pw.tensors.append((_TM_KIND[kind], layer, tile_major(t)))
 
 
+def drop_row_major(pw: "PackedWeights") -> None:
+    """Lean engine: remove the row-major matrices that have a tile-major copy (qkv, o, gate/up, down, and the lm_head unless
+    it is the embedding table itself), freeing their memory.  Needs one GPU, a vocabulary that is a multiple of 128 and all
+    five kinds of tile-major copies (b200llm_bind_weights checks)."""
+    have_tm = {(k, l) for k, l, _ in pw.tensors if k in _TM_KIND.values()}
+    if pw.tp_size != 1 or not all((_TM_KIND[k], l) in have_tm for k, l, _ in pw.tensors if k in _TM_KIND):
+        raise ValueError("drop_row_major: needs tp_size 1 and a tile-major copy of every matrix (use_megakernel on a geometry that tiles)")
+    embed = next(t for k, _, t in pw.tensors if k == _lib.W_EMBED)
+    keep = []
+    for k, l, t in pw.tensors:
+        if k in _TM_KIND and not (k == _lib.W_LM_HEAD and t.data_ptr() == embed.data_ptr()):
+            continue
+        keep.append((k, l, t))
+    pw.tensors[:] = keep
+
+
 def add_stage_major(pw: "PackedWeights", start: int = 0) -> None:
     """Append stage-major copies of the matrices pw.tensors[start:] (persistent-kernel layout)."""
     for kind, layer, t in list(pw.tensors[start:]):

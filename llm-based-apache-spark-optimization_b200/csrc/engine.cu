@@ -116,6 +116,7 @@ struct b200llm_engine {
     size_t kv_half_stride = 0;  // bytes from one layer's K region to its V region (and on to the next layer's K)
     int kv_page_heads = 0;      // (kv head, 16-token) tiles from one page to the next: nkv_l, or a shared pool's slot size
     bool kv_shared = false;     // pages are page-major slots of a pool shared with other engines
+    bool lean = false;          // only the tile-major matrices are bound: every pass runs the persistent kernel or the tcgen05 GEMM path
     // workspace
     uint8_t *ws = nullptr;
     float *h, *q, *att, *act, *delta, *logits, *part_max;
@@ -545,9 +546,20 @@ int b200llm_bind_weights(b200llm_engine *e, const b200llm_tensor_desc *descs, in
             default: set_error("tensor %d: unknown kind %d", i, t.kind); return B200LLM_EINVAL;
         }
     }
-    bool all = e->embed && e->lm_head && e->final_norm && e->inv_freq;
-    for (auto &l : e->layers) all = all && l.attn_norm && l.wqkv && l.wo && l.mlp_norm && l.wgu && l.wdown;
-    e->weights_bound = all;
+    // Either the row-major matrices (every path available) or, without them, all tile-major ones ("lean": half the weight
+    // footprint; the GEMV kernels, which read row-major rows, are then not available -- one GPU, vocabulary a multiple of 128)
+    bool norms = e->embed && e->final_norm && e->inv_freq;
+    for (auto &l : e->layers) norms = norms && l.attn_norm && l.mlp_norm;
+    bool rows_all = e->lm_head != nullptr, tiles_all = e->lm_head_tm != nullptr;
+    for (auto &l : e->layers) {
+        rows_all = rows_all && l.wqkv && l.wo && l.wgu && l.wdown;
+        tiles_all = tiles_all && l.wqkv_tm && l.wo_tm && l.wgu_tm && l.wdown_tm;
+    }
+    e->lean = norms && !rows_all && tiles_all;
+    if (e->lean)
+        B200_REQUIRE(c.tp_size == 1 && c.vocab % 128 == 0 && c.use_tc && c.use_megakernel,
+                     "bind_weights: tile-major matrices alone need tp_size 1, a vocabulary that is a multiple of 128, use_tc and use_megakernel");
+    e->weights_bound = norms && (rows_all || tiles_all);
     return B200LLM_OK;
 }
 
@@ -1085,7 +1097,7 @@ static bool tc_usable(const b200llm_engine *e, int rows) {
     // from 3 rows on the GEMM path is faster per step than the per-phase GEMV kernels (3B: 2.4 ms at any batch <= 16 against
     // 2.3 / 3.3 ms at 2 / 4 rows; profiles/harness_r2.txt)
     static const int min_rows = getenv("B200LLM_TC_MIN_ROWS") ? atoi(getenv("B200LLM_TC_MIN_ROWS")) : 3;
-    return c.use_tc && rows >= min_rows && rows <= 256 && okn((e->nq_l + 2 * e->nkv_l) * c.head_dim) && okn(c.d) &&
+    return c.use_tc && rows >= (e->lean ? 1 : min_rows) && rows <= 256 && okn((e->nq_l + 2 * e->nkv_l) * c.head_dim) && okn(c.d) &&
            okn(2 * e->ffn_l) && lm_ok && okk(c.d) && okk(e->nq_l * c.head_dim) && okk(e->ffn_l) &&
            getenv("B200LLM_NO_TC") == nullptr;
 }
@@ -1098,8 +1110,13 @@ static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, i
     const uint16_t *xb = x_buf ? reinterpret_cast<const uint16_t *>(x_buf) : e->xb;
     const int64_t lo = xb == e->xb2 ? e->xb2_lo : e->xb_lo;
     const int bk = tc_bk(T, lo != 0);
-    B200_TRY(get_map(e, w, N, K, 128, &mw, bk));
     B200_TRY(get_map(e, xb, e->cfg.max_rows, K, tc_x_box(N, T), &mx, bk));
+    if (w != nullptr) {
+        B200_TRY(get_map(e, w, N, K, 128, &mw, bk));
+    } else {   // lean engine: the weight tiles come from the tile-major copy, the kernel never touches its weight map
+        B200_REQUIRE(w_tm != nullptr, "gemm: neither a row-major nor a tile-major matrix");
+        mw = mx;
+    }
     if (lo != 0) B200_TRY(get_map(e, xb + lo, e->cfg.max_rows, K, tc_x_box(N, T), &mxl, bk));
     int accumulate = 1;
     if (out_swiglu != nullptr) {
@@ -1113,7 +1130,10 @@ static int tc_gemm(b200llm_engine *e, const void *w, int N, int K, float *out, i
     }
     // the tile-major copy (bound for the persistent decode kernel) serves this kernel too: one 16 KB bulk copy per weight tile
     static const bool use_tm = !(getenv("B200LLM_TC_TM") && atoi(getenv("B200LLM_TC_TM")) == 0);
-    if (!use_tm || bk != 64 || tc_cluster_size(N, T) != 1) w_tm = nullptr;
+    if (!use_tm || bk != 64 || tc_cluster_size(N, T) != 1) {
+        B200_REQUIRE(w != nullptr, "gemm: this engine holds tile-major matrices only (B200LLM_TC_TM=0, B200LLM_TC_BK=32 and B200LLM_TC_CLUSTER need the row-major ones)");
+        w_tm = nullptr;
+    }
     B200_TRY(tc_gemm_launch(mw, mx, out, out_stride, T, N, K, accumulate, e->stream, e->tc_pdl, out_swiglu, mxl,
                             out_swiglu != nullptr ? e->xb2_lo : 0, bk, w_tm));
     e->launches++;
@@ -1227,6 +1247,7 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
 
 static int forward_pass(b200llm_engine *e, const PassRows &pr, bool advance) {
     if (tc_usable(e, pr.rows)) return forward_pass_tc(e, pr, advance);
+    B200_REQUIRE(!e->lean, "this pass (%d rows) needs the GEMV kernels, which read the row-major matrices this engine was not given", pr.rows);
     return forward_pass_gemv(e, pr, advance);
 }
 
@@ -1326,7 +1347,7 @@ int b200llm_decode(b200llm_engine *e, const int32_t *lanes, int32_t n_lanes, int
     } else if (c.use_megakernel && n_lanes == 1 && (greedy || in_kernel) && tcd_usable(e)) {
         B200_TRY(tcd_decode(e, lanes, 1, n_steps, in_kernel));
         e->timing.kernel_launches = 1;
-    } else if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy &&
+    } else if (c.use_megakernel && n_lanes == 1 && c.tp_size == 1 && greedy && !e->lean &&
                mega_supported(c.d, c.ffn, c.n_q, c.n_kv, c.head_dim)) {
         B200_TRY(mega_decode(e, lanes[0], n_steps));
         e->timing.kernel_launches = 1;

@@ -721,3 +721,52 @@ def test_binding_a_buffer_of_another_gpu_is_refused():
         Engine(geo, w_other, device=0, max_lanes=1, max_ctx=64, max_rows=8)
     assert ei.value.code == _lib.EINVAL and "GPU 1" in str(ei.value) and "GPU 0" in str(ei.value)
     torch.cuda.set_device(0)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small"])
+def test_lean_engine_with_tile_major_weights_only(name, golden_dir):
+    """lean_weights=True drops the row-major matrices (the GEMV kernels' layout): the persistent kernel (1-4 lanes) and the
+    tcgen05 GEMM path (prefill chunks down to a single row, larger batches) both stream the tile-major copies.  Same
+    tokens as the oracle on every path, about half the weight bytes, and a clear error where a GEMV kernel would be needed."""
+    from b200llm import Engine, SamplingParams, _lib, geometry, weights
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    ogeo = lo.GEOMETRIES[name]
+    sd = lo.make_weights(ogeo, int(g["seed"]), sigma=float(g["sigma"]), embed_sigma=float(g["embed_sigma"]))
+    orc = lo.LlamaOracle(ogeo, sd, kv_dtype=torch.bfloat16)
+    geo = geometry.resolve(name)
+    full = weights.pack(geo, {k: v.cuda() for k, v in sd.items()})
+    weights.add_tile_major(full)
+    full_bytes = sum(t.numel() * t.element_size() for _, _, t in full.tensors)
+    w = weights.pack(geo, {k: v.cuda() for k, v in sd.items()})
+    eng = Engine(geo, w, max_lanes=6, max_ctx=160, max_rows=32, lean_weights=True)
+    lean_bytes = sum(t.numel() * t.element_size() for _, _, t in w.tensors)
+    assert lean_bytes < 0.7 * full_bytes
+    prompts = [wg.gen_tokens(n, 3000 + n, ogeo.vocab) for n in (33, 64, 20, 47, 9, 70)]      # 33 = 32 + a 1-row tail chunk
+    want = [orc.greedy(p, 9)[0] for p in prompts]
+    lanes = [eng.open_lane() for _ in prompts]
+    first = []
+    for ln, p in zip(lanes, prompts):
+        eng.prefill(ln, p)
+        first.append(eng.read_lane(ln)[0])
+    one = eng.decode(lanes[:1], 8)                      # persistent kernel, one lane
+    assert eng.timing().kernel_launches == 1 and [first[0]] + one[:, 0].tolist() == want[0]
+    three = eng.decode(lanes[1:4], 8)                   # persistent kernel, three lanes
+    assert eng.timing().kernel_launches == 1
+    for j in range(3):
+        assert [first[1 + j]] + three[:, j].tolist() == want[1 + j]
+    for ln, p in zip(lanes, prompts):                   # six lanes at once: the GEMM path
+        eng.close_lane(ln)
+    lanes = [eng.open_lane() for _ in prompts]
+    for ln, p in zip(lanes, prompts):
+        eng.prefill(ln, p)
+    six = eng.decode(lanes, 8)
+    for j in range(6):
+        assert [first[j]] + six[:, j].tolist() == want[j], f"lane {j} on the GEMM path"
+    # a sampler setting the persistent kernel does not take (top-k 200) runs the GEMM pass + the stand-alone sampler
+    eng.set_sampling(lanes[0], SamplingParams(temperature=0.7, top_k=200, top_p=0.95, repeat_penalty=1.0, seed=3))
+    assert eng.decode(lanes[:1], 2).shape == (2, 1) and eng.timing().kernel_launches > 1
+    eng.close()
+    # without the tcgen05 GEMM path nothing could run the prefill: refused at bind time
+    w2 = weights.pack(geo, {k: v.cuda() for k, v in sd.items()})
+    with pytest.raises(_lib.B200LLMError):
+        Engine(geo, w2, max_lanes=1, max_ctx=64, max_rows=8, lean_weights=True, use_tc=False)

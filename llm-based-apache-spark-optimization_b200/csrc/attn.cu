@@ -352,6 +352,234 @@ int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl
 }
 
 
+// ---------------------------------------------------------------- prefill chunks at short contexts
+//
+// attn_rows_kernel: the query rows of one prefill chunk (consecutive positions of ONE lane), four rows per CTA.
+// The decode kernel above gives every row its own CTA and streams the row's whole prefix from L2 for it: a chunk of
+// 160 rows re-reads the same K/V tiles 160 times (~200 MB of L2 reads per layer at 300 keys, which is what bounds it).
+// Here one CTA = one KV head x 4 consecutive rows; every page's K and V tiles are fetched ONCE per CTA into a 3-deep
+// shared ring (1-D TMA bulk copies) and all four warps -- one row each, with its own causal limit -- score it.  Same
+// arithmetic per row as the decode kernel (page-at-a-time online softmax in the log2 domain, 8 lanes per token), no
+// cross-warp merge (a warp owns its row), output as the bf16 hi + lo operand of the o_proj GEMM.
+// Used below ~512 keys (and where a rank has few heads); beyond, the tensor-core kernel of attn_prefill.cu takes over.
+constexpr int kRowsStages = 3;
+
+template <int HD, int G>
+__global__ void __launch_bounds__(kAttnWarps * 32) attn_rows_kernel(const __grid_constant__ AttnDev p) {
+    constexpr int EL = HD / 16;
+    constexpr int TILE = kPT * HD * 2;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const b200llm_attn_args &a = p.a;
+    const int hk = blockIdx.y;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tg = lane >> 3, p8 = lane & 7;
+    uint8_t *tiles = smem;                                                     // [stages][K tile | V tile]
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)kRowsStages * 2 * TILE);
+
+    if (tid == 0) {
+        for (int s = 0; s < kRowsStages; ++s) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_trigger();
+    pdl_wait();  // q and the chunk's K/V come from the previous kernels
+
+    const int row_first = blockIdx.x * kAttnWarps;
+    const int row = row_first + warp;
+    const bool live = row < a.bs;
+    const int row_last = min(row_first + kAttnWarps, a.bs) - 1;
+    const int pos = live ? a.row_pos[row] : -1;          // a warp without a row masks everything
+    const int n_pages = a.row_pos[row_last] / kPT + 1;   // positions ascend inside a chunk: the last row sees the most
+    const int32_t *ptab = a.page_table + (size_t)a.row_lane[row_first] * a.max_pages_per_lane;
+    const uint8_t *kbase = reinterpret_cast<const uint8_t *>(a.k_pages);
+    const uint8_t *vbase = reinterpret_cast<const uint8_t *>(a.v_pages);
+
+    float qa[G][EL], qb[G][EL];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const float *qp = a.q + (size_t)(live ? row : row_first) * a.n_q * HD + (size_t)(hk * G + g) * HD;
+#pragma unroll
+        for (int e = 0; e < EL; ++e) {
+            qa[g][e] = qp[p8 * EL + e] * p.scale_log2;
+            qb[g][e] = qp[HD / 2 + p8 * EL + e] * p.scale_log2;
+        }
+    }
+    float m[G], l[G], oa[G][EL], ob[G][EL];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        m[g] = -INFINITY, l[g] = 0.f;
+#pragma unroll
+        for (int e = 0; e < EL; ++e) oa[g][e] = 0.f, ob[g][e] = 0.f;
+    }
+    auto issue = [&](int i) {
+        const int st = i % kRowsStages;
+        const size_t off = ((size_t)ptab[i] * (a.kv_page_heads > 0 ? a.kv_page_heads : a.n_kv) + hk) * (size_t)TILE;
+        mbar_expect_tx(&full[st], 2 * TILE);
+        tma_load_1d(tiles + (size_t)st * 2 * TILE, kbase + off, TILE, &full[st]);
+        tma_load_1d(tiles + (size_t)st * 2 * TILE + TILE, vbase + off, TILE, &full[st]);
+    };
+    if (tid == 0)
+        for (int i = 0; i < min(n_pages, kRowsStages); ++i) issue(i);
+    for (int i = 0; i < n_pages; ++i) {
+        const int st = i % kRowsStages;
+        mbar_wait(&full[st], (i / kRowsStages) & 1);
+        const int t0 = i * kPT;
+        if (t0 <= pos) {   // (warp-uniform) the page holds keys this row may see
+            const uint8_t *ks = tiles + (size_t)st * 2 * TILE;
+            const uint8_t *vs = ks + TILE;
+            float sc[kPT / 4][G];
+#pragma unroll
+            for (int it = 0; it < kPT / 4; ++it) {
+                const int t = it * 4 + tg;
+                float ka[EL], kb[EL];
+                if constexpr (EL == 8) {
+                    const uint4 A = *reinterpret_cast<const uint4 *>(ks + (size_t)t * HD * 2 + p8 * 16);
+                    const uint4 B = *reinterpret_cast<const uint4 *>(ks + (size_t)t * HD * 2 + HD + p8 * 16);
+                    const uint32_t aw[4] = {A.x, A.y, A.z, A.w}, bw[4] = {B.x, B.y, B.z, B.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        ka[2 * e] = bf16lo(aw[e]), ka[2 * e + 1] = bf16hi(aw[e]);
+                        kb[2 * e] = bf16lo(bw[e]), kb[2 * e + 1] = bf16hi(bw[e]);
+                    }
+                } else {
+                    const uint2 A = *reinterpret_cast<const uint2 *>(ks + (size_t)t * HD * 2 + p8 * 8);
+                    const uint2 B = *reinterpret_cast<const uint2 *>(ks + (size_t)t * HD * 2 + HD + p8 * 8);
+                    ka[0] = bf16lo(A.x), ka[1] = bf16hi(A.x), ka[2] = bf16lo(A.y), ka[3] = bf16hi(A.y);
+                    kb[0] = bf16lo(B.x), kb[1] = bf16hi(B.x), kb[2] = bf16lo(B.y), kb[3] = bf16hi(B.y);
+                }
+                const bool ok = (t0 + t) <= pos;
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+                    float s = 0.f;
+#pragma unroll
+                    for (int e = 0; e < EL; ++e) s = fmaf(qa[g][e], ka[e], fmaf(qb[g][e], kb[e], s));
+                    s += __shfl_xor_sync(0xffffffffu, s, 1);
+                    s += __shfl_xor_sync(0xffffffffu, s, 2);
+                    s += __shfl_xor_sync(0xffffffffu, s, 4);
+                    sc[it][g] = ok ? s : -INFINITY;
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float mn = m[g];
+#pragma unroll
+                for (int it = 0; it < kPT / 4; ++it) mn = fmaxf(mn, sc[it][g]);
+                const float corr = mn == -INFINITY ? 1.f : exp2f(m[g] - mn);
+                float ps = 0.f;
+#pragma unroll
+                for (int it = 0; it < kPT / 4; ++it) {
+                    sc[it][g] = mn == -INFINITY ? 0.f : exp2f(sc[it][g] - mn);
+                    ps += sc[it][g];
+                }
+                l[g] = l[g] * corr + ps;
+                m[g] = mn;
+#pragma unroll
+                for (int e = 0; e < EL; ++e) oa[g][e] *= corr, ob[g][e] *= corr;
+            }
+#pragma unroll
+            for (int it = 0; it < kPT / 4; ++it) {
+                const int t = it * 4 + tg;
+                float va[EL], vb[EL];
+                if constexpr (EL == 8) {
+                    const uint4 C = *reinterpret_cast<const uint4 *>(vs + (size_t)t * HD * 2 + p8 * 16);
+                    const uint4 D = *reinterpret_cast<const uint4 *>(vs + (size_t)t * HD * 2 + HD + p8 * 16);
+                    const uint32_t cw[4] = {C.x, C.y, C.z, C.w}, dw[4] = {D.x, D.y, D.z, D.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        va[2 * e] = bf16lo(cw[e]), va[2 * e + 1] = bf16hi(cw[e]);
+                        vb[2 * e] = bf16lo(dw[e]), vb[2 * e + 1] = bf16hi(dw[e]);
+                    }
+                } else {
+                    const uint2 C = *reinterpret_cast<const uint2 *>(vs + (size_t)t * HD * 2 + p8 * 8);
+                    const uint2 D = *reinterpret_cast<const uint2 *>(vs + (size_t)t * HD * 2 + HD + p8 * 8);
+                    va[0] = bf16lo(C.x), va[1] = bf16hi(C.x), va[2] = bf16lo(C.y), va[3] = bf16hi(C.y);
+                    vb[0] = bf16lo(D.x), vb[1] = bf16hi(D.x), vb[2] = bf16lo(D.y), vb[3] = bf16hi(D.y);
+                }
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+#pragma unroll
+                    for (int e = 0; e < EL; ++e) {
+                        oa[g][e] = fmaf(sc[it][g], va[e], oa[g][e]);
+                        ob[g][e] = fmaf(sc[it][g], vb[e], ob[g][e]);
+                    }
+                }
+            }
+        }
+        __syncthreads();   // all four warps are done with the stage: its next page may land
+        if (tid == 0 && i + kRowsStages < n_pages) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            issue(i + kRowsStages);
+        }
+    }
+    // merge the 4 token-group streams of the warp; every lane ends with the row's totals
+#pragma unroll
+    for (int off = 8; off <= 16; off <<= 1) {
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            const float m2 = __shfl_xor_sync(0xffffffffu, m[g], off);
+            const float l2 = __shfl_xor_sync(0xffffffffu, l[g], off);
+            float c1, c2;
+            merge_state(m[g], l[g], m2, l2, c1, c2);
+#pragma unroll
+            for (int e = 0; e < EL; ++e) {
+                const float o2a = __shfl_xor_sync(0xffffffffu, oa[g][e], off);
+                const float o2b = __shfl_xor_sync(0xffffffffu, ob[g][e], off);
+                oa[g][e] = oa[g][e] * c1 + o2a * c2;
+                ob[g][e] = ob[g][e] * c1 + o2b * c2;
+            }
+        }
+    }
+    if (live && tg == 0) {
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            const float inv = 1.f / l[g];
+            const size_t base = (size_t)row * a.n_q * HD + (size_t)(hk * G + g) * HD;
+#pragma unroll
+            for (int e = 0; e < EL; ++e) {
+                const float ya = oa[g][e] * inv, yb = ob[g][e] * inv;
+                const size_t ia = base + p8 * EL + e, ib = base + HD / 2 + p8 * EL + e;
+                if (p.out_bf16 != nullptr) {
+                    const uint16_t ha = f32_to_bf16_bits(ya), hb = f32_to_bf16_bits(yb);
+                    p.out_bf16[ia] = ha, p.out_bf16[ib] = hb;
+                    if (p.out_lo_off != 0) {
+                        p.out_bf16[p.out_lo_off + ia] = f32_to_bf16_bits(ya - __uint_as_float((uint32_t)ha << 16));
+                        p.out_bf16[p.out_lo_off + ib] = f32_to_bf16_bits(yb - __uint_as_float((uint32_t)hb << 16));
+                    }
+                } else {
+                    a.out[ia] = ya, a.out[ib] = yb;
+                }
+            }
+        }
+    }
+}
+
+template <int HD, int G>
+static int launch_attn_rows(const AttnDev &d, cudaStream_t stream, bool pdl) {
+    constexpr size_t smem = (size_t)kRowsStages * 2 * kPT * HD * 2 + kRowsStages * 8;
+    LaunchCfg lc(dim3((d.a.bs + kAttnWarps - 1) / kAttnWarps, d.a.n_kv), dim3(kAttnWarps * 32), smem, stream, pdl);
+    B200_CUDA_OK(cudaLaunchKernelEx(&lc.cfg, attn_rows_kernel<HD, G>, d));
+    return B200LLM_OK;
+}
+
+// rows = consecutive positions of one lane (a prefill chunk): a.row_pos ascending, a.row_lane all equal
+int attn_rows_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16, int64_t out_lo_off) {
+    B200_REQUIRE(a.page_tokens == kPT, "attn: page_tokens must be %d (got %d)", kPT, a.page_tokens);
+    B200_REQUIRE(a.n_kv > 0 && a.n_q % a.n_kv == 0 && a.bs >= 1, "attn: bad head counts / rows");
+    AttnDev d{};
+    d.a = a;
+    d.out_bf16 = reinterpret_cast<uint16_t *>(out_bf16);
+    d.out_lo_off = out_lo_off;
+    d.scale_log2 = (float)(1.4426950408889634 / sqrt((double)a.head_dim));
+    const int G = a.n_q / a.n_kv;
+#define B200_ATTN_CASE(HD_, G_) \
+    if (a.head_dim == HD_ && G == G_) return launch_attn_rows<HD_, G_>(d, stream, pdl);
+    B200_ATTN_CASE(128, 1) B200_ATTN_CASE(128, 2) B200_ATTN_CASE(128, 3) B200_ATTN_CASE(128, 4)
+    B200_ATTN_CASE(64, 1) B200_ATTN_CASE(64, 2) B200_ATTN_CASE(64, 4)
+#undef B200_ATTN_CASE
+    set_error("attn: unsupported head_dim %d / group %d", a.head_dim, G);
+    return B200LLM_EINVAL;
+}
+
 // ---------------------------------------------------------------- no-allocation variant
 //
 // b200llm_op_attn_decode_static: the same split-T decode attention for callers that cannot

@@ -14,6 +14,8 @@ int gemv_grid(int N, int K, int bs, int epi, int grid_hint);
 // attn.cu
 int attn_decode_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16 = nullptr,
                        int64_t out_lo_off = 0);
+// prefill chunk (consecutive rows of one lane) at short contexts: 4 rows per CTA share every K/V tile (attn.cu)
+int attn_rows_launch(const b200llm_attn_args &a, cudaStream_t stream, bool pdl, void *out_bf16, int64_t out_lo_off);
 size_t attn_scratch_bytes(int bs, int n_q, int n_kv, int head_dim, int n_splits);
 // The arrival tickets live in a fixed-size region at the start of the scratch buffer, so that
 // launches with different batch sizes sharing one buffer never put partials where another

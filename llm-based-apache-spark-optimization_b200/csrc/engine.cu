@@ -1191,7 +1191,8 @@ static int forward_pass_tc(b200llm_engine *e, const PassRows &pr, bool advance) 
             B200_TRY(get_map(e, vl, v_rows, c.head_dim, c.page_tokens, &mv));
             B200_TRY(attn_prefill_launch(mk, mv, e->q, nullptr, e->xb, e->xb_lo, e->page_table + (size_t)pr.lane * c.max_pages_per_lane,
                                          c.max_pages_per_lane, rows, pr.pos0, n_q, n_kv, c.head_dim, e->kv_page_heads, st, pdl));
-        } else if (pr.lane >= 0 && rows >= 4 && n_kv * ((rows + 3) / 4) >= 1000 && getenv("B200LLM_NO_ROWS_ATTN") == nullptr) {
+        } else if (pr.lane >= 0 && rows >= 4 && (n_kv * ((rows + 3) / 4) >= 1000 || getenv("B200LLM_ROWS_ATTN") != nullptr) &&
+                   getenv("B200LLM_NO_ROWS_ATTN") == nullptr) {
             // prefill chunk at a short context, many kv heads (the 7B: 32): four rows per CTA share every K/V tile
             // (attn_rows_kernel) instead of one CTA per row streaming the row's whole prefix from L2.  A warp there walks all
             // pages of its row, so it needs the CTAs to fill the GPU twice over: 7B at 296 ids 18.3 -> 17.4 ms, but the 3B

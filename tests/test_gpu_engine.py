@@ -770,3 +770,28 @@ def test_lean_engine_with_tile_major_weights_only(name, golden_dir):
     w2 = weights.pack(geo, {k: v.cuda() for k, v in sd.items()})
     with pytest.raises(_lib.B200LLMError):
         Engine(geo, w2, max_lanes=1, max_ctx=64, max_rows=8, lean_weights=True, use_tc=False)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small"])
+def test_prefill_with_the_row_group_attention_kernel(name, golden_dir, monkeypatch):
+    """attn_rows_kernel (four rows of a prefill chunk per CTA share every K/V tile; the engine picks it for short contexts
+    with many kv heads) forced on for the small geometries: ragged prompts in 32-row chunks (a 3-row tail takes the per-row
+    kernel), prefill logits and 6 greedy tokens against the oracle."""
+    monkeypatch.setenv("B200LLM_ROWS_ATTN", "1")
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    geo = lo.GEOMETRIES[name]
+    sd = lo.make_weights(geo, int(g["seed"]), sigma=float(g["sigma"]), embed_sigma=float(g["embed_sigma"]))
+    orc = lo.LlamaOracle(geo, sd, kv_dtype=torch.bfloat16)
+    eng = _engine(name, sd, max_lanes=2, max_ctx=256, max_rows=32, use_tc=True)
+    for n in (7, 35, 64, 150, 201):
+        p = wg.gen_tokens(n, 4100 + n, geo.vocab)
+        st = orc.new_state()
+        ref = orc.forward(torch.as_tensor(p, dtype=torch.int64), st)
+        lane = eng.open_lane()
+        eng.prefill(lane, p)
+        eng.sync()
+        assert _rel(eng.logits(0), ref.numpy()) <= TIGHT_TOL, n
+        want = orc.greedy(p, 6)[0]
+        assert [eng.read_lane(lane)[0]] + eng.decode([lane], 5)[:, 0].tolist() == want, n
+        eng.close_lane(lane)
+    eng.close()

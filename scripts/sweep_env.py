@@ -17,7 +17,11 @@ from b200llm import Engine, SamplingParams, geometry, weights
 
 
 def main():
-    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    argv = sys.argv[1:]
+    if "--steps" in argv:        # (its value is not a sweep)
+        i = argv.index("--steps")
+        argv = argv[:i] + argv[i + 2:]
+    args = [a for a in argv if not a.startswith("--")]
     model, sweeps = args[0], [a.split("=") for a in args[1:]]
     steps = int(sys.argv[sys.argv.index("--steps") + 1]) if "--steps" in sys.argv else 128
     geo = geometry.resolve(model)

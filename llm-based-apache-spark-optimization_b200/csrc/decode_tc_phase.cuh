@@ -211,6 +211,13 @@ __device__ TcdScale<NB> tcd_prologue(const TcdParams &p, const TcdJob &job, cons
     }
     // phases with a norm (or that seed the residual stream from the embedding) read the whole
     // vector; the others only the chunks (8 values) of the k blocks this CTA streams
+    // The operand blocks below are still being READ by the previous phase's MMAs until that phase's accumulators are
+    // drained.  Where a grid barrier separates the phases, the epilogue warps have passed it; the attention edges have a
+    // CTA barrier of their own (tcd_attn_wait_qkv).  On the gate/up -> down edge nothing did: the other warps came
+    // straight from gate/up's prologue, polled, and could overwrite blocks that late gate/up tiles of THIS CTA were
+    // still multiplying (the two phases' slots overlap when a CTA's gate/up share wraps around its k blocks: the 7B; the
+    // stress run with two lanes found it).  So: wait for the epilogue warps, which have seen every accumulator.
+    if (x_kind == TCD_X_SWIGLU && (p.dataflow & 1)) bar_sync(1, kTC);
     const bool full_scan = gain != nullptr || x_kind == TCD_X_EMBED;
     const int n_iter = full_scan ? K / 8 : n_slots * 8;
     float ss[NB];

@@ -952,19 +952,20 @@ static int tcd_dataflow_bits(const b200llm_engine *e) {
     return bits;
 }
 
-// data-flow bits of a launch with `nb` lanes: with several lanes the gate/up -> down edge goes back to a grid barrier.
-// At 3-4 lanes it does not pay (the (sum, count) pairs are twice the bytes of the sums and every CTA polls its slice of
-// them for every lane: 3B, 4 lanes: 1.716 against 1.757 ms per step).  At 2 lanes it is level in speed, but the stress
-// run of the 7B showed rare token differences with it (3 of 400 launches of 32 steps, always in the second lane; none in
-// 400 launches with the edge off, none with the other two edges alone, and none in > 5000 single-lane launches with all
-// edges on: profiles/sanitizer_r2/README.md).  The cause has not been found, so the edge is used with one lane only.
-static int tcd_dataflow_for(const b200llm_engine *e, int nb) { return nb >= 2 ? (e->tcd_dataflow & ~1) : e->tcd_dataflow; }
+// data-flow bits of a launch with `nb` lanes: with 3-4 lanes the gate/up -> down edge goes back to a grid barrier -- the
+// (sum, count) pairs are twice the bytes of the sums, every CTA polls its slice of them for every lane, and at 3+
+// lanes that costs more than the barrier it saves (3B, 4 lanes: 1.716 against 1.757 ms per step).
+// (B200LLM_TCD_EDGE0_LANES: the most lanes that use the edge.)
+static int tcd_dataflow_for(const b200llm_engine *e, int nb) {
+    static const int edge0_lanes = getenv("B200LLM_TCD_EDGE0_LANES") ? atoi(getenv("B200LLM_TCD_EDGE0_LANES")) : 2;
+    return nb > edge0_lanes ? (e->tcd_dataflow & ~1) : e->tcd_dataflow;
+}
 
 static int tcd_prepare(b200llm_engine *e) {
     const b200llm_config &c = e->cfg;
     e->tcd_dataflow = tcd_dataflow_bits(e);
     const size_t n_jobs = 4 * (size_t)c.n_layers + 1;
-    std::vector<TcdJob> jobs(2 * n_jobs);   // set 0: one lane, set 1: 2-4 lanes
+    std::vector<TcdJob> jobs(2 * n_jobs);   // set 0: all edges, set 1: without the gate/up -> down edge (3-4 lanes)
     const int nq = e->nq_l, nkv = e->nkv_l, ffn = e->ffn_l;   // this rank's share (= the model's at tp 1)
     const int qd = nq * c.head_dim;
     const bool tp = c.tp_size > 1;
@@ -973,7 +974,7 @@ static int tcd_prepare(b200llm_engine *e) {
     float *row_out = tp ? e->delta : e->h;
     const int row_epi = (tp && (e->tcd_dataflow & 8)) ? TCD_EPI_ADD_CNT : TCD_EPI_ADD;
     for (int set = 0; set < 2; ++set) {
-        const int df = tcd_dataflow_for(e, set == 0 ? 1 : 2);
+        const int df = set == 0 ? e->tcd_dataflow : (e->tcd_dataflow & ~1);   // set 1: without the gate/up -> down edge
         TcdJob *jb = jobs.data() + set * n_jobs;
         for (int l = 0; l < c.n_layers; ++l) {
             const LayerW &w = e->layers[l];
@@ -1006,7 +1007,7 @@ static int tcd_decode(b200llm_engine *e, const int32_t *lanes, int nb, int n_ste
     if (!e->tcd_ready || e->tcd_dataflow != tcd_dataflow_bits(e)) B200_TRY(tcd_prepare(e));
     TcdParams p{};
     p.dataflow = tcd_dataflow_for(e, nb), p.gu2 = e->tcd_gu2, p.att2 = e->tcd_att2, p.qkv2 = e->tcd_qkv2;
-    p.jobs = reinterpret_cast<const TcdJob *>(e->mega_jobs) + (nb >= 2 ? 4 * (size_t)c.n_layers + 1 : 0), p.n_layers = c.n_layers;
+    p.jobs = reinterpret_cast<const TcdJob *>(e->mega_jobs) + ((p.dataflow & 1) == (e->tcd_dataflow & 1) ? 0 : 4 * (size_t)c.n_layers + 1), p.n_layers = c.n_layers;
     p.d = c.d, p.n_q = e->nq_l, p.n_kv = e->nkv_l, p.head_dim = c.head_dim, p.ffn = e->ffn_l, p.vocab = e->vocab_l;
     p.kv_page_heads = e->kv_page_heads;
     p.vocab_global = c.vocab, p.tp_rank = c.tp_rank, p.tp_size = c.tp_size;

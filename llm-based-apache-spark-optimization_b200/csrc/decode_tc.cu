@@ -1,35 +1,33 @@
-// decode_tc.cu -- the batch-1 decode step as ONE persistent kernel whose weight stream is
-// consumed by the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM).
+// decode_tc.cu -- a whole decode call (every phase of every step, 1..4 lanes) as ONE persistent kernel whose weight
+// stream is consumed by the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM).
 //
-// decode_mega.cu consumes its ring with mma.sync from registers and is bound by instruction
-// issue at about the HBM rate, so nothing the producer prefetches during a grid barrier is ever
-// caught up on.  Here the consumer is one thread issuing tcgen05.mma straight from shared
-// memory (M = 128 weight rows, N = 8, K = 16 per instruction, 4 KB of weights each; ~64 clk per
-// instruction from one thread, scripts/ubench_umma.cu), i.e. ~120 GB/s per SM against the
-// ~45 GB/s share of the HBM stream, so a ring that filled up during a barrier drains quickly:
-//   warp 13      producer: walks the whole weight schedule (every phase of every step) and pulls
-//                this CTA's share through a shared-memory ring of 16 KB stages (8-10 of them, what
-//                the 227 KB leave beside the operand blocks: tcd_plan), one 1-D TMA bulk copy per
-//                [128 rows x 64 k] tile.  The matrices are stored tile-major and pre-swizzled
-//                (tcd.h), so a tile lands as a ready 128B-swizzled K-major operand and a CTA's
-//                share of a matrix is one contiguous region of HBM.
-//   warp 12      MMA issuer: A = weight tile from the ring, B = the activation vector as
-//                [8 x 64 k] operand blocks (row 0 = bf16 hi part, row 1 = bf16 lo part, rows 2-7
-//                zero; hi + lo is ~fp32 accurate), D[128, 8] fp32 in TMEM; tcgen05.commit hands
-//                ring stages back to the producer and finished accumulators to the epilogue.
-//                Its loop carries no integer division: one modulo per stage cost 5 % of the step.
-//   warps 0-3    epilogue: tcgen05.ld of the warp's 32 accumulator lanes (= weight rows),
-//                (col 0 + col 1) * norm scale, then red.global.add / store.
-//   warps 0-11   phase prologues (activation vector -> operand blocks, fused RMSNorm / SwiGLU /
-//                embedding / merge of split-attention partials), attention, sampling, the grid
-//                barrier.
-// Work split: the (row tile, k block) units of a matrix are numbered tile-major and cut into 148
-// equal contiguous ranges (stream-K), so every CTA streams the same number of bytes (+-16 KB) in
-// every phase; partial sums of a tile meet in global memory with fp32 red.add (the residual
-// stream takes them directly, qkv and gate/up go to zeroed buffers whose consumers apply RoPE /
-// SwiGLU on load).  The lm_head is cut at tile boundaries instead so that logits are plain stores.
-// Tried and dropped: weights as the N = 256 operand, fully dynamic work
-// distribution from an atomic counter, L2 prefetch beyond a full ring, two issuer threads.
+// decode_mega.cu consumes its ring with mma.sync from registers and is bound by instruction issue at about the HBM rate,
+// so nothing the producer prefetches during a grid barrier is ever caught up on.  Here the consumer is a warp issuing
+// tcgen05.mma straight from shared memory (M = 128 weight rows, N = 8, K = 16 per instruction, 4 KB of weights each;
+// ~39 clk per instruction at best, scripts/ubench_umma.cu / ubench_issue.cu), several times this SM's share of the HBM
+// stream, so a ring that filled up during a barrier drains quickly.  148 CTAs x 480 threads:
+//   warp 14      producer: walks the whole weight schedule (every phase of every step) and pulls this CTA's share
+//                through a shared-memory ring of 16 KB stages (an even number, 8 for the 3B: what the 227 KB leave
+//                beside the operand blocks, tcd_plan), one 1-D TMA bulk copy per [128 rows x 64 k] tile.  The matrices
+//                are stored tile-major and pre-swizzled (tcd.h), so a tile lands as a ready 128B-swizzled K-major
+//                operand and a CTA's share of a matrix is one contiguous region of HBM.
+//   warps 12-13  MMA issuers (kTIssuers): stage i of the CTA's stream belongs to issuer i % 2 and ring slot i % n_stages.
+//                A = weight tile from the ring, B = the activations as [8 x 64 k] operand blocks (rows 2b / 2b + 1 =
+//                bf16 hi / lo parts of lane b's activations, hi + lo ~ fp32 accurate; unused rows zero), D[128, 8] fp32
+//                in TMEM (columns 2b / 2b + 1 = lane b); tcgen05.commit hands ring stages back to the producer and
+//                finished accumulators to the epilogue.  The whole warp walks the loop converged and an elected lane
+//                issues, with operands in uniform registers; no integer division in the loop.
+//   warps 0-3    epilogue: tcgen05.ld of the warp's 32 accumulator lanes (= weight rows), (hi + lo column) * norm
+//                scale per lane, then red.global.add (plain, or (sum, 1) pairs where the consumer polls) / store.
+//   warps 0-11   phase prologues (activations -> operand blocks, fused RMSNorm / SwiGLU / embedding / merge of
+//                split-attention partials), attention, argmax or the sampler chain, grid barriers.
+// Work split: the (row tile, k block) units of a matrix are numbered tile-major and cut into 148 equal contiguous ranges
+// (stream-K), so every CTA streams the same number of bytes (+-16 KB) in every phase; partial sums of a tile meet in
+// global memory with fp32 red.add (the residual stream takes them directly, qkv and gate/up go to zeroed buffers whose
+// consumers apply RoPE / SwiGLU on load).  The lm_head is cut at tile boundaries instead so that logits are plain stores.
+// Synchronisation between phases is by data where a phase has one consumer (TcdParams::dataflow), else a grid barrier.
+// Tried and dropped: weights as the N = 256 operand, fully dynamic work distribution from an atomic
+// counter, L2 prefetch beyond a full ring, tensor memory as ring overflow.
 #include "common.cuh"
 #include "kernels.h"
 #include "tcd.h"

@@ -7,7 +7,8 @@
 // q on load, and the current token's k/v by warp 0 of the item that owns the last page, which
 // rounds them to bf16, starts its running softmax with them and appends them to the KV page for
 // the steps to come.  The page loop masks the current position out of the cache reads.
-// Work items = (kv head, split); item i runs on CTA i % G.  With more than one split the items
+// Work items = (lane, kv head, split), lane after lane, each lane with its own position, page table and split count
+// (tcd_att_item); item i runs on CTA i % G.  With more than one split the items
 // leave (max, sum, unnormalised output) partials in part_ml / part_o and the next phase's
 // prologue merges them while it builds its operand (tcd_prologue, TCD_X_ATT).
 #pragma once

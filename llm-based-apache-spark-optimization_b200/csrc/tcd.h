@@ -1,4 +1,4 @@
-// tcd.h -- parameters of the tcgen05 persistent batch-1 decode kernel (decode_tc.cu).
+// tcd.h -- parameters of the tcgen05 persistent decode kernel (decode_tc.cu): one launch = n_steps decode steps of 1..4 lanes.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -29,7 +29,7 @@ struct TcdParams {
     int32_t kv_page_heads;   // (kv head, 16-token) tiles from one KV page to the next: n_kv in a pool of this engine's own, more in a shared pool
     float rms_eps;
     float scale_log2;     // log2(e) / sqrt(head_dim)
-    // activations (fp32), one row (batch 1)
+    // activations (fp32), one row per lane (lane b at base + b * row size, see `nb` below)
     float *h;             // residual stream [d]
     float *qkv;           // raw q|k|v sums of the current layer [(n_q + 2 n_kv) * head_dim], q/k rows pair-interleaved
     float *att;           // attention output [n_q * head_dim]
